@@ -1,0 +1,226 @@
+"""Generate tests/golden/*.npz by RUNNING THE REFERENCE ITSELF (imported read-only from
+/root/reference) -- TEST INFRASTRUCTURE, see oracle/__init__.py.
+
+Run in the build container only (the reference does not exist on the GPU box):
+
+    PYTHONDONTWRITEBYTECODE=1 python -m oracle.make_golden
+
+The reference ships no golden vectors, so these files are what pins the
+oracle (tests/test_oracle_golden.py) and, through it, the CUDA path.  Inputs and weights are
+re-derived from seeds by the oracle's own generators (platform-stable CPU torch.Generator
+streams); every file carries checksums of them so a mismatch is detected instead of silently
+comparing different problems.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = os.environ.get("MRISR_REFERENCE", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
+
+BIG = 4096  # tensors above this many elements are stored as (head, norm, sum) instead of in full
+
+
+def _import_reference():
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, REF)
+    from models.unet_model import UNetSuperRes          # noqa
+    import utils.losses as ref_losses                   # noqa
+    sys.path.pop(0)
+    return UNetSuperRes, ref_losses
+
+
+def _summ(t: torch.Tensor) -> dict:
+    t = t.detach().to(torch.float64).flatten()
+    return {"norm": float(t.norm()), "sum": float(t.sum()), "head": t[:512].to(torch.float32).numpy()}
+
+
+def _store_tensor(d: dict, key: str, t: torch.Tensor) -> None:
+    t = t.detach()
+    if t.numel() <= BIG:
+        d[key] = t.to(torch.float32).numpy()
+    else:
+        s = _summ(t)
+        d[key + "@head"] = s["head"]
+        d[key + "@norm"] = np.float64(s["norm"])
+        d[key + "@sum"] = np.float64(s["sum"])
+
+
+def _checksum_params(params) -> np.ndarray:
+    return np.array([float(sum(v.double().sum() for v in params.values())),
+                     float(sum((v.double() ** 2).sum() for v in params.values()))])
+
+
+def unet_case(UNetSuperRes, ref_losses, name, f, n, h, w, affine, ssim_weight, full_out=True):
+    from oracle.unet_oracle import init_params, randomize_affine
+    from oracle.synth import make_pairs
+    params = init_params(f, seed=1234)
+    if affine:
+        params = randomize_affine(params)
+    x, target = make_pairs(n, h, w, seed=1234)
+    model = UNetSuperRes(1, 1, base_filters=f)
+    model.load_state_dict(params, strict=True)          # the reference's own strict key/shape check
+    model.train()
+    crit = ref_losses.CombinedLoss(ssim_weight=ssim_weight, perceptual_weight=0.0)
+    metric = ref_losses.SSIM(device=torch.device("cpu"))
+    out = model(x)
+    out.retain_grad()
+    loss = crit(out, target)
+    loss.backward()
+    d = {"meta": np.array([f, n, h, w, int(affine)]), "ssim_weight": np.float64(ssim_weight),
+         "param_checksum": _checksum_params(params),
+         "x_checksum": np.array([float(x.double().sum()), float(target.double().sum())]),
+         "loss": np.float64(loss.item()),
+         "l1": np.float64((out - target).abs().mean().item()),
+         "ssim": np.float64(metric(out, target).item())}
+    if full_out:
+        d["out"] = out.detach().numpy()
+        d["dout"] = out.grad.numpy()
+    else:
+        _store_tensor(d, "out", out)
+        _store_tensor(d, "dout", out.grad)
+    for k, v in model.named_parameters():
+        _store_tensor(d, "grad:" + k, v.grad)
+    # intermediate activations after each encoder/decoder block (hooked from the reference modules)
+    feats = {}
+    hooks = []
+    for mod_name in ("inc", "down1", "down2", "down3", "up1", "up2", "up3"):
+        hooks.append(getattr(model, mod_name).register_forward_hook(
+            lambda m, i, o, k=mod_name: feats.__setitem__(k, o.detach())))
+    with torch.no_grad():
+        model(x)
+    for hk in hooks:
+        hk.remove()
+    for k, v in feats.items():
+        _store_tensor(d, "act:" + k, v)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **d)
+    print(name, "loss", d["loss"], "ssim", d["ssim"])
+
+
+def loss_cases(ref_losses):
+    """SSIM / CombinedLoss goldens on assorted shapes, incl. gradient wrt output."""
+    g = torch.Generator("cpu").manual_seed(77)
+    d = {}
+    shapes = [(1, 1, 16, 16), (2, 1, 40, 56), (3, 1, 64, 64), (1, 1, 11, 23), (2, 1, 96, 72)]
+    for i, shp in enumerate(shapes):
+        base = torch.rand(shp, generator=g)
+        base = torch.nn.functional.avg_pool2d(base, 5, 1, 2)
+        base = (base - base.amin()) / (base.amax() - base.amin())
+        pred = (base + 0.08 * torch.randn(shp, generator=g)).clamp(0, 1)
+        d[f"s{i}:target"] = base.numpy()
+        d[f"s{i}:pred"] = pred.numpy()
+        d[f"s{i}:ssim"] = np.float64(ref_losses.ssim(pred, base).item())
+        d[f"s{i}:ssim_per_sample"] = ref_losses.ssim(pred, base, size_average=False).numpy()
+        for j, (sw,) in enumerate([(0.4,), (0.0,), (1.0,), (0.3,)]):
+            p = pred.clone().requires_grad_(True)
+            crit = ref_losses.CombinedLoss(ssim_weight=sw)
+            loss = crit(p, base)
+            loss.backward()
+            d[f"s{i}:w{j}:sw"] = np.float64(sw)
+            d[f"s{i}:w{j}:loss"] = np.float64(loss.item())
+            d[f"s{i}:w{j}:grad"] = p.grad.numpy()
+    # identical images -> ssim == 1, clamp edge
+    x = torch.rand((1, 1, 32, 32), generator=g)
+    d["ident:ssim"] = np.float64(ref_losses.ssim(x, x).item())
+    # window taps as printed by the reference
+    d["taps"] = ref_losses.gaussian_window(11, 1.5).numpy()
+    d["window2d"] = ref_losses.create_window(11, 1, 1.5, torch.device("cpu")).numpy()
+    np.savez_compressed(os.path.join(OUT, "losses.npz"), **d)
+    print("losses: ", {k: float(v) for k, v in d.items() if k.endswith(":ssim")})
+
+
+def perceptual_case(ref_losses):
+    """CombinedLoss with the VGG19[:36] branch; ImageNet weights are not on disk / no network, so
+    torchvision.models.vgg19 is patched to weights=None and the oracle's seeded tensors are
+    loaded into it."""
+    import torchvision.models as tvm
+    from oracle.losses_oracle import make_vgg_params
+    from oracle.synth import make_pairs
+    vggp = make_vgg_params(seed=1235)
+    orig = tvm.vgg19
+
+    def patched(weights=None, **kw):
+        m = orig(weights=None, **kw)
+        convs = [l for l in m.features if isinstance(l, torch.nn.Conv2d)]
+        with torch.no_grad():
+            for l, (wt, b) in zip(convs, vggp):
+                l.weight.copy_(wt)
+                l.bias.copy_(b)
+        return m
+
+    tvm.vgg19 = patched
+    try:
+        d = {}
+        _, hr = make_pairs(2, 32, 32, seed=99)             # HR 64x64
+        g = torch.Generator("cpu").manual_seed(5)
+        pred0 = (hr + 0.1 * torch.randn(hr.shape, generator=g)).clamp(0, 1)
+        d["pred"] = pred0.numpy()
+        d["target"] = hr.numpy()
+        for tag, (sw, pw, typ) in {"a": (0.4, 0.1, "l1"), "b": (0.0, 1.0, "l2"), "c": (0.3, 0.2, "mse")}.items():
+            crit = ref_losses.CombinedLoss(ssim_weight=sw, perceptual_weight=pw, perceptual_loss_type=typ)
+            p = pred0.clone().requires_grad_(True)
+            loss = crit(p, hr)
+            loss.backward()
+            with torch.no_grad():
+                feats = crit.perceptual_loss.feature_extractor(pred0)
+                perc = crit.perceptual_loss(pred0, hr)
+            d[f"{tag}:cfg"] = np.array([sw, pw, {"l1": 1, "l2": 2, "mse": 2}[typ]])
+            d[f"{tag}:loss"] = np.float64(loss.item())
+            d[f"{tag}:perc"] = np.float64(perc.item())
+            d[f"{tag}:grad"] = p.grad.numpy()
+            if tag == "a":
+                _store_tensor(d, "feat", feats)
+        np.savez_compressed(os.path.join(OUT, "perceptual.npz"), **d)
+        print("perceptual:", {k: float(v) for k, v in d.items() if k.endswith("loss") or k.endswith("perc")})
+    finally:
+        tvm.vgg19 = orig
+
+
+def train_case(UNetSuperRes, ref_losses):
+    """Three reference train steps (scripts/train.py:296-323 body) at f=16."""
+    from oracle.unet_oracle import init_params, randomize_affine
+    from oracle.synth import make_pairs
+    params = randomize_affine(init_params(16, seed=1234))
+    model = UNetSuperRes(1, 1, base_filters=16)
+    model.load_state_dict(params, strict=True)
+    model.train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-5)   # lr raised so 3 steps move visibly
+    crit = ref_losses.CombinedLoss(ssim_weight=0.4)
+    metric = ref_losses.SSIM(device=torch.device("cpu"))
+    losses, ssims = [], []
+    for step in range(3):
+        x, t = make_pairs(2, 32, 32, seed=500 + step)
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = crit(out, t)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+        with torch.no_grad():
+            ssims.append(metric(out, t).item())
+    d = {"losses": np.array(losses), "ssims": np.array(ssims)}
+    for k, v in model.state_dict().items():
+        _store_tensor(d, "param:" + k, v)
+    np.savez_compressed(os.path.join(OUT, "train3.npz"), **d)
+    print("train3 losses", losses)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(os.cpu_count() or 1)
+    UNetSuperRes, ref_losses = _import_reference()
+    unet_case(UNetSuperRes, ref_losses, "unet_f16_n2_h32", 16, 2, 32, 32, True, 0.4)
+    unet_case(UNetSuperRes, ref_losses, "unet_f16_n1_h24x40", 16, 1, 24, 40, True, 0.3)
+    unet_case(UNetSuperRes, ref_losses, "unet_f32_n1_h64", 32, 1, 64, 64, False, 0.4, full_out=True)
+    loss_cases(ref_losses)
+    perceptual_case(ref_losses)
+    train_case(UNetSuperRes, ref_losses)
+
+
+if __name__ == "__main__":
+    main()
