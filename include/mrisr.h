@@ -1,0 +1,108 @@
+/*
+ * mrisr.h -- C ABI of the B200-native U-Net super-resolution hot path.
+ *
+ * The reference (rdd0582/mri_superresolution) is pure Python/PyTorch and has no FFI or plugin
+ * interface of its own: its seam for this path is the nn.Module API
+ *   models/unet_model.py:129,189   UNetSuperRes.__init__/forward
+ *   utils/losses.py:27             ssim()
+ *   utils/losses.py:159,200        CombinedLoss.__init__/forward
+ *   utils/losses.py:242            SSIM
+ *   scripts/train.py:186,296-323   Adam + train-step body
+ *   scripts/infer.py:268-276       inference body
+ * Each entry point below states which of those it replaces.  The Python mirror of the module
+ * API (mri_superresolution_b200/models/unet_model.py, utils/losses.py) calls ONLY these
+ * functions (ctypes, raw device pointers); INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; nothing is allocated or freed by
+ *     the library: the caller owns all memory, including the workspace.
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), never
+ *     synchronises, is re-entrant and CUDA-graph capturable.
+ *   - return value: 0 ok; > 0 a cudaError_t; < 0 an MRISR_E_* argument error.
+ *     mrisr_last_error() returns a thread-local message for the last non-zero return.
+ *   - images are N x 1 x H x W fp32, dense NCHW (== NHWC for one channel).
+ *   - parameters / gradients / Adam moments are flat fp32 arenas laid out in the reference's
+ *     parameter registration order (models/unet_model.py:129-175); see
+ *     mrisr_unet_param_offset().  The checkpoint layout (state_dict keys) is owned by Python.
+ */
+#ifndef MRISR_H
+#define MRISR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRISR_VERSION 100
+
+#define MRISR_E_BADARG   (-1)   /* null pointer / non-positive size */
+#define MRISR_E_SHAPE    (-2)   /* H or W not a multiple of 8, base_filters not a multiple of 16 */
+#define MRISR_E_DTYPE    (-3)   /* unknown precision mode */
+#define MRISR_E_WORKSPACE (-4)  /* workspace too small */
+#define MRISR_E_STATE    (-5)   /* backward without a matching train-mode forward */
+
+#define MRISR_FP32 0            /* activations fp32, CUDA-core convolutions (parity mode, 1e-4) */
+#define MRISR_BF16 1            /* activations/operands bf16, fp32 accumulate, tcgen05 convolutions */
+
+int mrisr_version(void);
+const char* mrisr_last_error(void);
+
+/* ---- parameter arena layout (models/unet_model.py:129-175 registration order) ------------- */
+/* number of parameter tensors (64) and total fp32 elements (1 823 122 at f = 32) */
+int      mrisr_unet_param_tensors(int base_filters);
+int64_t  mrisr_unet_param_elems(int base_filters);
+/* element offset of tensor `index` in the arena, and its element count */
+int64_t  mrisr_unet_param_offset(int base_filters, int index);
+int64_t  mrisr_unet_param_size(int base_filters, int index);
+
+/* ---- U-Net forward / backward (replaces UNetSuperRes.forward + its autograd graph) -------- */
+/* bytes of caller-owned workspace for one (N,H,W,f,precision) problem.  `train` != 0 keeps every
+ * tensor the backward pass needs.  The workspace must be ZERO-FILLED once before its first
+ * use with a given shape (zero borders of the padded NHWC activations are an invariant that the
+ * kernels preserve) and may then be reused for every later call of the same shape. */
+size_t mrisr_unet_workspace_bytes(int N, int H, int W, int base_filters, int precision, int train);
+
+/* x: N x 1 x H x W fp32  ->  y: N x 1 x 2H x 2W fp32 (sigmoid output, models/unet_model.py:211) */
+int mrisr_unet_forward(const float* params, const float* x, float* y, void* workspace, size_t workspace_bytes,
+                       int N, int H, int W, int base_filters, int precision, int train, void* stream);
+
+/* dy: gradient wrt y (N x 1 x 2H x 2W fp32); y: the forward output itself (sigmoid backward needs it);
+ * grads: flat fp32 arena, OVERWRITTEN (not accumulated) with d(loss)/d(param); dx: must be NULL (the
+ * reference never asks for the gradient wrt the input image, scripts/train.py:296-318).  Must follow
+ * a train-mode mrisr_unet_forward on the same workspace with the same params. */
+int mrisr_unet_backward(const float* params, const float* dy, const float* y, float* grads, float* dx,
+                        void* workspace, size_t workspace_bytes, int N, int H, int W, int base_filters,
+                        int precision, void* stream);
+
+/* ---- fused L1 + SSIM loss and gradient (replaces utils/losses.py:27-81,200-226) ------------ */
+/* out5 (device, 5 floats): [0] mean|p-t|  [1] unclamped SSIM  [2] total = l1_w*L1 + ssim_w*(1-clamp(ssim,0,1))
+ *                          [3], [4] reserved (perceptual term, total incl. perceptual).
+ * dpred (nullable): d(total)/d(pred), N x 1 x H x W fp32.  `scratch` >= mrisr_l1_ssim_scratch_bytes(). */
+size_t mrisr_l1_ssim_scratch_bytes(int N, int H, int W);
+int mrisr_l1_ssim_fwd_bwd(const float* pred, const float* target, float* dpred, float* out5, void* scratch,
+                          int N, int H, int W, float l1_weight, float ssim_weight,
+                          int window_size, float sigma, float val_range, void* stream);
+/* SSIM metric only (utils/losses.py:242-266): per_sample[n] = mean SSIM map of sample n */
+int mrisr_ssim_forward(const float* img1, const float* img2, float* per_sample, void* scratch,
+                       int N, int H, int W, int window_size, float sigma, float val_range, void* stream);
+
+/* ---- fused Adam (replaces torch.optim.Adam(lr, weight_decay) of scripts/train.py:186,318) -- */
+/* L2 weight decay folded into the gradient (torch.optim.Adam semantics, not AdamW);
+ * grad_scale multiplies g first (1/world_size for data parallel, 1/loss_scale for AMP). */
+int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                    float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                    float grad_scale, void* stream);
+
+/* ---- debugging aid: copy one internal workspace tensor out as dense NCHW fp32 --------------- */
+/* kind: 0 raw conv output R[l], 1 activation A[l], 2 pooled P[l], 3 low-res 1x1 output Q[l], 4 dR[l], 5 G[l]
+ * (gradient wrt the input of conv l), 6 dQ[l], 7 UB, 8 XM (blend), 9 DY3.  dims_host[4] (HOST) receives N,C,H,W;
+ * `out` may be NULL to query dims only.  Used by tests to localise a parity failure to one layer. */
+int mrisr_unet_debug_tensor(void* workspace, int N, int H, int W, int base_filters, int precision, int kind,
+                            int layer, float* out, int* dims_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRISR_H */

@@ -1,0 +1,107 @@
+// Shared device/host helpers for the mrisr sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+namespace mrisr {
+
+constexpr int kGroups = 8;            // GroupNorm(8, C)   models/unet_model.py:30
+constexpr float kGnEps = 1e-5f;       // torch.nn.GroupNorm default
+constexpr float kSlope = 0.2f;        // LeakyReLU(0.2)    models/unet_model.py:31
+
+void set_error(const char* fmt, ...);
+const char* g_err_ptr();
+
+#define MRISR_CUDA_CHECK(expr)                                                              \
+    do {                                                                                    \
+        cudaError_t _e = (expr);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            ::mrisr::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return (int)_e;                                                                 \
+        }                                                                                   \
+    } while (0)
+
+#define MRISR_LAUNCH_CHECK() MRISR_CUDA_CHECK(cudaGetLastError())
+
+// Padded NHWC activation view: [N][H+2][W+2][C], zero one-pixel border kept as an invariant.
+// `p` points at the padded origin (n=0, row -1, col -1, c=0).
+template <typename T>
+struct Act {
+    T* p;
+    int N, H, W, C;
+    __host__ __device__ __forceinline__ int pw() const { return W + 2; }
+    __host__ __device__ __forceinline__ int64_t sample_stride() const { return (int64_t)(H + 2) * (W + 2) * C; }
+    // offset of interior pixel (y, x) in [0,H) x [0,W)
+    __host__ __device__ __forceinline__ int64_t off(int n, int y, int x) const {
+        return n * sample_stride() + ((int64_t)(y + 1) * (W + 2) + (x + 1)) * C;
+    }
+};
+
+__device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : kSlope * z; }
+__device__ __forceinline__ float lrelu_grad(float z) { return z > 0.f ? 1.f : kSlope; }
+
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// 8-channel vector load/store (16 B for bf16, 32 B for fp32); pointers must be 8-element aligned.
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    const float4 b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 r = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+}
+__device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 r;
+    r.x = pack_bf16x2(v[0], v[1]); r.y = pack_bf16x2(v[2], v[3]);
+    r.z = pack_bf16x2(v[4], v[5]); r.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Bilinear x2, align_corners=True source coordinates exactly as ATen computes them
+// (area_pixel_compute_scale: scale = (in-1)/(out-1) in float; src = scale*dst; i0 = (int)src).
+struct Lerp { int i0, i1; float w1; };
+__host__ __device__ __forceinline__ float up_scale(int in_size) {
+    const int out_size = 2 * in_size;
+    return out_size > 1 ? (float)(in_size - 1) / (float)(out_size - 1) : 0.f;
+}
+__device__ __forceinline__ Lerp up_coord(int dst, int in_size, float scale) {
+    const float s = scale * (float)dst;
+    Lerp l;
+    l.i0 = (int)s;
+    l.i1 = l.i0 + (l.i0 < in_size - 1 ? 1 : 0);
+    l.w1 = s - (float)l.i0;
+    return l;
+}
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+}  // namespace mrisr

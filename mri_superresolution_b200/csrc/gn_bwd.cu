@@ -1,0 +1,294 @@
+// Backward of conv -> GroupNorm(8) -> LeakyReLU(0.2) blocks: given a description of the gradient
+// wrt the activation ("source": plain tensor, + max-pool routing, rank-1 final-conv form, blend /
+// pixel-shuffle adjoints) produce the gradient wrt the raw conv output, d(gamma), d(beta).
+// The reference has no hand-written backward (autograd of models/unet_model.py:29-37,52,93,110-113,
+// 206-211); formulas: z = gamma*xh + beta, xh = (r-mean)*rstd, dz = dA*lrelu'(z),
+//   dr = rstd * (gamma*dz - mean_g(gamma*dz) - xh * mean_g(gamma*dz*xh)).
+#include "kernels.cuh"
+
+namespace mrisr {
+namespace {
+constexpr int NTHR = 256;
+constexpr int UNITS_PER_THREAD = 8;
+
+template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
+
+// Per-thread context for 8 channels of one sample
+struct ChanCtx {
+    float sc[8], sh[8], mean[8], rstd[8], gam[8];
+};
+
+template <typename T, int KIND>
+__device__ __forceinline__ void load_ctx(const GnBwdArgs<T>& a, int n, int cv, ChanCtx& c) {
+    const int gs = a.r.C / kGroups;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int ch = cv * 8 + k, g = ch / gs;
+        const int pc = KIND == SRC_BLEND_PS ? ch / 4 : ch;
+        c.mean[k] = a.stats[(n * kGroups + g) * 2];
+        c.rstd[k] = a.stats[(n * kGroups + g) * 2 + 1];
+        c.gam[k] = a.gamma[pc];
+        c.sc[k] = c.gam[k] * c.rstd[k];
+        c.sh[k] = a.beta[pc] - c.mean[k] * c.sc[k];
+    }
+}
+
+// Computes xh and dz for one unit (1 pixel, or a 2x2 window for the pool kinds).
+// dl_out: (SRC_OUTER) dl of the pixel; act_out: lrelu(z) (SRC_OUTER weight gradient)
+template <typename T, int KIND, int P>
+__device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx& c, int n, int uy, int ux, int cv,
+                                           float (&xh)[P][8], float (&dz)[P][8], float& dl_out, float (&act_out)[8]) {
+    float z[P][8];
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+        const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+        float v[8];
+        load8(a.r.p + a.r.off(n, y, x) + cv * 8, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            xh[q][k] = (v[k] - c.mean[k]) * c.rstd[k];
+            z[q][k] = fmaf(v[k], c.sc[k], c.sh[k]);
+        }
+        float dA[8];
+        if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
+            load8(a.g.p + a.g.off(n, y, x) + a.coff + cv * 8, dA);
+        } else if (KIND == SRC_BLEND_BIL) {
+            const float al = 1.f / (1.f + __expf(-a.alpha[0]));
+            load8(a.g.p + a.g.off(n, y, x) + cv * 8, dA);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dA[k] *= al;
+        } else if (KIND == SRC_BLEND_PS) {
+            const float om = 1.f - 1.f / (1.f + __expf(-a.alpha[0]));
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int ch = cv * 8 + k, cs = ch >> 2, i = (ch >> 1) & 1, j = ch & 1;
+                dA[k] = om * to_f(a.g.p[a.g.off(n, 2 * y + i, 2 * x + j) + cs]);
+            }
+        } else if (KIND == SRC_OUTER) {
+            const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
+            const float yy = a.y[pi];
+            const float dl = a.dy[pi] * yy * (1.f - yy);
+            dl_out = dl;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                dA[k] = dl * a.wvec[cv * 8 + k];
+                act_out[k] = lrelu(z[q][k]);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dA[k] = 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dz[q][k] = dA[k];
+    }
+    if (KindTraits<KIND>::pool) {
+        // route the pooled gradient to the first maximum in scan order (ATen max_pool2d uses '>'),
+        // comparing the activations as stored by the forward pass (rounded to T)
+        float gp[8];
+        load8(a.gpool.p + a.gpool.off(n, uy, ux) + cv * 8, gp);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            int best = 0;
+            float bv = to_f(from_f<T>(lrelu(z[0][k])));
+#pragma unroll
+            for (int q = 1; q < P; ++q) {
+                const float vq = to_f(from_f<T>(lrelu(z[q][k])));
+                if (vq > bv) { bv = vq; best = q; }
+            }
+#pragma unroll
+            for (int q = 0; q < P; ++q) dz[q][k] += (q == best) ? gp[k] : 0.f;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < P; ++q)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dz[q][k] *= lrelu_grad(z[q][k]);
+}
+
+// part layout: [N][slots][3][C+8]  (row 0: sum dz, row 1: sum dz*xh, row 2: SRC_OUTER sum dl*act; column C: sum dl)
+template <typename T, int KIND>
+__global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int units_per_block) {
+    constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
+    __shared__ float s_red[3][2048];
+    __shared__ float s_dl[NTHR];
+    const int C = a.r.C, nv = C / 8, PL = NTHR / nv;
+    const int tid = threadIdx.x, cv = tid % nv, pl = tid / nv;
+    const int n = blockIdx.y;
+    const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
+    float s1[8], s2[8], s3[8], sdl = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
+    if (pl < PL) {
+        ChanCtx c;
+        load_ctx<T, KIND>(a, n, cv, c);
+        const int u_end = min(UH * UW, (int)(blockIdx.x + 1) * units_per_block);
+        for (int u = blockIdx.x * units_per_block + pl; u < u_end; u += PL) {
+            float xh[P][8], dz[P][8], act[8], dl = 0.f;
+            unit_grads<T, KIND, P>(a, c, n, u / UW, u % UW, cv, xh, dz, dl, act);
+#pragma unroll
+            for (int q = 0; q < P; ++q)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { s1[k] += dz[q][k]; s2[k] += dz[q][k] * xh[q][k]; }
+            if (KIND == SRC_OUTER) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
+                if (cv == 0) sdl += dl;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s_red[0][pl * C + cv * 8 + k] = s1[k];
+            s_red[1][pl * C + cv * 8 + k] = s2[k];
+            s_red[2][pl * C + cv * 8 + k] = s3[k];
+        }
+    }
+    s_dl[tid] = sdl;
+    __syncthreads();
+    const int64_t row = (int64_t)(C + 8);
+    float* out = a.part + ((int64_t)n * gridDim.x + blockIdx.x) * 3 * row;
+    for (int i = tid; i < 3 * C; i += NTHR) {
+        const int which = i / C, ch = i % C;
+        float t = 0.f;
+        for (int j = 0; j < PL; ++j) t += s_red[which][j * C + ch];
+        out[which * row + ch] = t;
+    }
+    if (KIND == SRC_OUTER && tid == 0) {
+        float t = 0.f;
+        for (int j = 0; j < NTHR; ++j) t += s_dl[j];
+        out[C] = t;
+    }
+}
+
+// blocks [0, N*8): m1, m2 per (n, group).  blocks [N*8, N*8 + C): per-channel parameter gradients.
+template <typename T, int KIND>
+__global__ void gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_count) {
+    const int C = a.r.C, gs = C / kGroups, N = a.r.N;
+    const int64_t row = (int64_t)(C + 8);
+    const int lane = threadIdx.x;
+    if ((int)blockIdx.x < N * kGroups) {
+        const int n = blockIdx.x / kGroups, g = blockIdx.x % kGroups;
+        double m1 = 0.0, m2 = 0.0;
+        for (int i = lane; i < slots * gs; i += 32) {
+            const int s = i / gs, ch = g * gs + i % gs;
+            const float* q = a.part + ((int64_t)n * slots + s) * 3 * row;
+            const double gm = (double)a.gamma[KIND == SRC_BLEND_PS ? ch / 4 : ch];
+            m1 += gm * (double)q[ch];
+            m2 += gm * (double)q[row + ch];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m1 += __shfl_xor_sync(0xffffffffu, m1, o);
+            m2 += __shfl_xor_sync(0xffffffffu, m2, o);
+        }
+        if (lane == 0) {
+            a.mstat[blockIdx.x * 2] = (float)(m1 * inv_count);
+            a.mstat[blockIdx.x * 2 + 1] = (float)(m2 * inv_count);
+        }
+    } else {
+        // one block per parameter channel pc; raw channels mapping to it: [pc*rep, (pc+1)*rep)
+        const int rep = KIND == SRC_BLEND_PS ? 4 : 1;
+        const int pc = blockIdx.x - N * kGroups;
+        double d1 = 0.0, d2 = 0.0, d3 = 0.0, d4 = 0.0;
+        for (int i = lane; i < N * slots * rep; i += 32) {
+            const int ch = pc * rep + i % rep;
+            const float* q = a.part + (int64_t)(i / rep) * 3 * row;
+            d1 += (double)q[ch];
+            d2 += (double)q[row + ch];
+            if (KIND == SRC_OUTER) {
+                d3 += (double)q[2 * row + ch];
+                if (pc == 0) d4 += (double)q[C];
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            d1 += __shfl_xor_sync(0xffffffffu, d1, o);
+            d2 += __shfl_xor_sync(0xffffffffu, d2, o);
+            d3 += __shfl_xor_sync(0xffffffffu, d3, o);
+            d4 += __shfl_xor_sync(0xffffffffu, d4, o);
+        }
+        if (lane == 0) {
+            a.dbeta[pc] = (float)d1;
+            a.dgamma[pc] = (float)d2;
+            if (KIND == SRC_OUTER) {
+                a.dwvec[pc] = (float)d3;
+                if (pc == 0) a.dbias[0] = (float)d4;
+            }
+        }
+    }
+}
+
+template <typename T, int KIND>
+__global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a) {
+    constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
+    const int C = a.r.C, nv = C / 8, gs = C / kGroups;
+    const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
+    const int64_t total = (int64_t)a.r.N * UH * UW * nv;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % nv);
+        const int ux = (int)((i / nv) % UW), uy = (int)((i / ((int64_t)nv * UW)) % UH);
+        const int n = (int)(i / ((int64_t)nv * UW * UH));
+        ChanCtx c;
+        load_ctx<T, KIND>(a, n, cv, c);
+        float xh[P][8], dz[P][8], act[8], dl;
+        unit_grads<T, KIND, P>(a, c, n, uy, ux, cv, xh, dz, dl, act);
+        float m1[8], m2[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int g = (cv * 8 + k) / gs;
+            m1[k] = a.mstat[(n * kGroups + g) * 2];
+            m2[k] = a.mstat[(n * kGroups + g) * 2 + 1];
+        }
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+            const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = c.rstd[k] * (c.gam[k] * dz[q][k] - m1[k] - xh[q][k] * m2[k]);
+            store8(a.dr.p + a.dr.off(n, y, x) + cv * 8, o);
+        }
+    }
+}
+
+template <typename T, int KIND>
+int run(const GnBwdArgs<T>& a, cudaStream_t s) {
+    constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
+    const int C = a.r.C, nv = C / 8, PL = NTHR / nv;
+    const int units = (a.r.H / (P == 4 ? 2 : 1)) * (a.r.W / (P == 4 ? 2 : 1));
+    const int upb = PL * UNITS_PER_THREAD;
+    const int slots = ceil_div(units, upb);
+    dim3 grid(slots, a.r.N);
+    gn_bwd_reduce_kernel<T, KIND><<<grid, NTHR, 0, s>>>(a, upb);
+    MRISR_LAUNCH_CHECK();
+    const int pcs = KIND == SRC_BLEND_PS ? C / 4 : C;
+    const double inv_count = 1.0 / ((double)(C / kGroups) * a.r.H * a.r.W);
+    gn_bwd_finalize_kernel<T, KIND><<<a.r.N * kGroups + pcs, 32, 0, s>>>(a, slots, inv_count);
+    MRISR_LAUNCH_CHECK();
+    int64_t total = (int64_t)a.r.N * units * nv;
+    int64_t blocks = ceil_div64(total, NTHR);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    gn_bwd_apply_kernel<T, KIND><<<(unsigned)blocks, NTHR, 0, s>>>(a);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+}  // namespace
+
+int gn_bwd_slots(int H, int W, int C) {
+    const int PL = NTHR / (C / 8);
+    return ceil_div(H * W, PL * UNITS_PER_THREAD);   // upper bound (pool kinds use a quarter of the units)
+}
+
+template <typename T>
+int launch_gn_bwd(const GnBwdArgs<T>& a, cudaStream_t s) {
+    switch (a.kind) {
+        case SRC_DIRECT: return run<T, SRC_DIRECT>(a, s);
+        case SRC_DIRECT_POOL: return run<T, SRC_DIRECT_POOL>(a, s);
+        case SRC_OUTER: return run<T, SRC_OUTER>(a, s);
+        case SRC_BLEND_BIL: return run<T, SRC_BLEND_BIL>(a, s);
+        case SRC_BLEND_PS: return run<T, SRC_BLEND_PS>(a, s);
+        default: set_error("gn_bwd: bad source kind %d", a.kind); return -1;
+    }
+}
+template int launch_gn_bwd<float>(const GnBwdArgs<float>&, cudaStream_t);
+template int launch_gn_bwd<__nv_bfloat16>(const GnBwdArgs<__nv_bfloat16>&, cudaStream_t);
+
+}  // namespace mrisr

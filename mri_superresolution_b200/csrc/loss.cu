@@ -1,0 +1,260 @@
+// Fused L1 + Gaussian-window SSIM loss and gradient (one pass over pred/target, one write of dpred).
+// Forward follows utils/losses.py:27-81 (five zero-padded 'same' depthwise Gaussian filters, C1=(0.01R)^2,
+// C2=(0.03R)^2, global mean) and :200-226 (l1_w*mean|p-t| + ssim_w*(1-clamp(ssim,0,1))).
+// The reference has no hand-written gradient; the analytic form used here (SURVEY.md 8(a) L2'):
+//   A1=2*mu1*mu2+C1, A2=2*s12+C2, B1=mu1^2+mu2^2+C1, B2=s11+s22+C2, S=A1*A2/(B1*B2)
+//   dE11 = -S/B2;  dE12 = 2*A1/(B1*B2);  dmu1 = 2*mu2*(A2-A1)/(B1*B2) - 2*mu1*S/B1 + 2*mu1*S/B2
+//   d mean(S)/d x = ( w*dmu1 + 2x (w*dE11) + y (w*dE12) ) / numel     (w* = same zero-padded filter)
+#include "kernels.cuh"
+#include <math.h>
+
+namespace mrisr {
+namespace {
+constexpr int T = 32;          // output tile edge
+constexpr int NTHR = 256;
+
+struct Taps { float w[11]; };
+
+template <int R, bool GRAD>
+struct Geo {
+    static constexpr int HALO = GRAD ? 2 * R : R;
+    static constexpr int IN = T + 2 * HALO;        // staged input edge
+    static constexpr int MID = GRAD ? T + 2 * R : T;  // edge of the SSIM-map region
+    static constexpr size_t smem_floats = 2 * IN * IN + 5 * IN * MID + (GRAD ? 3 * MID * MID : 0);
+};
+
+// scratch layout: [nblocks][2] block partials (sum|p-t|, sum S), blocks ordered n-major
+template <int R, bool GRAD>
+__global__ void __launch_bounds__(NTHR) l1_ssim_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                       float* __restrict__ dpred, float* __restrict__ partial, int H,
+                                                       int W, Taps taps, float C1, float C2, float l1_coef,
+                                                       float ssim_coef) {
+    using G = Geo<R, GRAD>;
+    constexpr int IN = G::IN, MID = G::MID, HALO = G::HALO, WIN = 2 * R + 1;
+    extern __shared__ float smem[];
+    float* sx = smem;                      // [IN][IN]
+    float* sy = sx + IN * IN;              // [IN][IN]
+    float* hb = sy + IN * IN;              // [5][IN][MID]  horizontal pass (reused for the backward h-pass)
+    float* mp = hb + 5 * IN * MID;         // [3][MID][MID] derivative maps (GRAD only)
+    __shared__ float s_red[2][NTHR / 32];
+
+    const int tid = threadIdx.x;
+    const int n = blockIdx.z, ty0 = blockIdx.y * T, tx0 = blockIdx.x * T;
+    const float* px = pred + (int64_t)n * H * W;
+    const float* py = tgt + (int64_t)n * H * W;
+
+    for (int i = tid; i < IN * IN; i += NTHR) {
+        const int gy = ty0 - HALO + i / IN, gx = tx0 - HALO + i % IN;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        sx[i] = in ? px[(int64_t)gy * W + gx] : 0.f;
+        sy[i] = in ? py[(int64_t)gy * W + gx] : 0.f;
+    }
+    __syncthreads();
+    // horizontal pass of x, y, xx, yy, xy
+    for (int i = tid; i < IN * MID; i += NTHR) {
+        const int r = i / MID, c = i % MID;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+        for (int t = 0; t < WIN; ++t) {
+            const float w = taps.w[t], x = sx[r * IN + c + t], y = sy[r * IN + c + t];
+            a0 = fmaf(w, x, a0); a1 = fmaf(w, y, a1);
+            a2 = fmaf(w, x * x, a2); a3 = fmaf(w, y * y, a3); a4 = fmaf(w, x * y, a4);
+        }
+        hb[i] = a0; hb[IN * MID + i] = a1; hb[2 * IN * MID + i] = a2; hb[3 * IN * MID + i] = a3; hb[4 * IN * MID + i] = a4;
+    }
+    __syncthreads();
+    // vertical pass -> SSIM map (+ derivative maps)
+    float ssum = 0.f, lsum = 0.f;
+    for (int i = tid; i < MID * MID; i += NTHR) {
+        const int r = i / MID, c = i % MID;
+        float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+        for (int t = 0; t < WIN; ++t) {
+            const float w = taps.w[t];
+            const int j = (r + t) * MID + c;
+            m1 = fmaf(w, hb[j], m1); m2 = fmaf(w, hb[IN * MID + j], m2);
+            e11 = fmaf(w, hb[2 * IN * MID + j], e11); e22 = fmaf(w, hb[3 * IN * MID + j], e22);
+            e12 = fmaf(w, hb[4 * IN * MID + j], e12);
+        }
+        const int off = GRAD ? R : 0;
+        const int gy = ty0 - off + r, gx = tx0 - off + c;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+        const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
+        const float inv = 1.f / (B1 * B2);
+        const float S = A1 * A2 * inv;
+        const bool center = r >= off && r < off + T && c >= off && c < off + T;
+        if (in && center) ssum += S;
+        if (GRAD) {
+            const float d11 = in ? -S / B2 : 0.f;
+            const float d12 = in ? 2.f * A1 * inv : 0.f;
+            const float d1 = in ? 2.f * m2 * (A2 - A1) * inv - 2.f * m1 * S / B1 + 2.f * m1 * S / B2 : 0.f;
+            mp[i] = d1; mp[MID * MID + i] = d11; mp[2 * MID * MID + i] = d12;
+        }
+    }
+    if (GRAD) {
+        __syncthreads();
+        // horizontal pass of the three derivative maps: rows MID, cols T  (into hb)
+        for (int i = tid; i < MID * T; i += NTHR) {
+            const int r = i / T, c = i % T;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+            for (int t = 0; t < WIN; ++t) {
+                const float w = taps.w[t];
+                const int j = r * MID + c + t;
+                a0 = fmaf(w, mp[j], a0); a1 = fmaf(w, mp[MID * MID + j], a1); a2 = fmaf(w, mp[2 * MID * MID + j], a2);
+            }
+            hb[i] = a0; hb[MID * T + i] = a1; hb[2 * MID * T + i] = a2;
+        }
+        __syncthreads();
+        for (int i = tid; i < T * T; i += NTHR) {
+            const int r = i / T, c = i % T;
+            const int gy = ty0 + r, gx = tx0 + c;
+            if (gy < H && gx < W) {
+                float g1 = 0.f, g11 = 0.f, g12 = 0.f;
+#pragma unroll
+                for (int t = 0; t < WIN; ++t) {
+                    const float w = taps.w[t];
+                    const int j = (r + t) * T + c;
+                    g1 = fmaf(w, hb[j], g1); g11 = fmaf(w, hb[MID * T + j], g11); g12 = fmaf(w, hb[2 * MID * T + j], g12);
+                }
+                const float x = sx[(r + HALO) * IN + c + HALO], y = sy[(r + HALO) * IN + c + HALO];
+                const float d = x - y;
+                lsum += fabsf(d);
+                const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+                if (dpred) dpred[(int64_t)n * H * W + (int64_t)gy * W + gx] =
+                    l1_coef * sg + ssim_coef * (g1 + 2.f * x * g11 + y * g12);
+            }
+        }
+    }
+    ssum = warp_sum(ssum);
+    lsum = warp_sum(lsum);
+    if ((tid & 31) == 0) { s_red[0][tid >> 5] = lsum; s_red[1][tid >> 5] = ssum; }
+    __syncthreads();
+    if (tid < 2) {
+        float t = 0.f;
+        for (int w = 0; w < NTHR / 32; ++w) t += s_red[tid][w];
+        const int64_t b = ((int64_t)n * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        partial[b * 2 + tid] = t;
+    }
+}
+
+// out5 = [l1, ssim, total, 0, total]; also a flag in out5-adjacent scratch is not needed: fix-up reads out5[1]
+__global__ void loss_finalize_kernel(const float* __restrict__ partial, int nblocks, double inv_numel, float l1_w,
+                                     float ssim_w, float* __restrict__ out5) {
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < nblocks; i += 32) { a += (double)partial[2 * i]; b += (double)partial[2 * i + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (threadIdx.x == 0) {
+        const float l1 = (float)(a * inv_numel), ss = (float)(b * inv_numel);
+        const float sc = fminf(fmaxf(ss, 0.f), 1.f);
+        float total = 0.f;
+        if (l1_w > 0.f) total += l1_w * l1;
+        if (ssim_w > 0.f) total += ssim_w * (1.f - sc);
+        out5[0] = l1; out5[1] = ss; out5[2] = total; out5[3] = 0.f; out5[4] = total;
+    }
+}
+
+// torch.clamp passes gradient only while 0 <= ssim <= 1 (utils/losses.py:221): when the mean SSIM left that
+// range (anti-correlated images) the SSIM part of dpred is dropped.  Rare path: rewrites dpred as L1-only.
+__global__ void clamp_fixup_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                   float* __restrict__ dpred, const float* __restrict__ out5, int64_t numel,
+                                   float l1_coef) {
+    const float ss = out5[1];
+    if (ss >= 0.f && ss <= 1.f) return;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < numel; i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = pred[i] - tgt[i];
+        dpred[i] = l1_coef * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
+    }
+}
+
+__global__ void ssim_per_sample_kernel(const float* __restrict__ partial, int blocks_per_sample, double inv_hw,
+                                       float* __restrict__ out) {
+    const int n = blockIdx.x;
+    double b = 0.0;
+    for (int i = threadIdx.x; i < blocks_per_sample; i += 32) b += (double)partial[2 * ((int64_t)n * blocks_per_sample + i) + 1];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) b += __shfl_xor_sync(0xffffffffu, b, o);
+    if (threadIdx.x == 0) out[n] = (float)(b * inv_hw);
+}
+
+bool make_taps(int win, float sigma, Taps& t) {
+    if (win < 3 || win > 11 || (win & 1) == 0 || !(sigma > 0.f)) return false;
+    float g[11], sum = 0.f;                      // utils/losses.py:10-18 in fp32
+    for (int i = 0; i < win; ++i) {
+        const float c = (float)i - (float)(win / 2);
+        g[i] = expf(-(c * c) / (2.f * sigma * sigma));
+        sum += g[i];
+    }
+    for (int i = 0; i < 11; ++i) t.w[i] = i < win ? g[i] / sum : 0.f;
+    return true;
+}
+
+template <int R, bool GRAD>
+int run(const float* pred, const float* tgt, float* dpred, float* partial, int N, int H, int W, const Taps& taps,
+        float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
+    const size_t smem = Geo<R, GRAD>::smem_floats * sizeof(float);
+    static bool configured = false;   // attribute is per-function, idempotent
+    if (!configured) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(l1_ssim_kernel<R, GRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid(ceil_div(W, T), ceil_div(H, T), N);
+    l1_ssim_kernel<R, GRAD><<<grid, NTHR, smem, s>>>(pred, tgt, dpred, partial, H, W, taps, C1, C2, l1_coef, ssim_coef);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+template <bool GRAD>
+int dispatch(int win, const float* pred, const float* tgt, float* dpred, float* partial, int N, int H, int W,
+             const Taps& taps, float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
+    switch (win / 2) {
+        case 1: return run<1, GRAD>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 2: return run<2, GRAD>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 3: return run<3, GRAD>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 4: return run<4, GRAD>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        default: return run<5, GRAD>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    }
+}
+}  // namespace
+
+size_t l1_ssim_scratch_bytes(int N, int H, int W) {
+    return (size_t)N * ceil_div(H, T) * ceil_div(W, T) * 2 * sizeof(float);
+}
+
+int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* out5, void* scratch, int N, int H,
+                   int W, float l1_w, float ssim_w, int win, float sigma, float val_range, cudaStream_t s) {
+    Taps taps;
+    if (!make_taps(win, sigma, taps)) { set_error("l1_ssim: window_size must be odd in [3,11], sigma > 0"); return -1; }
+    const float C1 = (0.01f * val_range) * (0.01f * val_range), C2 = (0.03f * val_range) * (0.03f * val_range);
+    const double numel = (double)N * H * W;
+    const float l1_coef = l1_w > 0.f ? (float)(l1_w / numel) : 0.f;
+    const float ssim_coef = ssim_w > 0.f ? (float)(-ssim_w / numel) : 0.f;
+    float* partial = (float*)scratch;
+    int rc = dispatch<true>(win, pred, target, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    if (rc) return rc;
+    const int nblocks = N * ceil_div(H, T) * ceil_div(W, T);
+    loss_finalize_kernel<<<1, 32, 0, s>>>(partial, nblocks, 1.0 / numel, l1_w, ssim_w, out5);
+    MRISR_LAUNCH_CHECK();
+    if (dpred && ssim_w > 0.f) {
+        clamp_fixup_kernel<<<148 * 4, 256, 0, s>>>(pred, target, dpred, out5, (int64_t)N * H * W, l1_coef);
+        MRISR_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+int launch_ssim_forward(const float* a, const float* b, float* per_sample, void* scratch, int N, int H, int W,
+                        int win, float sigma, float val_range, cudaStream_t s) {
+    Taps taps;
+    if (!make_taps(win, sigma, taps)) { set_error("ssim: window_size must be odd in [3,11], sigma > 0"); return -1; }
+    const float C1 = (0.01f * val_range) * (0.01f * val_range), C2 = (0.03f * val_range) * (0.03f * val_range);
+    float* partial = (float*)scratch;
+    int rc = dispatch<false>(win, a, b, nullptr, partial, N, H, W, taps, C1, C2, 0.f, 0.f, s);
+    if (rc) return rc;
+    ssim_per_sample_kernel<<<N, 32, 0, s>>>(partial, ceil_div(H, T) * ceil_div(W, T), 1.0 / ((double)H * W), per_sample);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mrisr

@@ -1,0 +1,272 @@
+// GroupNorm statistics / apply (+LeakyReLU, +2x2 max-pool), bilinear x2 up-sampling and its adjoint.
+// Forward semantics follow models/unet_model.py:29-37 (conv -> GroupNorm(8) -> LeakyReLU(0.2)),
+// :52 (MaxPool2d(2)), :71/:151 (Upsample(2, bilinear, align_corners=True)).
+#include "kernels.cuh"
+
+namespace mrisr {
+namespace {
+constexpr int NTHR = 256;
+constexpr int PIX_PER_THREAD = 16;
+
+template <typename T>
+__global__ void pack_input_kernel(const float* __restrict__ x, Act<T> dst) {
+    const int64_t total = (int64_t)dst.N * dst.H * dst.W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int xx = (int)(i % dst.W), yy = (int)((i / dst.W) % dst.H), n = (int)(i / ((int64_t)dst.W * dst.H));
+        dst.p[dst.off(n, yy, xx)] = from_f<T>(x[i]);
+    }
+}
+
+// ---- statistics: per (n, slot, group) partial sum / sum of squares -------------------------
+template <typename T>
+__global__ void __launch_bounds__(NTHR) gn_stats_kernel(Act<T> r, float* __restrict__ part, int pix_per_block) {
+    __shared__ float s_red[2][2048];
+    const int C = r.C, nv = C / 8, PL = NTHR / nv;
+    const int tid = threadIdx.x, cv = tid % nv, pl = tid / nv;
+    const int n = blockIdx.y, HW = r.H * r.W;
+    float s1[8], s2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+    if (pl < PL) {
+        const int p_end = min(HW, (int)(blockIdx.x + 1) * pix_per_block);
+        for (int p = blockIdx.x * pix_per_block + pl; p < p_end; p += PL) {
+            float v[8];
+            load8(r.p + r.off(n, p / r.W, p % r.W) + cv * 8, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { s1[k] += v[k]; s2[k] += v[k] * v[k]; }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { s_red[0][pl * C + cv * 8 + k] = s1[k]; s_red[1][pl * C + cv * 8 + k] = s2[k]; }
+    }
+    __syncthreads();
+    for (int i = tid; i < 2 * C; i += NTHR) {
+        const int which = i / C, c = i % C;
+        float t = 0.f;
+        for (int j = 0; j < PL; ++j) t += s_red[which][j * C + c];
+        s_red[which][c] = t;           // row 0 reuse: safe, each thread only touches its own column
+    }
+    __syncthreads();
+    if (tid < 2 * kGroups) {
+        const int which = tid / kGroups, g = tid % kGroups, gs = C / kGroups;
+        float t = 0.f;
+        for (int c = g * gs; c < (g + 1) * gs; ++c) t += s_red[which][c];
+        part[(((int64_t)n * gridDim.x + blockIdx.x) * kGroups + g) * 2 + which] = t;
+    }
+}
+
+__global__ void gn_finalize_kernel(const float* __restrict__ part, float* __restrict__ stats, int slots, double count) {
+    const int ng = blockIdx.x;                   // n * 8 + g
+    const int n = ng / kGroups, g = ng % kGroups;
+    double s1 = 0.0, s2 = 0.0;
+    for (int s = threadIdx.x; s < slots; s += 32) {
+        const float* q = part + (((int64_t)n * slots + s) * kGroups + g) * 2;
+        s1 += (double)q[0];
+        s2 += (double)q[1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if (threadIdx.x == 0) {
+        const double mean = s1 / count;
+        double var = s2 / count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        stats[ng * 2] = (float)mean;
+        stats[ng * 2 + 1] = (float)(1.0 / sqrt(var + (double)kGnEps));
+    }
+}
+
+// ---- apply: a = lrelu(gamma * (r - mean) * rstd + beta), optional 2x2 max-pool --------------
+template <typename T, bool POOL>
+__global__ void __launch_bounds__(NTHR) gn_apply_kernel(Act<T> r, const float* __restrict__ stats,
+                                                        const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, Act<T> a, Act<T> pooled) {
+    const int C = r.C, nv = C / 8, gs = C / kGroups;
+    const int WH = POOL ? r.H / 2 : r.H, WW = POOL ? r.W / 2 : r.W;
+    const int64_t total = (int64_t)r.N * WH * WW * nv;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % nv);
+        const int wx = (int)((i / nv) % WW), wy = (int)((i / ((int64_t)nv * WW)) % WH);
+        const int n = (int)(i / ((int64_t)nv * WW * WH));
+        float sc[8], sh[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = cv * 8 + k, g = c / gs;
+            const float mean = stats[(n * kGroups + g) * 2], rstd = stats[(n * kGroups + g) * 2 + 1];
+            sc[k] = gamma[c] * rstd;
+            sh[k] = beta[c] - mean * sc[k];
+        }
+        if (!POOL) {
+            float v[8];
+            load8(r.p + r.off(n, wy, wx) + cv * 8, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
+            store8(a.p + a.off(n, wy, wx) + cv * 8, v);
+        } else {
+            float m[8];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int y = 2 * wy + (q >> 1), x = 2 * wx + (q & 1);
+                float v[8];
+                load8(r.p + r.off(n, y, x) + cv * 8, v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
+                store8(a.p + a.off(n, y, x) + cv * 8, v);
+                // max over the values as stored (rounded to T) so backward's argmax recomputation agrees
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float vr = to_f(from_f<T>(v[k]));
+                    m[k] = q == 0 ? vr : fmaxf(m[k], vr);
+                }
+            }
+            store8(pooled.p + pooled.off(n, wy, wx) + cv * 8, m);
+        }
+    }
+}
+
+// ---- bilinear x2, align_corners=True ------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(NTHR) upsample2x_kernel(Act<T> src, Act<T> dst, float sy, float sx) {
+    const int nv = src.C / 8;
+    const int64_t total = (int64_t)dst.N * dst.H * dst.W * nv;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % nv);
+        const int X = (int)((i / nv) % dst.W), Y = (int)((i / ((int64_t)nv * dst.W)) % dst.H);
+        const int n = (int)(i / ((int64_t)nv * dst.W * dst.H));
+        const Lerp ly = up_coord(Y, src.H, sy), lx = up_coord(X, src.W, sx);
+        float v00[8], v01[8], v10[8], v11[8], o[8];
+        load8(src.p + src.off(n, ly.i0, lx.i0) + cv * 8, v00);
+        load8(src.p + src.off(n, ly.i0, lx.i1) + cv * 8, v01);
+        load8(src.p + src.off(n, ly.i1, lx.i0) + cv * 8, v10);
+        load8(src.p + src.off(n, ly.i1, lx.i1) + cv * 8, v11);
+        const float h1 = ly.w1, h0 = 1.f - h1, w1 = lx.w1, w0 = 1.f - w1;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = h0 * (w0 * v00[k] + w1 * v01[k]) + h1 * (w0 * v10[k] + w1 * v11[k]);
+        store8(dst.p + dst.off(n, Y, X) + cv * 8, o);
+    }
+}
+
+__device__ __forceinline__ void adj_range(int i, int in_size, float scale, int& lo, int& hi) {
+    const int out_size = 2 * in_size;
+    if (scale <= 0.f) { lo = 0; hi = out_size - 1; return; }
+    lo = (int)floorf((float)(i - 1) / scale) - 1;
+    hi = (int)ceilf((float)(i + 1) / scale) + 1;
+    if (lo < 0) lo = 0;
+    if (hi > out_size - 1) hi = out_size - 1;
+}
+__device__ __forceinline__ float adj_weight(int dst, int i, int in_size, float scale) {
+    const Lerp l = up_coord(dst, in_size, scale);
+    return (l.i0 == i ? 1.f - l.w1 : 0.f) + (l.i1 == i ? l.w1 : 0.f);
+}
+
+// gather form of the adjoint: deterministic, no atomics
+template <typename T>
+__global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T> addend, Act<T> dsrc, float sy,
+                                                              float sx) {
+    const int nv = dsrc.C / 8;
+    const int64_t total = (int64_t)dsrc.N * dsrc.H * dsrc.W * nv;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % nv);
+        const int x = (int)((i / nv) % dsrc.W), y = (int)((i / ((int64_t)nv * dsrc.W)) % dsrc.H);
+        const int n = (int)(i / ((int64_t)nv * dsrc.W * dsrc.H));
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        if (addend.p) load8(addend.p + addend.off(n, y, x) + cv * 8, acc);
+        int ylo, yhi, xlo, xhi;
+        adj_range(y, dsrc.H, sy, ylo, yhi);
+        adj_range(x, dsrc.W, sx, xlo, xhi);
+        for (int Y = ylo; Y <= yhi; ++Y) {
+            const float wy = adj_weight(Y, y, dsrc.H, sy);
+            if (wy == 0.f) continue;
+            for (int X = xlo; X <= xhi; ++X) {
+                const float w = wy * adj_weight(X, x, dsrc.W, sx);
+                if (w == 0.f) continue;
+                float v[8];
+                load8(ddst.p + ddst.off(n, Y, X) + cv * 8, v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+            }
+        }
+        store8(dsrc.p + dsrc.off(n, y, x) + cv * 8, acc);
+    }
+}
+
+inline int grid_for(int64_t total) {
+    int64_t b = ceil_div64(total, NTHR);
+    if (b > 148 * 16) b = 148 * 16;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+}  // namespace
+
+template <typename T>
+int launch_pack_input(const float* x, Act<T> dst, cudaStream_t s) {
+    pack_input_kernel<T><<<grid_for((int64_t)dst.N * dst.H * dst.W), NTHR, 0, s>>>(x, dst);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+int stat_slots_generic(int H, int W, int C) {
+    const int PL = NTHR / (C / 8);
+    return ceil_div(H * W, PL * PIX_PER_THREAD);
+}
+
+template <typename T>
+int launch_gn_stats(Act<T> r, float* part, cudaStream_t s) {
+    const int PL = NTHR / (r.C / 8);
+    dim3 grid(stat_slots_generic(r.H, r.W, r.C), r.N);
+    gn_stats_kernel<T><<<grid, NTHR, 0, s>>>(r, part, PL * PIX_PER_THREAD);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_gn_finalize(const float* part, float* stats, int N, int slots, double count, cudaStream_t s) {
+    gn_finalize_kernel<<<N * kGroups, 32, 0, s>>>(part, stats, slots, count);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T>
+int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const float* beta, Act<T> a, Act<T> pooled,
+                    cudaStream_t s) {
+    const int nv = r.C / 8;
+    if (pooled.p) {
+        gn_apply_kernel<T, true><<<grid_for((int64_t)r.N * (r.H / 2) * (r.W / 2) * nv), NTHR, 0, s>>>(r, stats, gamma,
+                                                                                                     beta, a, pooled);
+    } else {
+        gn_apply_kernel<T, false><<<grid_for((int64_t)r.N * r.H * r.W * nv), NTHR, 0, s>>>(r, stats, gamma, beta, a,
+                                                                                          pooled);
+    }
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T>
+int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
+    upsample2x_kernel<T><<<grid_for((int64_t)dst.N * dst.H * dst.W * (src.C / 8)), NTHR, 0, s>>>(
+        src, dst, up_scale(src.H), up_scale(src.W));
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T>
+int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t s) {
+    upsample2x_bwd_kernel<T><<<grid_for((int64_t)dsrc.N * dsrc.H * dsrc.W * (dsrc.C / 8)), NTHR, 0, s>>>(
+        ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W));
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+#define INST(T)                                                                                                   \
+    template int launch_pack_input<T>(const float*, Act<T>, cudaStream_t);                                        \
+    template int launch_gn_stats<T>(Act<T>, float*, cudaStream_t);                                                \
+    template int launch_gn_apply<T>(Act<T>, const float*, const float*, const float*, Act<T>, Act<T>, cudaStream_t); \
+    template int launch_upsample2x<T>(Act<T>, Act<T>, cudaStream_t);                                              \
+    template int launch_upsample2x_bwd<T>(Act<T>, Act<T>, Act<T>, cudaStream_t);
+INST(float)
+INST(__nv_bfloat16)
+#undef INST
+
+}  // namespace mrisr

@@ -1,0 +1,61 @@
+// Static description of UNetSuperRes (models/unet_model.py:129-175) and the workspace layout.
+#pragma once
+#include <vector>
+#include "kernels.cuh"
+
+namespace mrisr {
+
+constexpr int kNumConv = 20;     // GEMM-shaped convolutions (the final 1x1 -> 1 channel is fused into final_head)
+
+// Parameter tensor indices in registration order (alpha first, then children in __init__ order).
+struct ParamLayout {
+    std::vector<int64_t> off, size;
+    int64_t total = 0;
+    explicit ParamLayout(int f);
+};
+
+// resolution level: 0 -> HxW, 1 -> H/2, 2 -> H/4, 3 -> H/8, -1 -> 2Hx2W
+struct ConvDesc {
+    int ks, cin, cout, lvl;
+    int w, bias, gamma, beta;    // parameter indices (-1 if absent)
+};
+void conv_table(int f, ConvDesc (&t)[kNumConv]);
+
+inline int lvl_dim(int d, int lvl) { return lvl < 0 ? 2 * d : d >> lvl; }
+
+// Bump allocator over the caller's workspace (base == nullptr -> size query only).
+struct Arena {
+    char* base;
+    size_t used = 0;
+    explicit Arena(void* b) : base((char*)b) {}
+    void* take(size_t bytes) {
+        void* p = base ? base + used : nullptr;
+        used += (bytes + 255) & ~(size_t)255;
+        return p;
+    }
+};
+
+template <typename T>
+struct Workspace {
+    int N, H, W, f;
+    ConvDesc conv[kNumConv];
+    // forward tensors
+    Act<T> X0, R[kNumConv], Q[kNumConv];          // Q: low-res 1x1 outputs of layers 8, 11, 14
+    Act<T> A[kNumConv];                            // post GN+LReLU activation of conv l (l = 17, 18 unused)
+    Act<T> P[kNumConv];                            // pooled activation (l = 1, 3, 5)
+    Act<T> UB, XM;
+    float* stats[kNumConv];                        // [N][8][2] mean, rstd
+    float* stat_part;                              // shared partial-statistics scratch
+    T* wf[kNumConv];                               // packed forward weights  [tap][Cin][Cout]
+    T* wd[kNumConv];                               // packed dgrad weights    [tap'][Cout][Cin]
+    // backward tensors (train only)
+    Act<T> dR[kNumConv], dQ[kNumConv], G[kNumConv], DY3;
+    float *gn_part, *mstat, *wg_part, *misc;
+    int* state;                                    // [0] = 1 after a train-mode forward
+    size_t bytes;
+
+    Workspace(void* base, int N, int H, int W, int f, bool train);
+    Act<T> make_act(Arena& ar, int lvl, int C);
+};
+
+}  // namespace mrisr

@@ -1,0 +1,290 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the drop-in modules) against the oracle and the
+committed golden vectors.  Tolerances (BASELINE.json north_star): activations and loss within 1e-4
+relative in fp32 mode and 1e-2 in bf16 mode; PSNR within 0.05 dB, SSIM within 1e-3.
+'relative' is measured against the tensor's max magnitude: |a-b|_inf <= tol * |b|_inf."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import losses_oracle as LO
+from oracle import unet_oracle as UO
+from oracle.synth import make_pairs
+from oracle.train_oracle import OracleTrainer
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _golden(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name + ".npz")))
+
+
+def rel_inf(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / max(float(b.abs().max()), 1e-30))
+
+
+def _model(f, precision, params=None):
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    m = UNetSuperRes(base_filters=f, precision=precision).to(_dev())
+    if params is not None:
+        m.load_state_dict(params, strict=True)
+    return m
+
+
+def test_native_library_loaded():
+    from mri_superresolution_b200 import _native
+    assert _native.lib().mrisr_version() == 100
+
+
+# ------------------------------------------------------------------ loss kernel
+def test_loss_kernel_matches_golden(golden_dir):
+    from mri_superresolution_b200.utils.losses import CombinedLoss, ssim
+    d = _golden(golden_dir, "losses")
+    i = 0
+    while f"s{i}:pred" in d:
+        pred = torch.from_numpy(d[f"s{i}:pred"]).to(_dev())
+        tgt = torch.from_numpy(d[f"s{i}:target"]).to(_dev())
+        assert abs(ssim(pred, tgt).item() - float(d[f"s{i}:ssim"])) < 1e-5
+        np.testing.assert_allclose(ssim(pred, tgt, size_average=False).cpu().numpy(), d[f"s{i}:ssim_per_sample"], atol=1e-5)
+        j = 0
+        while f"s{i}:w{j}:sw" in d:
+            p = pred.clone().requires_grad_(True)
+            crit = CombinedLoss(ssim_weight=float(d[f"s{i}:w{j}:sw"]))
+            loss = crit(p, tgt)
+            loss.backward()
+            assert abs(loss.item() - float(d[f"s{i}:w{j}:loss"])) < 1e-4 * max(1.0, abs(float(d[f"s{i}:w{j}:loss"])))
+            g_ref = torch.from_numpy(d[f"s{i}:w{j}:grad"])
+            assert rel_inf(p.grad, g_ref) < 2e-4, (i, j, rel_inf(p.grad, g_ref))
+            j += 1
+        i += 1
+    assert i == 5
+    x = torch.rand(1, 1, 32, 32, device=_dev())
+    assert abs(ssim(x, x).item() - 1.0) < 1e-5
+
+
+def test_loss_kernel_scaled_backward_and_clamp():
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    g = torch.Generator("cpu").manual_seed(3)
+    t = torch.rand(2, 1, 48, 40, generator=g).to(_dev())
+    p = (1.0 - t).clone().requires_grad_(True)          # anti-correlated: mean SSIM < 0 -> clamp kills the SSIM gradient
+    crit = CombinedLoss(ssim_weight=0.4)
+    loss = crit(p, t)
+    (loss * 8.0).backward()                              # upstream scale (GradScaler-style), scripts/train.py:309
+    pr = (1.0 - t).cpu().clone().requires_grad_(True)
+    lr = LO.combined_loss(pr, t.cpu(), ssim_weight=0.4)
+    (lr * 8.0).backward()
+    assert LO.ssim(pr, t.cpu()).item() < 0
+    assert abs(loss.item() - lr.item()) < 1e-5
+    assert rel_inf(p.grad, pr.grad) < 2e-4
+
+
+def test_loss_full_size_properties():
+    """BASELINE config-2 size (64 x 512^2): size-independent properties instead of an oracle run."""
+    from mri_superresolution_b200.utils.losses import CombinedLoss, ssim
+    _, hr = make_pairs(8, 256, 256, seed=7)
+    hr = hr.to(_dev())
+    assert abs(ssim(hr, hr).item() - 1.0) < 1e-5
+    crit = CombinedLoss(ssim_weight=0.4)
+    assert crit(hr, hr).item() < 1e-5
+    p = (hr * 0.9 + 0.05).requires_grad_(True)
+    loss = crit(p, hr)
+    loss.backward()
+    # directional derivative check of the analytic gradient
+    v = torch.randn_like(p)
+    eps = 1e-3
+    with torch.no_grad():
+        lp = crit(p + eps * v, hr).item()
+        lm = crit(p - eps * v, hr).item()
+    num = (lp - lm) / (2 * eps)
+    ana = float((p.grad * v).sum())
+    assert abs(num - ana) < 2e-2 * max(abs(num), abs(ana), 1e-6), (num, ana)
+
+
+# ------------------------------------------------------------------ U-Net forward/backward
+CASES = ["unet_f16_n2_h32", "unet_f16_n1_h24x40", "unet_f32_n1_h64"]
+
+
+def _run_case(golden_dir, name, precision):
+    from mri_superresolution_b200.utils.losses import CombinedLoss, SSIM
+    d = _golden(golden_dir, name)
+    f, n, h, w, affine = [int(v) for v in d["meta"]]
+    params = UO.init_params(f, seed=1234)
+    if affine:
+        params = UO.randomize_affine(params)
+    x, tgt = make_pairs(n, h, w, seed=1234)
+    model = _model(f, precision, params)
+    model.train()
+    crit = CombinedLoss(ssim_weight=float(d["ssim_weight"]))
+    out = model(x.to(_dev()))
+    loss = crit(out, tgt.to(_dev()))
+    loss.backward()
+    metric = SSIM()(out.detach(), tgt.to(_dev())).item()
+    return d, model, out, loss, metric, tgt
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_unet_fp32_matches_golden(golden_dir, name):
+    d, model, out, loss, metric, tgt = _run_case(golden_dir, name, "fp32")
+    assert out.shape == tuple(d["out"].shape) and out.dtype == torch.float32
+    ref_out = torch.from_numpy(d["out"])
+    assert rel_inf(out, ref_out) < 1e-4, rel_inf(out, ref_out)
+    assert abs(loss.item() - float(d["loss"])) < 1e-4 * abs(float(d["loss"]))
+    assert abs(metric - float(d["ssim"])) < 1e-4
+    assert abs(LO.psnr(out.cpu(), tgt) - LO.psnr(ref_out, tgt)) < 0.05
+    for k, p in model.named_parameters():
+        if "grad:" + k in d:
+            e = rel_inf(p.grad, torch.from_numpy(d["grad:" + k]).view(p.shape))
+        else:
+            e = abs(float(p.grad.double().norm()) - float(d["grad:" + k + "@norm"])) / float(d["grad:" + k + "@norm"])
+            head = torch.from_numpy(d["grad:" + k + "@head"])
+            e = max(e, rel_inf(p.grad.flatten()[:512], head) * float(head.abs().max()) / float(p.grad.abs().max()))
+        assert e < 2e-3, (k, e)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_unet_bf16_matches_golden(golden_dir, name):
+    d, model, out, loss, metric, tgt = _run_case(golden_dir, name, "bf16")
+    ref_out = torch.from_numpy(d["out"])
+    assert rel_inf(out, ref_out) < 1e-2, rel_inf(out, ref_out)
+    assert abs(loss.item() - float(d["loss"])) < 1e-2 * abs(float(d["loss"]))
+    assert abs(metric - float(d["ssim"])) < 1e-3
+    assert abs(LO.psnr(out.cpu(), tgt) - LO.psnr(ref_out, tgt)) < 0.05
+    # bf16 gradients: direction and magnitude of every parameter tensor stored in full
+    for k, p in model.named_parameters():
+        if "grad:" + k in d:
+            r = torch.from_numpy(d["grad:" + k]).view(p.shape).double()
+            g = p.grad.double().cpu()
+            if r.numel() > 1:
+                cos = float((g * r).sum() / (g.norm() * r.norm() + 1e-30))
+                assert cos > 0.98, (k, cos)
+            assert abs(float(g.norm()) - float(r.norm())) < 0.1 * float(r.norm()) + 1e-8, k
+        else:
+            nr = float(d["grad:" + k + "@norm"])
+            assert abs(float(p.grad.double().norm()) - nr) < 0.1 * nr, k
+
+
+def test_inference_matches_training_forward_and_clamp(golden_dir):
+    d = _golden(golden_dir, "unet_f16_n2_h32")
+    params = UO.randomize_affine(UO.init_params(16, seed=1234))
+    x, _ = make_pairs(2, 32, 32, seed=1234)
+    model = _model(16, "fp32", params).eval()
+    with torch.no_grad():
+        y = torch.clamp(model(x.to(_dev())), 0, 1)           # scripts/infer.py:275-276
+    assert rel_inf(y, torch.from_numpy(d["out"])) < 1e-4
+    assert float(y.min()) >= 0 and float(y.max()) <= 1
+
+
+def test_backward_after_newer_forward_raises():
+    model = _model(16, "fp32")
+    x, _ = make_pairs(1, 16, 16)
+    y1 = model(x.to(_dev()))
+    _ = model(x.to(_dev()))
+    with pytest.raises(RuntimeError):
+        y1.sum().backward()
+
+
+def test_gradient_accumulation_matches_sum():
+    model = _model(16, "fp32", UO.randomize_affine(UO.init_params(16)))
+    xa, _ = make_pairs(1, 16, 16, seed=1)
+    xb, _ = make_pairs(1, 16, 16, seed=2)
+    model(xa.to(_dev())).sum().backward()
+    ga = [p.grad.clone() for p in model.parameters()]
+    model.zero_grad(set_to_none=True)
+    model(xb.to(_dev())).sum().backward()
+    gb = [p.grad.clone() for p in model.parameters()]
+    model.zero_grad(set_to_none=True)
+    model(xa.to(_dev())).sum().backward()
+    model(xb.to(_dev())).sum().backward()             # accumulates into .grad
+    for p, a, b in zip(model.parameters(), ga, gb):
+        assert torch.allclose(p.grad, a + b, rtol=1e-5, atol=1e-7)
+
+
+def test_cpu_tensor_raises():
+    model = _model(16, "fp32")
+    with pytest.raises(RuntimeError):
+        model(torch.zeros(1, 1, 16, 16))
+    with pytest.raises(ValueError):
+        model(torch.zeros(1, 1, 12, 16, device=_dev()))       # H not a multiple of 8
+
+
+# ------------------------------------------------------------------ optimiser / train step
+def test_fused_adam_matches_torch():
+    from mri_superresolution_b200.optim import FusedAdam
+    model = _model(16, "fp32", UO.randomize_affine(UO.init_params(16)))
+    ref = [p.detach().clone().requires_grad_(True) for p in model.parameters()]
+    opt_ref = torch.optim.Adam(ref, lr=1e-3, weight_decay=1e-5)
+    opt = FusedAdam(model, lr=1e-3, weight_decay=1e-5)
+    g = torch.Generator("cpu").manual_seed(0)
+    for step in range(3):
+        x, _ = make_pairs(1, 16, 16, seed=10 + step)
+        opt.zero_grad()
+        model(x.to(_dev())).square().mean().backward()
+        for r, p in zip(ref, model.parameters()):
+            r.grad = p.grad.detach().clone()
+        opt.step()
+        opt_ref.step()
+    for r, p in zip(ref, model.parameters()):
+        assert torch.allclose(p, r, rtol=1e-5, atol=1e-7)
+
+
+def test_three_train_steps_match_golden(golden_dir):
+    from mri_superresolution_b200.optim import FusedAdam
+    from mri_superresolution_b200.utils.losses import CombinedLoss, SSIM
+    d = _golden(golden_dir, "train3")
+    model = _model(16, "fp32", UO.randomize_affine(UO.init_params(16, seed=1234)))
+    opt = FusedAdam(model, lr=1e-3, weight_decay=1e-5)
+    crit, metric = CombinedLoss(ssim_weight=0.4), SSIM()
+    for step in range(3):
+        x, t = make_pairs(2, 32, 32, seed=500 + step)
+        x, t = x.to(_dev()), t.to(_dev())
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = crit(out, t)
+        loss.backward()
+        opt.step()
+        assert abs(loss.item() - d["losses"][step]) < 2e-4 * d["losses"][step], step
+        with torch.no_grad():
+            assert abs(metric(out, t).item() - d["ssims"][step]) < 2e-4
+    sd = model.state_dict()
+    for k, v in sd.items():
+        if "param:" + k in d:
+            assert rel_inf(v, torch.from_numpy(d["param:" + k]).view(v.shape)) < 5e-3, k
+
+
+def test_stock_torch_adam_works_on_arena_views():
+    """scripts/train.py:186 builds torch.optim.Adam(model.parameters()): must keep working (drop-in)."""
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    params = UO.randomize_affine(UO.init_params(16, seed=1234))
+    model = _model(16, "fp32", params)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-5)
+    tr = OracleTrainer(params, lr=1e-3, weight_decay=1e-5, ssim_weight=0.4)
+    crit = CombinedLoss(ssim_weight=0.4)
+    for step in range(2):
+        x, t = make_pairs(2, 32, 32, seed=500 + step)
+        opt.zero_grad(set_to_none=True)
+        loss = crit(model(x.to(_dev())), t.to(_dev()))
+        loss.backward()
+        opt.step()
+        lo, _ = tr.step(x, t)
+        assert abs(loss.item() - lo) < 2e-4 * lo
+    assert model._is_flat()
+
+
+def test_full_size_forward_properties():
+    """Config-2 shape (256^2 input) at a small batch: output range/shape and batch-independence
+    (GroupNorm is per-sample, so sample i of a batch equals the same sample run alone)."""
+    model = _model(32, "bf16", UO.init_params(32, seed=1234)).eval()
+    x, _ = make_pairs(3, 256, 256, seed=11)
+    x = x.to(_dev())
+    with torch.no_grad():
+        y = model(x)
+        y1 = model(x[1:2].contiguous())
+    assert y.shape == (3, 1, 512, 512)
+    assert float(y.min()) >= 0 and float(y.max()) <= 1
+    assert torch.equal(y[1:2], y1)

@@ -1,0 +1,160 @@
+"""CPU-side tests: the C-ABI library loads and exports every symbol include/mrisr.h declares, argument
+validation mirrors the reference, checkpoint layout matches, and the data-parallel bucket logic
+(world_size 2, gloo).  No compute calls (there is no GPU here)."""
+import os
+import re
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from oracle import unet_oracle as UO
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from mri_superresolution_b200 import _native
+    L = _native.lib()
+    hdr = open(os.path.join(ROOT, "include", "mrisr.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(mrisr_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 13
+    for name in declared:
+        assert hasattr(L, name), name
+    assert declared == set(_native.SIGNATURES), declared ^ set(_native.SIGNATURES)
+    assert L.mrisr_version() == 100
+
+
+def test_param_arena_layout_matches_reference_order():
+    from mri_superresolution_b200 import _native
+    from mri_superresolution_b200.models.unet_model import param_specs
+    L = _native.lib()
+    for f in (16, 32, 64):
+        specs = param_specs(f)
+        assert specs == UO.param_specs(f)
+        assert L.mrisr_unet_param_tensors(f) == len(specs) == 64
+        off = 0
+        for i, (_, shape) in enumerate(specs):
+            n = 1
+            for s in shape:
+                n *= s
+            assert L.mrisr_unet_param_offset(f, i) == off
+            assert L.mrisr_unet_param_size(f, i) == n
+            off += n
+        assert L.mrisr_unet_param_elems(f) == off
+    assert L.mrisr_unet_param_elems(32) == 1823122
+
+
+def test_shape_validation_and_workspace_query():
+    from mri_superresolution_b200 import _native
+    L = _native.lib()
+    assert L.mrisr_unet_workspace_bytes(2, 32, 32, 16, _native.FP32, 1) > L.mrisr_unet_workspace_bytes(2, 32, 32, 16, _native.FP32, 0) > 0
+    assert L.mrisr_unet_workspace_bytes(2, 30, 32, 16, _native.FP32, 1) == 0        # H % 8 != 0
+    assert b"multiples of 8" in L.mrisr_last_error()
+    assert L.mrisr_unet_workspace_bytes(2, 32, 32, 24, _native.FP32, 1) == 0        # f % 16 != 0
+    assert L.mrisr_unet_workspace_bytes(2, 32, 32, 16, 7, 1) == 0                   # unknown precision
+    rc = L.mrisr_unet_forward(None, None, None, None, 0, 1, 8, 8, 16, 0, 0, None)
+    assert rc == -1
+
+
+def test_module_mirrors_reference_interface():
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    m = UNetSuperRes(in_channels=1, out_channels=1, base_filters=32, initial_alpha=50.0)
+    assert (m.in_channels, m.out_channels, m.base_filters) == (1, 1, 32)
+    assert abs(m.alpha.item() - 0.5) < 1e-7
+    sd = m.state_dict()
+    assert list(sd.keys()) == [n for n, _ in UO.param_specs(32)]
+    assert all(tuple(sd[n].shape) == s for n, s in UO.param_specs(32))
+    assert [n for n, _ in m.named_parameters()] == list(sd.keys())
+    m.load_state_dict(UO.init_params(32), strict=True)      # strict load of a reference-style state dict
+    assert m._is_flat()
+    with pytest.raises(RuntimeError):
+        m.load_state_dict({"alpha": torch.tensor(0.0)}, strict=True)
+    with pytest.raises(ValueError):
+        UNetSuperRes(in_channels=3)
+    with pytest.raises(ValueError):
+        UNetSuperRes(base_filters=24)
+    with pytest.raises(RuntimeError):                  # no CPU fallback
+        m(torch.zeros(1, 1, 16, 16))
+    # kaiming fan_out statistics of the initialiser (models/unet_model.py:181)
+    w = UNetSuperRes(base_filters=32).get_parameter("down3.maxpool_conv.1.double_conv.3.weight")
+    assert abs(w.std().item() - (2.0 / (1 + 0.01 ** 2) / (256 * 9)) ** 0.5) < 2e-3
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    a, b = UNetSuperRes(base_filters=16), UNetSuperRes(base_filters=16)
+    path = tmp_path / "best_model_unet.pth"
+    torch.save({"epoch": 3, "model_state_dict": a.state_dict(), "val_loss": 0.1, "val_ssim": 0.9}, path)   # scripts/train.py:411-418
+    ck = torch.load(path, map_location="cpu")
+    b.load_state_dict(ck["model_state_dict"])                                                             # scripts/infer.py:59-61
+    assert torch.equal(a.flat_parameters(), b.flat_parameters())
+
+
+def test_loss_module_validation_and_attributes():
+    from mri_superresolution_b200.utils.losses import CombinedLoss, SSIM, create_window, gaussian_window
+    for sw, pw in ((-0.1, 0.0), (1.1, 0.0), (0.5, -0.1), (0.7, 0.5)):
+        with pytest.raises(ValueError):
+            CombinedLoss(ssim_weight=sw, perceptual_weight=pw)
+    c = CombinedLoss(ssim_weight=0.4)
+    assert abs(c.l1_weight - 0.6) < 1e-12 and c.use_perceptual is False and c.perceptual_loss is None
+    assert c.window.shape == (1, 1, 11, 11) and (c.window_size, c.sigma, c.val_range) == (11, 1.5, 1.0)
+    from oracle.losses_oracle import gaussian_taps, gaussian_window2d
+    assert torch.equal(gaussian_window(11, 1.5), gaussian_taps())
+    assert torch.allclose(create_window(11, 1, 1.5, "cpu")[0, 0], gaussian_window2d(), atol=0, rtol=0)
+    assert SSIM(device=torch.device("cpu")).window.shape == (1, 1, 11, 11)
+    with pytest.raises(RuntimeError):
+        c(torch.zeros(1, 1, 16, 16), torch.zeros(1, 1, 16, 16))     # CPU tensors: no fallback
+
+
+def test_bucket_bounds_cover_arena():
+    from mri_superresolution_b200.parallel import bucket_bounds
+    for total, nb in ((1823122, 3), (10, 3), (7, 10), (5, 1)):
+        b = bucket_bounds(total, nb)
+        assert sorted(b)[0][0] == 0 and sorted(b)[-1][1] == total
+        assert sum(e - s for s, e in b) == total
+        assert b[0][1] == total                      # last slice of the arena goes first
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _dp_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    from mri_superresolution_b200.parallel import GradientBuckets
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    model = UNetSuperRes(base_filters=16)
+    # emulate an arena-backed backward on CPU: rank-dependent gradients written as arena views
+    arena = torch.empty(model._total)
+    model._grad_arenas.append(arena)
+    g = torch.Generator().manual_seed(100 + rank)
+    arena.copy_(torch.randn(model._total, generator=g))
+    for p, o in zip(model._param_list(), model._offs):
+        p.grad = arena[o:o + p.numel()].view(p.shape)
+    scale = GradientBuckets(model, n_buckets=3).allreduce()
+    expect = sum(torch.randn(model._total, generator=torch.Generator().manual_seed(100 + r)) for r in range(world))
+    ok = torch.allclose(model.flat_grads(), expect, atol=1e-6) and abs(scale - 1.0 / world) < 1e-12
+    q.put((rank, bool(ok)))
+    dist.destroy_process_group()
+
+
+def test_data_parallel_bucketed_allreduce_gloo_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_dp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]
