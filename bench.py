@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""Benchmark of the U-Net super-resolution training step (BASELINE.json configs[1]) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode train|infer]
+
+One "step" = one pass of the hot path over one batch of synthetic slices:
+  train: zero_grad -> UNetSuperRes forward -> CombinedLoss(L1 + 0.4 SSIM) -> backward -> (bucketed NCCL
+         gradient all-reduce when N > 1) -> fused Adam   (the loop body of scripts/train.py:296-318)
+  infer: no_grad forward + clamp(0,1)                     (scripts/infer.py:268-276)
+Per-GPU batch is fixed (64 slices of 256x256 -> 512x512), so N > 1 is weak scaling; ranks are launched by
+torch.distributed.run (one process per GPU, NCCL).  Rank 0 prints ONE JSON line.
+
+  value : slices/s with inputs resident in HBM (CUDA events, max over ranks)
+  e2e   : slices/s through the public module API with inputs in pinned HOST memory, the host->device copies and
+          the loss read-back (loss.item(), as scripts/train.py:321 does) inside the timed region
+  roofline : the dominant kernel family of the step, timed live with CUDA events on the launching stream
+             (mrisr_prof_*), algorithmic FLOPs (or bytes) / time against MEASURED_PEAKS.json
+  cpu_baseline : the oracle (plain PyTorch fp32 restatement of the reference, oracle/) timed on the host cores on a
+             bounded sample of the same workload.  `--impl reference` prints that arm alone.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASE_FILTERS = 32
+H = W = 256                     # network input (LR) size; target / output is 512 x 512
+PER_GPU_BATCH = 64
+SSIM_WEIGHT = 0.4
+LR, WD = 1e-4, 1e-5             # scripts/train.py:186 defaults (lr 1e-4, weight_decay 1e-5)
+SEED = 1234
+METRIC = "U-Net train slices/sec at 256^2 bf16"
+INFER_METRIC = "U-Net infer slices/sec at 256^2 bf16"
+
+
+# ----------------------------------------------------------------------------------------- FLOP / byte model
+def unet_conv_table(f: int):
+    """(ks, cin, cout, level) of the 21 convolutions; level l -> (H >> l), -1 -> 2H."""
+    return [(3, 1, f, 0), (3, f, f, 0), (3, f, 2 * f, 1), (3, 2 * f, 2 * f, 1), (3, 2 * f, 4 * f, 2),
+            (3, 4 * f, 4 * f, 2), (3, 4 * f, 8 * f, 3), (3, 8 * f, 8 * f, 3),
+            (1, 8 * f, 4 * f, 2), (3, 8 * f, 4 * f, 2), (3, 4 * f, 4 * f, 2),
+            (1, 4 * f, 2 * f, 1), (3, 4 * f, 2 * f, 1), (3, 2 * f, 2 * f, 1),
+            (1, 2 * f, f, 0), (3, 2 * f, f, 0), (3, f, f, 0),
+            (3, f, f // 2, -1), (3, f, 2 * f, 0), (3, f // 2, f // 2, -1), (1, f // 2, 1, -1)]
+
+
+def unet_flops_per_slice(f: int, h: int, w: int, train: bool) -> float:
+    """2*MAC of the reference's 21 convs (1x1 up-convs counted at the reference's high resolution)."""
+    fwd = 0.0
+    first = 0.0
+    for i, (ks, ci, co, lvl) in enumerate(unet_conv_table(f)):
+        hh, ww = (2 * h, 2 * w) if lvl < 0 else (h >> lvl, w >> lvl)
+        fl = 2.0 * ci * co * ks * ks * hh * ww
+        fwd += fl
+        if i == 0:
+            first = fl
+    return 3.0 * fwd - first if train else fwd
+
+
+def tag_flops(tag: str, n: int) -> float:
+    """Algorithmic FLOPs of one launch of a conv / wgrad kernel from its profiler tag 'name:k3:Cin>Cout@HxW'."""
+    try:
+        _, k, chans, = tag.split(":")[0:3]
+        ks = int(k[1:])
+        cc, hw = chans.split("@")
+        ci, co = [int(v) for v in cc.split(">")]
+        hh, ww = [int(v) for v in hw.split("x")]
+        return 2.0 * ci * co * ks * ks * hh * ww * n
+    except Exception:
+        return 0.0
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            d = json.load(open(path))
+            for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained"):
+                if k in d:
+                    p[k] = float(d[k])
+            p["source"] = "measured"
+        except Exception:
+            pass
+    return p
+
+
+# ----------------------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        for ts, line in self.rows:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                clk = float(parts[1])
+                smax = float(parts[2])
+            except ValueError:
+                continue
+            if t0 <= ts <= t1 + 0.2:
+                sm.append(clk)
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[4:8]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------- reference / CPU arm
+def cpu_oracle_run(mode: str, steps: int, warmup: int, budget_s: float):
+    """Times the oracle (reference algorithm, plain PyTorch fp32, all host threads) on a bounded sample of the
+    workload: per step one batch of `b` slices of 256x256, b chosen so the whole run fits `budget_s`."""
+    import torch
+    from oracle import unet_oracle as UO
+    from oracle.synth import make_pairs
+    from oracle.train_oracle import OracleTrainer, infer_step
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    params = UO.init_params(BASE_FILTERS, seed=SEED)
+    trainer = OracleTrainer(params, lr=LR, weight_decay=WD, ssim_weight=SSIM_WEIGHT) if mode == "train" else None
+
+    def one(b, seed):
+        x, t = make_pairs(b, H, W, seed=seed)
+        t0 = time.perf_counter()
+        if mode == "train":
+            trainer.step(x, t)
+        else:
+            infer_step(params, x)
+        return time.perf_counter() - t0
+
+    one(1, SEED)                                    # page-in / thread-pool warm-up, not counted
+    t1 = one(1, SEED + 1)
+    total = max(1, steps + warmup)
+    b = int(max(1, min(8, (budget_s / total) / max(t1, 1e-3))))
+    for i in range(warmup):
+        one(b, SEED + 10 + i)
+    dt = 0.0
+    for i in range(steps):
+        dt += one(b, SEED + 100 + i)
+    return {"value": b * steps / dt, "ms_per_step": 1e3 * dt / steps, "batch": b, "cores": cores,
+            "threads": torch.get_num_threads()}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    mode = args.mode
+    r = cpu_oracle_run(mode, args.steps, args.warmup, budget_s=150.0)
+    unit = "slices/s"
+    sample = (f"{r['batch']} slices of {H}x{W} per step x {args.steps} steps, oracle ({'train step' if mode == 'train' else 'forward'}"
+              f", fp32, torch CPU, {r['threads']} threads)")
+    line = {
+        "impl": "reference", "metric": METRIC if mode == "train" else INFER_METRIC, "value": r["value"], "unit": unit,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+        "config": workload_config(mode, max(1, args.gpus), args.batch),
+        "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["threads"], "kind": "port", "sample": sample},
+        "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(mode: str, world: int, per_gpu_batch: int):
+    return {"workload": (f"BASELINE.json configs[1]: U-Net(base_filters={BASE_FILTERS}) "
+                         f"{'training step, L1+SSIM(0.4) loss, Adam' if mode == 'train' else 'inference forward'}, "
+                         f"batch {per_gpu_batch}/GPU, {H}x{W} input -> {2 * H}x{2 * W} output"),
+            "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * world, "input": [H, W],
+            "parallelism": f"dp{world}", "l2": "working set per step (>= 8 GB of activations) >> 126 MB L2; inputs re-read from HBM"}
+
+
+# ----------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from mri_superresolution_b200 import _native
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    from mri_superresolution_b200.optim import FusedAdam
+    from mri_superresolution_b200.parallel import GradientBuckets
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    from mri_superresolution_b200.utils.synthetic import make_pairs
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    mode, nb = args.mode, args.batch
+    _native.lib()                                   # fail loudly if the CUDA library is missing
+
+    torch.manual_seed(SEED)
+    model = UNetSuperRes(base_filters=BASE_FILTERS, precision=args.precision).to(dev)
+    crit = CombinedLoss(ssim_weight=SSIM_WEIGHT)
+    opt = FusedAdam(model, lr=LR, weight_decay=WD)
+    buckets = GradientBuckets(model) if world > 1 else None
+    x_cpu, t_cpu = make_pairs(nb, H, W, seed=SEED, rank=rank)
+    x_pin, t_pin = x_cpu.pin_memory(), t_cpu.pin_memory()
+    x_dev, t_dev = x_cpu.to(dev), t_cpu.to(dev)
+
+    def train_step(x, t):
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = crit(out, t)
+        loss.backward()
+        scale = buckets.allreduce() if buckets is not None else 1.0
+        opt.step(grad_scale=scale)
+        return loss
+
+    def infer_step(x, t):
+        with torch.no_grad():
+            return torch.clamp(model(x), 0, 1)
+
+    step = train_step if mode == "train" else infer_step
+    if mode == "infer":
+        model.eval()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- resident-input timing -------------------------------------------------------------
+    for _ in range(args.warmup):
+        step(x_dev, t_dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    launches0 = _native.launch_count()
+    t_wall0 = time.time()
+    ms = timed(lambda: step(x_dev, t_dev), args.steps)
+    t_wall1 = time.time()
+    launches = _native.launch_count() - launches0
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    value = nb * world * args.steps / (ms * 1e-3)
+
+    # ---- end to end: pinned host inputs, H2D copies and loss read-back inside the timed region
+    xb, tb = torch.empty_like(x_dev), torch.empty_like(t_dev)
+    d2h = [0]
+
+    def e2e_step():
+        xb.copy_(x_pin, non_blocking=True)
+        tb.copy_(t_pin, non_blocking=True)
+        r = step(xb, tb)
+        if mode == "train":
+            r.item()                                 # scripts/train.py:321 reads the loss every step
+            d2h[0] = 4
+        else:
+            r[:1].cpu()                              # first super-resolved slice back to the host
+            d2h[0] = r[:1].numel() * 4
+
+    e2e_step()
+    e2e_steps = max(2, min(args.steps, 10))
+    ms_e2e = timed(e2e_step, e2e_steps)
+    e2e_value = nb * world * e2e_steps / (ms_e2e * 1e-3)
+    h2d = x_pin.numel() * 4 + t_pin.numel() * 4
+
+    # ---- per-kernel attribution (same workload, CUDA events on the launching stream) ---------
+    roofline, families = None, []
+    if rank == 0:
+        pk = peaks()
+        prof_steps = 2
+        torch.cuda.synchronize()
+        _native.profile(True)
+        for _ in range(prof_steps):
+            step(x_dev, t_dev)
+        rep = _native.profile_report()
+        _native.profile(False)
+        fam = {}
+        for tag, calls, tms in rep:
+            name = tag.split(":")[0]
+            f = fam.setdefault(name, {"ms": 0.0, "calls": 0, "flops": 0.0})
+            f["ms"] += tms / prof_steps
+            f["calls"] += calls // prof_steps
+            f["flops"] += tag_flops(tag, nb) * calls / prof_steps
+        total_ms = sum(f["ms"] for f in fam.values()) or 1.0
+        for name, f in sorted(fam.items(), key=lambda kv: -kv[1]["ms"]):
+            families.append({"kernel": name, "ms_per_step": round(f["ms"], 4), "launches_per_step": f["calls"],
+                             "share": round(f["ms"] / total_ms, 4),
+                             "tflops": round(f["flops"] / (f["ms"] * 1e-3) / 1e12, 2) if f["flops"] else None})
+        top = families[0]
+        tf = fam[top["kernel"]]
+        if tf["flops"] > 0:
+            achieved = tf["flops"] / (tf["ms"] * 1e-3) / 1e12
+            peak = pk["bf16_tflops_sustained"]
+            roofline = {"kernel": top["kernel"], "bound": "tensor", "achieved": round(achieved, 2), "peak": peak,
+                        "unit": "TFLOP/s", "frac": round(achieved / peak, 4), "traffic": None,
+                        "peak_source": pk["source"] + " (sustained bf16: kernel timed inside a long step)",
+                        "flops_per_step": tf["flops"], "ms_per_step": round(tf["ms"], 4),
+                        "launches_per_step": tf["calls"], "share_of_step": top["share"]}
+        elif top["kernel"] in ("l1_ssim",):
+            nbytes = 12.0 * nb * (2 * H) * (2 * W)   # fp32 pred + target read, fp32 grad written
+            achieved = nbytes / (tf["ms"] * 1e-3) / 1e9
+            roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
+                        "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": None,
+                        "peak_source": pk["source"], "share_of_step": top["share"]}
+        else:
+            roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": None, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                        "frac": None, "traffic": None, "share_of_step": top["share"],
+                        "note": "elementwise helper kernel dominates; its bytes count against the conv roofline"}
+        flops_step = unet_flops_per_slice(BASE_FILTERS, H, W, mode == "train") * nb
+        whole = {"unet_conv_tflops": round(flops_step / (ms / args.steps * 1e-3) / 1e12, 2),
+                 "frac_of_bf16_sustained": round(flops_step / (ms / args.steps * 1e-3) / 1e12 / pk["bf16_tflops_sustained"], 4)}
+    else:
+        whole = None
+
+    # ---- CPU baseline (rank 0, N = 1 only) ----------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_oracle_run(mode, steps=3, warmup=1, budget_s=25.0)
+        cpu = {"value": r["value"], "unit": "slices/s", "cores": r["threads"], "kind": "port",
+               "sample": f"{r['batch']} slices of {H}x{W} per step x 3 steps of the oracle "
+                         f"({'train step' if mode == 'train' else 'forward'}, fp32, torch CPU)"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC if mode == "train" else INFER_METRIC, "value": value, "unit": "slices/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": workload_config(mode, world, nb),
+            "e2e": {"value": e2e_value, "unit": "slices/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h[0],
+                    "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "kernels": families, "whole_step": whole,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="train", choices=["train", "infer"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="slices per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus != world and world == 1 and args.gpus > 1:
+        # convenience: re-launch under torch.distributed.run when called as `python bench.py --gpus N`
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

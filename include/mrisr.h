@@ -102,6 +102,15 @@ int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* ex
 int mrisr_unet_debug_tensor(void* workspace, int N, int H, int W, int base_filters, int precision, int kind,
                             int layer, float* out, int* dims_host, void* stream);
 
+/* ---- measurement aids (used by bench.py; no reference counterpart) --------------------------- */
+/* number of kernel launches issued by this library in this process so far */
+long long mrisr_launch_count(void);
+/* per-kernel-family CUDA-event timing on the launching stream: enable, run steps, then report.
+ * mrisr_prof_report synchronises the device and writes "<tag> <calls> <total_ms>\n" lines (sorted by time)
+ * into the HOST buffer buf (NUL-terminated, at most cap bytes); returns the number of tags. */
+int mrisr_prof_enable(int on);
+int mrisr_prof_report(char* host_buf, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,9 @@ SIGNATURES = {
                                    c_int, c_float, c_float, c_void_p]),
     "mrisr_unet_debug_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_void_p]),
+    "mrisr_launch_count": (ctypes.c_longlong, []),
+    "mrisr_prof_enable": (c_int, [c_int]),
+    "mrisr_prof_report": (c_int, [c_char_p, c_size_t]),
     "mrisr_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                                 c_float, c_float, c_int, c_float, c_void_p]),
 }
@@ -94,3 +97,24 @@ def ptr(t) -> int:
 def stream_ptr() -> int:
     import torch
     return torch.cuda.current_stream().cuda_stream
+
+
+def launch_count() -> int:
+    """Kernel launches issued by the library in this process so far."""
+    return int(lib().mrisr_launch_count())
+
+
+def profile(on: bool) -> None:
+    _native_check = lib().mrisr_prof_enable(1 if on else 0)
+    assert _native_check == 0
+
+
+def profile_report():
+    """[(tag, calls, total_ms)] since profiling was enabled (synchronises the device)."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    lib().mrisr_prof_report(buf, len(buf))
+    out = []
+    for line in buf.value.decode().splitlines():
+        tag, calls, ms = line.rsplit(" ", 2)
+        out.append((tag, int(calls), float(ms)))
+    return out

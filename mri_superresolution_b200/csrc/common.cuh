@@ -24,7 +24,21 @@ const char* g_err_ptr();
         }                                                                                   \
     } while (0)
 
-#define MRISR_LAUNCH_CHECK() MRISR_CUDA_CHECK(cudaGetLastError())
+// every kernel launch goes through this: counts launches (bench.py reports them) and checks for errors
+void count_launch();
+#define MRISR_LAUNCH_CHECK() do { ::mrisr::count_launch(); MRISR_CUDA_CHECK(cudaGetLastError()); } while (0)
+
+// Optional per-kernel-family timing (mrisr_prof_* in include/mrisr.h): when enabled, each launcher brackets its
+// launches with CUDA events on the launching stream; mrisr_prof_report() sums them per tag after a sync.
+// Disabled (the default) it costs one predictable branch.
+bool prof_on();
+const char* prof_intern(const char* tag);      // stable copy of a formatted tag
+struct ProfScope {
+    int slot;
+    cudaStream_t s;
+    ProfScope(const char* tag, cudaStream_t stream);
+    ~ProfScope();
+};
 
 // Padded NHWC activation view: [N][H+2][W+2][C], zero one-pixel border kept as an invariant.
 // `p` points at the padded origin (n=0, row -1, col -1, c=0).

@@ -151,6 +151,13 @@ int conv_generic_stat_slots(int H, int W, int Cout) {
 
 template <typename T>
 int launch_conv_generic(const ConvArgs<T>& a, cudaStream_t s) {
+    const char* tag = "conv_generic";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "conv_generic:k%d:%d>%d@%dx%d", a.ks, a.src1.C + (a.src2.p ? a.src2.C : 0), a.dst.C, a.dst.H, a.dst.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
     const int Cin = a.src1.C + (a.src2.p ? a.src2.C : 0);
     if (a.dst.C % 8 != 0 || (Cin >= 8 && (a.src1.C % 8 != 0 || Cin % 8 != 0)) || (a.ks != 1 && a.ks != 3)) {
         set_error("conv_generic: unsupported channels Cin=%d (C1=%d) Cout=%d ks=%d", Cin, a.src1.C, a.dst.C, a.ks);

@@ -120,6 +120,13 @@ size_t wgrad_generic_scratch_elems(int N, int H, int W, int Cin, int Cout, int k
 
 template <typename T>
 int launch_wgrad_generic(const WgradArgs<T>& a, cudaStream_t s) {
+    const char* tag = "wgrad_generic";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "wgrad_generic:k%d:%d>%d@%dx%d", a.ks, a.src1.C + (a.src2.p ? a.src2.C : 0), a.dy.C, a.dy.H, a.dy.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
     const int Cin = a.src1.C + (a.src2.p ? a.src2.C : 0), Cout = a.dy.C;
     int bx, sp, tps;
     wgrad_plan(a.dy.N, a.dy.H, a.dy.W, Cin, Cout, bx, sp, tps);
@@ -137,6 +144,7 @@ template int launch_wgrad_generic<__nv_bfloat16>(const WgradArgs<__nv_bfloat16>&
 
 template <typename T>
 int launch_pack_weights(const float* w, T* wf, T* wd, int Cout, int Cin, int ks, cudaStream_t s) {
+    ProfScope prof_("pack_weights", s);
     const int64_t total = (int64_t)Cout * Cin * ks * ks;
     int blocks = (int)ceil_div64(total, 256);
     if (blocks > 1184) blocks = 1184;

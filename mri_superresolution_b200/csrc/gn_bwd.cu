@@ -279,6 +279,7 @@ int gn_bwd_slots(int H, int W, int C) {
 
 template <typename T>
 int launch_gn_bwd(const GnBwdArgs<T>& a, cudaStream_t s) {
+    ProfScope prof_("gn_bwd", s);
     switch (a.kind) {
         case SRC_DIRECT: return run<T, SRC_DIRECT>(a, s);
         case SRC_DIRECT_POOL: return run<T, SRC_DIRECT_POOL>(a, s);

@@ -163,6 +163,7 @@ constexpr int COLSUM_PPT = 32;
 
 template <typename T>
 int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s) {
+    ProfScope prof_("head_blend", s);
     head_blend_kernel<T><<<grid_for((int64_t)a.xm.N * a.xm.H * a.xm.W * (a.xm.C / 8)), NTHR, 0, s>>>(a);
     MRISR_LAUNCH_CHECK();
     return 0;
@@ -172,6 +173,7 @@ size_t blend_dalpha_scratch_elems(int, int, int) { return 148 * 16; }
 
 template <typename T>
 int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float* scratch, cudaStream_t s) {
+    ProfScope prof_("blend_dalpha", s);
     const int nb = grid_for((int64_t)a.xm.N * a.xm.H * a.xm.W * (a.xm.C / 8));
     blend_dalpha_kernel<T><<<nb, NTHR, 0, s>>>(a, dxm, scratch);
     MRISR_LAUNCH_CHECK();
@@ -183,6 +185,7 @@ int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float*
 template <typename T>
 int launch_final_head(Act<T> r, const float* stats, const float* gamma, const float* beta, const float* w1x1,
                       const float* b1x1, float* y, cudaStream_t s) {
+    ProfScope prof_("final_head", s);
     final_head_kernel<T><<<grid_for((int64_t)r.N * r.H * r.W), NTHR, 0, s>>>(r, stats, gamma, beta, w1x1, b1x1, y);
     MRISR_LAUNCH_CHECK();
     return 0;
@@ -195,6 +198,7 @@ size_t colsum_scratch_elems(int N, int H, int W, int C) {
 
 template <typename T>
 int launch_colsum(Act<T> t, float* out, float* scratch, cudaStream_t s) {
+    ProfScope prof_("colsum", s);
     const int PL = NTHR / (t.C / 8);
     const int slots = ceil_div(t.H * t.W, PL * COLSUM_PPT);
     colsum_kernel<T><<<dim3(slots, t.N), NTHR, 0, s>>>(t, scratch, PL * COLSUM_PPT);

@@ -225,6 +225,7 @@ size_t l1_ssim_scratch_bytes(int N, int H, int W) {
 
 int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* out5, void* scratch, int N, int H,
                    int W, float l1_w, float ssim_w, int win, float sigma, float val_range, cudaStream_t s) {
+    ProfScope prof_("l1_ssim", s);
     Taps taps;
     if (!make_taps(win, sigma, taps)) { set_error("l1_ssim: window_size must be odd in [3,11], sigma > 0"); return -1; }
     const float C1 = (0.01f * val_range) * (0.01f * val_range), C2 = (0.03f * val_range) * (0.03f * val_range);
@@ -246,6 +247,7 @@ int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* 
 
 int launch_ssim_forward(const float* a, const float* b, float* per_sample, void* scratch, int N, int H, int W,
                         int win, float sigma, float val_range, cudaStream_t s) {
+    ProfScope prof_("ssim_forward", s);
     Taps taps;
     if (!make_taps(win, sigma, taps)) { set_error("ssim: window_size must be odd in [3,11], sigma > 0"); return -1; }
     const float C1 = (0.01f * val_range) * (0.01f * val_range), C2 = (0.03f * val_range) * (0.03f * val_range);

@@ -203,6 +203,7 @@ inline int grid_for(int64_t total) {
 
 template <typename T>
 int launch_pack_input(const float* x, Act<T> dst, cudaStream_t s) {
+    ProfScope prof_("pack_input", s);
     pack_input_kernel<T><<<grid_for((int64_t)dst.N * dst.H * dst.W), NTHR, 0, s>>>(x, dst);
     MRISR_LAUNCH_CHECK();
     return 0;
@@ -215,6 +216,7 @@ int stat_slots_generic(int H, int W, int C) {
 
 template <typename T>
 int launch_gn_stats(Act<T> r, float* part, cudaStream_t s) {
+    ProfScope prof_("gn_stats", s);
     const int PL = NTHR / (r.C / 8);
     dim3 grid(stat_slots_generic(r.H, r.W, r.C), r.N);
     gn_stats_kernel<T><<<grid, NTHR, 0, s>>>(r, part, PL * PIX_PER_THREAD);
@@ -223,6 +225,7 @@ int launch_gn_stats(Act<T> r, float* part, cudaStream_t s) {
 }
 
 int launch_gn_finalize(const float* part, float* stats, int N, int slots, double count, cudaStream_t s) {
+    ProfScope prof_("gn_finalize", s);
     gn_finalize_kernel<<<N * kGroups, 32, 0, s>>>(part, stats, slots, count);
     MRISR_LAUNCH_CHECK();
     return 0;
@@ -231,6 +234,7 @@ int launch_gn_finalize(const float* part, float* stats, int N, int slots, double
 template <typename T>
 int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const float* beta, Act<T> a, Act<T> pooled,
                     cudaStream_t s) {
+    ProfScope prof_("gn_apply", s);
     const int nv = r.C / 8;
     if (pooled.p) {
         gn_apply_kernel<T, true><<<grid_for((int64_t)r.N * (r.H / 2) * (r.W / 2) * nv), NTHR, 0, s>>>(r, stats, gamma,
@@ -245,6 +249,7 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
+    ProfScope prof_("upsample2x", s);
     upsample2x_kernel<T><<<grid_for((int64_t)dst.N * dst.H * dst.W * (src.C / 8)), NTHR, 0, s>>>(
         src, dst, up_scale(src.H), up_scale(src.W));
     MRISR_LAUNCH_CHECK();
@@ -253,6 +258,7 @@ int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
 
 template <typename T>
 int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t s) {
+    ProfScope prof_("upsample2x_bwd", s);
     upsample2x_bwd_kernel<T><<<grid_for((int64_t)dsrc.N * dsrc.H * dsrc.W * (dsrc.C / 8)), NTHR, 0, s>>>(
         ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W));
     MRISR_LAUNCH_CHECK();
