@@ -95,6 +95,22 @@ int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* ex
                     float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                     float grad_scale, void* stream);
 
+/* ---- convolution building block over padded NHWC bf16 tensors ---------------------------------
+ * The implicit-GEMM kernels behind every nn.Conv2d of models/unet_model.py:29,34,72,101,152,168 (and of the VGG19
+ * feature stack, utils/losses.py:90-95), exposed one layer at a time: the parity tests call them with both engines.
+ * Tensors are [N][H+2][W+2][C] bf16 with a zero one-pixel border (pointer = padded origin); `w` is the reference's fp32
+ * [Cout][Cin][ks][ks] weight.  engine: 0 = CUDA cores, 1 = tcgen05/TMEM/TMA.  transposed != 0 computes the data
+ * gradient instead: src1 = dL/d(out) with C1 = forward Cout channels, dst = dL/d(in) with `Cout` = forward Cin channels,
+ * `w` still the forward weight [C1][Cout][ks][ks].  stats (nullable): [N][8][2] GroupNorm(8) (mean, rstd) of dst.
+ * Border pixels of dst are never written (they must already be zero). */
+size_t mrisr_conv2d_scratch_bytes(int N, int H, int W, int C1, int C2, int Cout, int ks);
+int mrisr_conv2d_bf16(const void* src1, int C1, const void* src2, int C2, const float* w, const float* bias, void* dst,
+                      float* stats, void* scratch, size_t scratch_bytes, int N, int H, int W, int Cout, int ks,
+                      int transposed, int engine, void* stream);
+/* dw: fp32 [Cout][C1+C2][ks][ks], overwritten with sum over pixels of in (x) dy; dy must have a zero border. */
+int mrisr_conv2d_wgrad_bf16(const void* src1, int C1, const void* src2, int C2, const void* dy, float* dw, void* scratch,
+                            size_t scratch_bytes, int N, int H, int W, int Cout, int ks, int engine, void* stream);
+
 /* ---- debugging aid: copy one internal workspace tensor out as dense NCHW fp32 --------------- */
 /* kind: 0 raw conv output R[l], 1 activation A[l], 2 pooled P[l], 3 low-res 1x1 output Q[l], 4 dR[l], 5 G[l]
  * (gradient wrt the input of conv l), 6 dQ[l], 7 UB, 8 XM (blend), 9 DY3.  dims_host[4] (HOST) receives N,C,H,W;

@@ -39,6 +39,11 @@ SIGNATURES = {
                                    c_int, c_float, c_float, c_void_p]),
     "mrisr_unet_debug_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_void_p]),
+    "mrisr_conv2d_scratch_bytes": (c_size_t, [c_int] * 7),
+    "mrisr_conv2d_bf16": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_size_t, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_conv2d_wgrad_bf16": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
+                                        c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mrisr_launch_count": (ctypes.c_longlong, []),
     "mrisr_prof_enable": (c_int, [c_int]),
     "mrisr_prof_report": (c_int, [c_char_p, c_size_t]),

@@ -1,0 +1,421 @@
+// tcgen05 implicit-GEMM convolution (3x3 pad 1 / 1x1, stride 1) over padded NHWC bf16 activations, fp32 accumulate in TMEM.
+// Replaces the cuDNN convolutions behind nn.Conv2d in models/unet_model.py:29,34,72,101,152,168 for the forward pass and,
+// with tap-flipped transposed weights, their data gradients (autograd; the reference has no hand-written backward).
+//
+// Formulation.  A padded activation [N][H+2][W+2][C] is a 2-D matrix [rows = N*(H+2)*(W+2)][C]; with a zero border a 3x3
+// tap (ty, tx) is the SAME matrix shifted by (ty-1)*(W+2) + (tx-1) rows.  One CTA tile is 128 consecutive rows (pixels) x
+// all Cout channels:  D[128 x Cout] = sum_{tap, k-chunk} A_shift(tap)[128 x BK] * Wt[tap][Cout x BK]^T.
+// A and B tiles are fetched by TMA straight into the 32/64/128-byte swizzled K-major layout tcgen05.mma reads
+// (out-of-range rows are zero-filled by TMA), so the skip-concatenation is just a second tensor map over the K loop.
+// Rows that are border pixels compute garbage and are simply not stored (the zero border is an invariant).
+//
+// Warp roles (192 threads, 1 CTA/SM, persistent over tiles): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue (TMEM -> registers -> +bias -> bf16 -> global, GroupNorm partial sums).  Two TMEM accumulator
+// buffers let the epilogue of tile i overlap the MMAs of tile i+1.
+#include <mutex>
+#include "kernels.cuh"
+#include "tc_common.cuh"
+
+namespace mrisr {
+namespace tc {
+
+// ---------------------------------------------------------------- host: tensor map encoder
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return -6; }
+    const uint32_t bytes = box_cols * 2;
+    CUtensorMapSwizzle sw = bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    if (sw == CU_TENSOR_MAP_SWIZZLE_NONE || box_rows > 256 || (cols * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0) {
+        set_error("make_tmap_2d_bf16: unsupported box %ux%u / cols %llu / base %p", box_rows, box_cols, (unsigned long long)cols, base);
+        return -6;
+    }
+    const cuuint64_t gdim[2] = {cols, rows};
+    const cuuint64_t gstride[1] = {cols * 2};
+    const cuuint32_t box[2] = {box_cols, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return -6; }
+    return 0;
+}
+
+// ---------------------------------------------------------------- device
+struct ConvTcParams {
+    __nv_bfloat16* dst;     // padded origin of the output tensor (Cout = BN channels per row)
+    const float* bias;      // [BN] or nullptr
+    float* stat_part;       // [num_tiles][2][8][2] GroupNorm partial (sum, sumsq) or nullptr
+    int chunks1, chunks2;   // K chunks of BK channels taken from source 1 / source 2
+    int taps;               // 1 or 9
+    int pw;                 // padded row pitch W + 2
+    int S;                  // padded pixels per sample (H + 2) * (W + 2)
+    int H, W;
+    int total_rows;         // N * S
+    int num_tiles;
+};
+
+template <int BN, int BK>
+struct ConvTcCfg {
+    static constexpr int BM = 128;
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
+    static constexpr int SWZ = BK * 2;
+    static constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
+};
+
+// sum of 16 per-lane values over the warp in 16 shuffles: afterwards v[0] on lane l holds the total of index l >> 1
+__device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float send = (lane & 16) ? v[i] : v[i + 8], keep = (lane & 16) ? v[i + 8] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float send = (lane & 8) ? v[i] : v[i + 4], keep = (lane & 8) ? v[i + 4] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const float send = (lane & 4) ? v[i] : v[i + 2], keep = (lane & 4) ? v[i + 2] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    {
+        const float send = (lane & 2) ? v[0] : v[1], keep = (lane & 2) ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+template <int BN, int BK>
+__global__ void __launch_bounds__(192, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+    using Cfg = ConvTcCfg<BN, BK>;
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr uint32_t LT = layout_type_for(Cfg::SWZ);
+    constexpr uint32_t SBO = 8 * Cfg::SWZ;
+    constexpr uint32_t IDESC = make_idesc_bf16(128, BN, 0, 0);
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES];
+    __shared__ __align__(8) uint64_t tfull_bar[2];
+    __shared__ __align__(8) uint64_t tempty_bar[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_part[2][4][2][16];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmA2);
+        tma_prefetch_desc(&tmB);
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 128); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(&s_tmem, Cfg::TMEM_COLS);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = s_tmem;
+    const int cpt = p.chunks1 + p.chunks2;            // K chunks per tap
+    const int num_kb = p.taps * cpt;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                const int m0 = tile * 128;
+                for (int tap = 0; tap < p.taps; ++tap) {
+                    const int shift = p.taps == 9 ? (tap / 3 - 1) * p.pw + (tap % 3 - 1) : 0;
+                    for (int c = 0; c < cpt; ++c) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                        uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
+                        if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, m0 + shift);
+                        else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, m0 + shift);
+                        tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * BN);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+                const int buf = it & 1;
+                mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d = tmem_base + (uint32_t)(buf * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after_sync();
+                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint32_t b_addr = a_addr + Cfg::A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t adesc = make_smem_desc(a_addr + k * 32, 16, SBO, LT);
+                        const uint64_t bdesc = make_smem_desc(b_addr + k * 32, 16, SBO, LT);
+                        umma_bf16(d, adesc, bdesc, IDESC, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs have read it
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull_bar[buf]);                // accumulator complete -> epilogue
+            }
+        }
+    } else {
+        // ===== epilogue: 4 warps, warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32) =====
+        const int q = warp & 3;
+        constexpr int GS = BN / 8;                           // channels per GroupNorm group
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
+            tc_fence_after_sync();
+            const int row = tile * 128 + q * 32 + lane;
+            const int n = row / p.S;
+            const int rem = row - n * p.S;
+            const int y = rem / p.pw, x = rem - y * p.pw;
+            const bool valid = row < p.total_rows && y >= 1 && y <= p.H && x >= 1 && x <= p.W;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+            __nv_bfloat16* out = p.dst + (int64_t)row * BN;
+            float s1[8], s2[8];
+#pragma unroll
+            for (int g = 0; g < 8; ++g) s1[g] = s2[g] = 0.f;
+#pragma unroll
+            for (int c0 = 0; c0 < BN; c0 += 16) {
+                float v[16];
+                tmem_ld16(taddr + c0, v);
+                if (p.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += __ldg(p.bias + c0 + i);
+                }
+                if (valid) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int g = (c0 + i) / GS;
+                        s1[g] += v[i];
+                        s2[g] = fmaf(v[i], v[i], s2[g]);
+                    }
+                    uint4 o0, o1;
+                    o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
+                    o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
+                    o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
+                    o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
+                    *reinterpret_cast<uint4*>(out + c0) = o0;
+                    *reinterpret_cast<uint4*>(out + c0 + 8) = o1;
+                }
+            }
+            tc_fence_before_sync();
+            mbar_arrive(&tempty_bar[buf]);                   // TMEM buffer may be overwritten by tile it + 2
+            if (p.stat_part) {
+                const int n0 = (tile * 128) / p.S;
+                const int slot = n - n0;                     // 0 or 1 (S >= 128)
+#pragma unroll
+                for (int sl = 0; sl < 2; ++sl) {
+                    const bool mine = valid && slot == sl;
+                    if (__ballot_sync(0xffffffffu, mine) != 0u) {
+                        float w[16];
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) { w[2 * g] = mine ? s1[g] : 0.f; w[2 * g + 1] = mine ? s2[g] : 0.f; }
+                        warp_reduce16(w, lane);
+                        if ((lane & 1) == 0) s_part[it & 1][q][sl][lane >> 1] = w[0];
+                    } else if (lane < 16) {
+                        s_part[it & 1][q][sl][lane] = 0.f;
+                    }
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (q == 0) {
+                    const int sl = lane >> 4, idx = lane & 15;
+                    const float t = (s_part[it & 1][0][sl][idx] + s_part[it & 1][1][sl][idx]) +
+                                    (s_part[it & 1][2][sl][idx] + s_part[it & 1][3][sl][idx]);
+                    p.stat_part[((int64_t)tile * 2 + sl) * 16 + idx] = t;
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+// stats[n][g] = (mean, rstd) from the per-tile partials of conv_tc_kernel
+__global__ void __launch_bounds__(256) gn_finalize_tc_kernel(const float* __restrict__ part, float* __restrict__ stats, int S,
+                                                             int num_tiles, double count) {
+    __shared__ double s_acc[16][16];
+    const int n = blockIdx.x;
+    const int idx = threadIdx.x & 15, tl = threadIdx.x >> 4;
+    const int t_first = (int)(((int64_t)n * S) / 128), t_last = (int)((((int64_t)n + 1) * S - 1) / 128);
+    double acc = 0.0;
+    for (int t = t_first + tl; t <= t_last && t < num_tiles; t += 16) {
+        const int sl = n - (int)(((int64_t)t * 128) / S);
+        if (sl == 0 || sl == 1) acc += (double)part[((int64_t)t * 2 + sl) * 16 + idx];
+    }
+    s_acc[tl][idx] = acc;
+    __syncthreads();
+    if (threadIdx.x < kGroups) {
+        const int g = threadIdx.x;
+        double a = 0.0, b = 0.0;
+        for (int j = 0; j < 16; ++j) { a += s_acc[j][2 * g]; b += s_acc[j][2 * g + 1]; }
+        const double mean = a / count;
+        double var = b / count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        stats[(n * kGroups + g) * 2] = (float)mean;
+        stats[(n * kGroups + g) * 2 + 1] = (float)(1.0 / sqrt(var + (double)kGnEps));
+    }
+}
+
+// fp32 NCHW [Cout][Cin][ks][ks] -> wt_fwd[tap][Cout][Cin] and wt_dgrad[taps-1-tap][Cin][Cout] (both K-major bf16)
+__global__ void pack_weights_tc_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wf,
+                                       __nv_bfloat16* __restrict__ wd, int Cout, int Cin, int taps) {
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int tap = (int)(i % taps);
+        const int ci = (int)((i / taps) % Cin);
+        const int co = (int)(i / ((int64_t)taps * Cin));
+        const __nv_bfloat16 v = __float2bfloat16_rn(w[i]);
+        wf[((int64_t)tap * Cout + co) * Cin + ci] = v;
+        if (wd) wd[((int64_t)(taps - 1 - tap) * Cin + ci) * Cout + co] = v;
+    }
+}
+
+template <int BN, int BK>
+static int launch_cfg(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
+                      cudaStream_t s) {
+    using Cfg = ConvTcCfg<BN, BK>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        attr_done = true;
+    }
+    conv_tc_kernel<BN, BK><<<grid, 192, Cfg::SMEM_BYTES, s>>>(tA1, tA2, tB, p);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int BN>
+static int launch_bn(int bk, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
+                     cudaStream_t s) {
+    switch (bk) {
+        case 64: return launch_cfg<BN, 64>(tA1, tA2, tB, p, grid, s);
+        case 32: return launch_cfg<BN, 32>(tA1, tA2, tB, p, grid, s);
+        default: return launch_cfg<BN, 16>(tA1, tA2, tB, p, grid, s);
+    }
+}
+
+int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+}  // namespace tc
+
+using bf16 = __nv_bfloat16;
+
+bool conv_tc_supported(int H, int W, int C1, int C2, int Cout, int ks) {
+    const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256;
+    return cout_ok && C1 >= 16 && C1 % 16 == 0 && C2 % 16 == 0 && (ks == 1 || ks == 3) && (int64_t)(H + 2) * (W + 2) >= 128;
+}
+
+int conv_tc_stat_elems(int N, int H, int W) {
+    const int64_t rows = (int64_t)N * (H + 2) * (W + 2);
+    return (int)(((rows + 127) / 128) * 32);
+}
+
+int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
+    const int C1 = a.src1.C, C2 = a.src2.p ? a.src2.C : 0, Cin = C1 + C2, Cout = a.dst.C;
+    const int H = a.dst.H, W = a.dst.W, N = a.dst.N;
+    if (!conv_tc_supported(H, W, C1, C2, Cout, a.ks)) {
+        set_error("conv_tc: unsupported shape C1=%d C2=%d Cout=%d ks=%d %dx%d", C1, C2, Cout, a.ks, H, W);
+        return -2;
+    }
+    const char* tag = "conv_tc";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "conv_tc:k%d:%d>%d@%dx%d", a.ks, Cin, Cout, H, W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
+    int bk = 64;
+    if (C1 % 64 || C2 % 64) bk = (C1 % 32 || C2 % 32) ? 16 : 32;
+    const int64_t rows = (int64_t)N * (H + 2) * (W + 2);
+    const int taps = a.ks * a.ks;
+    CUtensorMap tA1, tA2, tB;
+    int rc = tc::make_tmap_2d_bf16(&tA1, a.src1.p, (uint64_t)rows, (uint64_t)C1, 128, (uint32_t)bk);
+    if (rc) return rc;
+    if (C2) { rc = tc::make_tmap_2d_bf16(&tA2, a.src2.p, (uint64_t)rows, (uint64_t)C2, 128, (uint32_t)bk); if (rc) return rc; }
+    else tA2 = tA1;
+    rc = tc::make_tmap_2d_bf16(&tB, a.w, (uint64_t)taps * Cout, (uint64_t)Cin, (uint32_t)Cout, (uint32_t)bk);
+    if (rc) return rc;
+    tc::ConvTcParams p;
+    p.dst = a.dst.p; p.bias = a.bias; p.stat_part = a.stat_part;
+    p.chunks1 = C1 / bk; p.chunks2 = C2 / bk; p.taps = taps;
+    p.pw = W + 2; p.S = (H + 2) * (W + 2); p.H = H; p.W = W;
+    p.total_rows = (int)rows; p.num_tiles = (int)((rows + 127) / 128);
+    const int grid = p.num_tiles < tc::num_sms() ? p.num_tiles : tc::num_sms();
+    switch (Cout) {
+        case 16: return tc::launch_bn<16>(bk, tA1, tA2, tB, p, grid, s);
+        case 32: return tc::launch_bn<32>(bk, tA1, tA2, tB, p, grid, s);
+        case 64: return tc::launch_bn<64>(bk, tA1, tA2, tB, p, grid, s);
+        case 128: return tc::launch_bn<128>(bk, tA1, tA2, tB, p, grid, s);
+        default: return tc::launch_bn<256>(bk, tA1, tA2, tB, p, grid, s);
+    }
+}
+
+int launch_gn_finalize_tc(const float* part, float* stats, int N, int H, int W, double count, cudaStream_t s) {
+    ProfScope prof_("gn_finalize", s);
+    const int S = (H + 2) * (W + 2);
+    const int num_tiles = (int)(((int64_t)N * S + 127) / 128);
+    tc::gn_finalize_tc_kernel<<<N, 256, 0, s>>>(part, stats, S, num_tiles, count);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_pack_weights_tc(const float* w, bf16* wf, bf16* wd, int Cout, int Cin, int ks, cudaStream_t s) {
+    ProfScope prof_("pack_weights", s);
+    const int64_t total = (int64_t)Cout * Cin * ks * ks;
+    int blocks = (int)ceil_div64(total, 256);
+    if (blocks > 1184) blocks = 1184;
+    tc::pack_weights_tc_kernel<<<blocks, 256, 0, s>>>(w, wf, wd, Cout, Cin, ks * ks);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mrisr

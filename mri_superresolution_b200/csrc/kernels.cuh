@@ -34,6 +34,18 @@ template <typename T> int launch_wgrad_generic(const WgradArgs<T>& a, cudaStream
 template <typename T>
 int launch_pack_weights(const float* w, T* w_fwd, T* w_dgrad, int Cout, int Cin, int ks, cudaStream_t s);
 
+// ---------------------------------------------------------------- tcgen05 convolution (conv_tc.cu, wgrad_tc.cu), bf16 only
+// ConvArgs::w is the K-major pack of launch_pack_weights_tc ([tap][Cout][Cin] forward, [tap'][Cin][Cout] dgrad);
+// ConvArgs::stat_part receives [tiles][2][8][2] partials (conv_tc_stat_elems floats) consumed by launch_gn_finalize_tc.
+bool conv_tc_supported(int H, int W, int C1, int C2, int Cout, int ks);
+int conv_tc_stat_elems(int N, int H, int W);
+int launch_conv_tc(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s);
+int launch_gn_finalize_tc(const float* part, float* stats, int N, int H, int W, double count, cudaStream_t s);
+int launch_pack_weights_tc(const float* w, __nv_bfloat16* wf, __nv_bfloat16* wd, int Cout, int Cin, int ks, cudaStream_t s);
+bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks);
+size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks);
+int launch_wgrad_tc(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
+
 // ---------------------------------------------------------------- normalisation / activation (norm_act.cu)
 template <typename T> int launch_pack_input(const float* x, Act<T> dst, cudaStream_t s);
 

@@ -84,8 +84,13 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         const int h = lvl_dim(H, rl), w = lvl_dim(W, rl);
         size_t slots = std::max(conv_generic_stat_slots(h, w, c.cout), stat_slots_generic(h, w, c.cout));
         part_max = std::max(part_max, (size_t)N * slots * kGroups * 2);
+        part_max = std::max(part_max, (size_t)conv_tc_stat_elems(N, h, w));
         gnp_max = std::max(gnp_max, (size_t)N * gn_bwd_slots(h, w, c.cout) * 3 * (c.cout + 8));
         wg_max = std::max(wg_max, wgrad_generic_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
+        if (sizeof(T) == 2 && layer_uses_tc(c, l, H, W)) {
+            const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin;
+            wg_max = std::max(wg_max, wgrad_tc_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c1, c.cin - c1, c.cout, c.ks));
+        }
     }
     UB = make_act(ar, -1, f);
     XM = make_act(ar, -1, f / 2);

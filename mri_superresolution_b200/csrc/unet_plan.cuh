@@ -1,5 +1,6 @@
 // Static description of UNetSuperRes (models/unet_model.py:129-175) and the workspace layout.
 #pragma once
+#include <stdlib.h>
 #include <vector>
 #include "kernels.cuh"
 
@@ -22,6 +23,16 @@ struct ConvDesc {
 void conv_table(int f, ConvDesc (&t)[kNumConv]);
 
 inline int lvl_dim(int d, int lvl) { return lvl < 0 ? 2 * d : d >> lvl; }
+inline bool is_concat_conv(int l) { return l == 9 || l == 12 || l == 15; }   // DoubleConv fed by cat([skip, up])
+// bf16 mode: does conv l (forward, data gradient and weight gradient) run on the tcgen05 kernels at input size HxW?
+inline bool layer_uses_tc(const ConvDesc& c, int l, int H, int W) {
+    static const bool disabled = getenv("MRISR_DEBUG_NO_TC") != nullptr;   // debugging aid: all layers on CUDA cores
+    if (disabled) return false;
+    const int h = lvl_dim(H, c.lvl), w = lvl_dim(W, c.lvl);
+    const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin, c2 = c.cin - c1;
+    return conv_tc_supported(h, w, c1, c2, c.cout, c.ks) && conv_tc_supported(h, w, c.cout, 0, c.cin, c.ks) &&
+           wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks);
+}
 
 // Bump allocator over the caller's workspace (base == nullptr -> size query only).
 struct Arena {

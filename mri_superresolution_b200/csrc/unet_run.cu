@@ -15,6 +15,7 @@ struct Runner {
     const float* params;
     cudaStream_t s;
     const float* P(int idx) const { return params + pl.off[idx]; }
+    bool tc(int l) const { return sizeof(T) == 2 && layer_uses_tc(ws.conv[l], l, ws.H, ws.W); }
 
     // conv l: (src1 [, src2]) -> dst, GroupNorm partial statistics when `stats`
     int conv(int l, Act<T> src1, Act<T> src2, Act<T> dst, bool want_stats) {
@@ -23,6 +24,14 @@ struct Runner {
         a.src1 = src1; a.src2 = src2; a.w = ws.wf[l];
         a.bias = c.bias >= 0 ? P(c.bias) : nullptr;
         a.dst = dst; a.stat_part = want_stats ? ws.stat_part : nullptr; a.ks = c.ks;
+        if constexpr (sizeof(T) == 2) {
+            if (tc(l)) {
+                TRY(launch_conv_tc(a, s));
+                if (want_stats) TRY(launch_gn_finalize_tc(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W,
+                                                          (double)(dst.C / kGroups) * dst.H * dst.W, s));
+                return 0;
+            }
+        }
         TRY(launch_conv_generic<T>(a, s));
         if (want_stats) {
             const int slots = conv_generic_stat_slots(dst.H, dst.W, dst.C);
@@ -63,6 +72,12 @@ struct Runner {
         const Act<T> none{nullptr, 0, 0, 0, 0};
         for (int l = 0; l < kNumConv; ++l) {
             const ConvDesc& c = ws.conv[l];
+            if constexpr (sizeof(T) == 2) {
+                if (tc(l)) {
+                    TRY(launch_pack_weights_tc(P(c.w), ws.wf[l], train && l > 0 ? ws.wd[l] : nullptr, c.cout, c.cin, c.ks, s));
+                    continue;
+                }
+            }
             TRY(launch_pack_weights<T>(P(c.w), ws.wf[l], train && l > 0 ? ws.wd[l] : nullptr, c.cout, c.cin, c.ks, s));
         }
         TRY(launch_pack_input<T>(x, ws.X0, s));
@@ -112,11 +127,19 @@ struct Runner {
         const Act<T> none{nullptr, 0, 0, 0, 0};
         WgradArgs<T> w;
         w.src1 = src1; w.src2 = src2; w.dy = dy; w.dw = GP(c.w); w.partial = ws.wg_part; w.ks = c.ks;
-        TRY(launch_wgrad_generic<T>(w, s));
+        bool use_tc = false;
+        if constexpr (sizeof(T) == 2) use_tc = tc(l);
+        if constexpr (sizeof(T) == 2) {
+            if (use_tc) TRY(launch_wgrad_tc(w, s));
+        }
+        if (!use_tc) TRY(launch_wgrad_generic<T>(w, s));
         if (want_dgrad) {
             ConvArgs<T> a;
             a.src1 = dy; a.src2 = none; a.w = ws.wd[l]; a.bias = nullptr; a.dst = ws.G[l]; a.stat_part = nullptr; a.ks = c.ks;
-            TRY(launch_conv_generic<T>(a, s));
+            if constexpr (sizeof(T) == 2) {
+                if (use_tc) TRY(launch_conv_tc(a, s));
+            }
+            if (!use_tc) TRY(launch_conv_generic<T>(a, s));
         }
         return 0;
     }

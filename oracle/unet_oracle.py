@@ -162,3 +162,81 @@ def unet_forward(p: Dict[str, torch.Tensor], x: torch.Tensor, taps: Dict[str, to
                   p["final_conv.1.weight"], p["final_conv.1.bias"])                     # :168-170
     z = F.conv2d(z, p["final_conv.3.weight"], p["final_conv.3.bias"])                   # :172
     return torch.sigmoid(z)                                                             # :211
+
+
+# ----------------------------------------------------------------------------------------------
+# bf16-storage restatement: the SAME algorithm with every operand the CUDA bf16 mode stores in
+# bfloat16 rounded at exactly that point (input image, conv weights, raw conv outputs, activations,
+# the low-resolution 1x1 output of Up.up, the blended head tensor); all arithmetic in fp32.
+# Rounding is straight-through for autograd, so .backward() gives the gradient of the bf16
+# forward with fp32 gradient arithmetic.  It separates "the kernels compute the bf16-operand
+# algorithm exactly" (tight tolerance against THIS function) from the bf16-vs-fp32 noise floor of
+# a 21-conv network (measured against unet_forward and reported in DESIGN.md).
+class _RoundBF16(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def _q(x: torch.Tensor) -> torch.Tensor:
+    return _RoundBF16.apply(x)
+
+
+def _gn_lrelu_q(r: torch.Tensor, w: torch.Tensor, b: torch.Tensor, stats_from_rounded: bool = False) -> torch.Tensor:
+    """GroupNorm statistics from the fp32 conv result (the conv epilogue accumulates them before
+    rounding), normalisation applied to the stored bf16 tensor, result stored in bf16."""
+    n, c = r.shape[:2]
+    rq = _q(r)
+    src = rq if stats_from_rounded else r
+    g = src.reshape(n, GN_GROUPS, -1)
+    mean = g.mean(2, keepdim=True)
+    var = g.var(2, unbiased=False, keepdim=True)
+    xn = ((rq.reshape(n, GN_GROUPS, -1) - mean) * torch.rsqrt(var + GN_EPS)).reshape(r.shape)
+    return _q(F.leaky_relu(xn * w.view(1, c, 1, 1) + b.view(1, c, 1, 1), LRELU_SLOPE))
+
+
+def unet_forward_bf16_storage(p: Dict[str, torch.Tensor], x: torch.Tensor, first_layer_fp32: bool = False) -> torch.Tensor:
+    def dconv(prefix: str, t: torch.Tensor, first: bool = False) -> torch.Tensor:
+        w0, w3 = p[f"{prefix}.double_conv.0.weight"], p[f"{prefix}.double_conv.3.weight"]
+        r = F.conv2d(t, w0 if first and first_layer_fp32 else _q(w0), None, padding=1)
+        t = _gn_lrelu_q(r, p[f"{prefix}.double_conv.1.weight"], p[f"{prefix}.double_conv.1.bias"])
+        r = F.conv2d(t, _q(w3), None, padding=1)
+        return _gn_lrelu_q(r, p[f"{prefix}.double_conv.4.weight"], p[f"{prefix}.double_conv.4.bias"])
+
+    def up(name: str, x1: torch.Tensor, x2: torch.Tensor) -> torch.Tensor:
+        # conv1x1 commuted below the bilinear interpolation (both linear, no bias): models/unet_model.py:70-72
+        ql = _q(F.conv2d(x1, _q(p[f"{name}.up.1.weight"]), None))
+        r = F.interpolate(ql, scale_factor=2, mode="bilinear", align_corners=True)
+        u = _gn_lrelu_q(r, p[f"{name}.up.2.weight"], p[f"{name}.up.2.bias"], stats_from_rounded=True)
+        return dconv(f"{name}.conv", torch.cat([x2, u], dim=1))
+
+    x1 = dconv("inc", x if first_layer_fp32 else _q(x), first=True)
+    x2 = dconv("down1.maxpool_conv.1", F.max_pool2d(x1, 2))
+    x3 = dconv("down2.maxpool_conv.1", F.max_pool2d(x2, 2))
+    x4 = dconv("down3.maxpool_conv.1", F.max_pool2d(x3, 2))
+    y = up("up1", x4, x3)
+    y = up("up2", y, x2)
+    y = up("up3", y, x1)
+    ub = _q(F.interpolate(y, scale_factor=2, mode="bilinear", align_corners=True))
+    r17 = F.conv2d(ub, _q(p["final_up_bilinear.1.weight"]), None, padding=1)
+    r18 = F.conv2d(y, _q(p["final_up_pixelshuffle.conv.weight"]), p["final_up_pixelshuffle.conv.bias"], padding=1)
+
+    def gn_only(r, w, b):      # the head blends the two normalised branches in registers: only XM is stored
+        n, c = r.shape[:2]
+        g = r.reshape(n, GN_GROUPS, -1)
+        mean, var = g.mean(2, keepdim=True), g.var(2, unbiased=False, keepdim=True)
+        xn = ((_q(r).reshape(n, GN_GROUPS, -1) - mean) * torch.rsqrt(var + GN_EPS)).reshape(r.shape)
+        return F.leaky_relu(xn * w.view(1, c, 1, 1) + b.view(1, c, 1, 1), LRELU_SLOPE)
+
+    xb = gn_only(r17, p["final_up_bilinear.2.weight"], p["final_up_bilinear.2.bias"])
+    xp = gn_only(F.pixel_shuffle(r18, 2), p["final_up_pixelshuffle.norm.weight"], p["final_up_pixelshuffle.norm.bias"])
+    a = torch.sigmoid(p["alpha"])
+    xm = _q(a * xb + (1 - a) * xp)
+    r19 = F.conv2d(xm, _q(p["final_conv.0.weight"]), None, padding=1)
+    z = gn_only(r19, p["final_conv.1.weight"], p["final_conv.1.bias"])
+    z = F.conv2d(z, p["final_conv.3.weight"], p["final_conv.3.bias"])
+    return torch.sigmoid(z)

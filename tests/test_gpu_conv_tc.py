@@ -1,0 +1,144 @@
+"""GPU parity tests of the convolution building block (mrisr_conv2d_*): the tcgen05/TMEM/TMA engine and the CUDA-core
+engine against a torch fp32 convolution of the same bf16-rounded operands (the per-layer restatement of nn.Conv2d /
+its autograd, models/unet_model.py:29-37).  Tolerance: bf16 output rounding (<= 2^-8 relative to the tensor's max) for
+activations; 2e-3 relative for the fp32 weight gradient and GroupNorm statistics."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from mri_superresolution_b200 import _native
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def pad_nhwc(x):
+    """NCHW fp32 -> padded NHWC bf16 [N][H+2][W+2][C] with a zero border."""
+    n, c, h, w = x.shape
+    out = torch.zeros(n, h + 2, w + 2, c, dtype=torch.bfloat16, device=x.device)
+    out[:, 1:-1, 1:-1, :] = x.permute(0, 2, 3, 1).to(torch.bfloat16)
+    return out.contiguous()
+
+
+def unpad_nchw(p):
+    return p[:, 1:-1, 1:-1, :].permute(0, 3, 1, 2).float().contiguous()
+
+
+def rel_inf(a, b):
+    return float((a.double() - b.double()).abs().max() / max(float(b.double().abs().max()), 1e-30))
+
+
+def run_conv(x1, x2, w, bias, cout, ks, engine, want_stats, transposed=False):
+    L = _native.lib()
+    n, c1, h, wd = x1.shape
+    c2 = x2.shape[1] if x2 is not None else 0
+    sb = L.mrisr_conv2d_scratch_bytes(n, h, wd, c1, c2, cout, ks)
+    scratch = torch.empty(sb, dtype=torch.uint8, device=x1.device)
+    p1 = pad_nhwc(x1)
+    p2 = pad_nhwc(x2) if x2 is not None else None
+    dst = torch.zeros(n, h + 2, wd + 2, cout, dtype=torch.bfloat16, device=x1.device)
+    stats = torch.zeros(n, 8, 2, device=x1.device) if want_stats else None
+    rc = L.mrisr_conv2d_bf16(_native.ptr(p1), c1, _native.ptr(p2), c2, _native.ptr(w), _native.ptr(bias), _native.ptr(dst),
+                             _native.ptr(stats), _native.ptr(scratch), sb, n, h, wd, cout, ks, 1 if transposed else 0,
+                             engine, _native.stream_ptr())
+    _native.check(rc, "conv2d")
+    torch.cuda.synchronize()
+    border = dst.clone()
+    border[:, 1:-1, 1:-1, :] = 0
+    assert float(border.float().abs().max()) == 0.0, "border pixels were written"
+    return unpad_nchw(dst), stats
+
+
+def run_wgrad(x1, x2, dy, ks, engine):
+    L = _native.lib()
+    n, c1, h, wd = x1.shape
+    c2 = x2.shape[1] if x2 is not None else 0
+    cout = dy.shape[1]
+    sb = L.mrisr_conv2d_scratch_bytes(n, h, wd, c1, c2, cout, ks)
+    scratch = torch.empty(sb, dtype=torch.uint8, device=x1.device)
+    p1, p2, pdy = pad_nhwc(x1), (pad_nhwc(x2) if x2 is not None else None), pad_nhwc(dy)
+    dw = torch.zeros(cout, c1 + c2, ks, ks, device=x1.device)
+    rc = L.mrisr_conv2d_wgrad_bf16(_native.ptr(p1), c1, _native.ptr(p2), c2, _native.ptr(pdy), _native.ptr(dw),
+                                   _native.ptr(scratch), sb, n, h, wd, cout, ks, engine, _native.stream_ptr())
+    _native.check(rc, "wgrad")
+    torch.cuda.synchronize()
+    return dw
+
+
+def bf(x):
+    return x.to(torch.bfloat16).float()
+
+
+# (N, H, W, C1, C2, Cout, ks, bias)
+SHAPES = [
+    (2, 16, 16, 16, 0, 16, 3, False),       # BK=16 / 32-byte swizzle, N=16
+    (2, 24, 40, 32, 0, 32, 3, False),       # BK=32 / 64-byte swizzle, ragged tile edge
+    (3, 16, 24, 64, 0, 64, 3, True),        # BK=64 / 128-byte swizzle, bias
+    (2, 16, 16, 64, 64, 64, 3, False),      # skip-concat from two sources
+    (2, 16, 16, 32, 32, 32, 3, False),
+    (1, 32, 32, 128, 0, 256, 3, False),     # N=256: two full TMEM accumulator buffers
+    (2, 16, 16, 256, 0, 128, 1, False),     # 1x1
+    (2, 12, 20, 128, 128, 128, 3, False),
+    (4, 32, 32, 32, 0, 16, 3, False),       # head shapes
+    (2, 64, 64, 32, 0, 64, 3, True),
+    (2, 64, 48, 16, 0, 16, 3, False),
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv_forward_engines(shape):
+    n, h, w, c1, c2, cout, ks, use_bias = shape
+    g = torch.Generator("cpu").manual_seed(hash(shape) % 1000)
+    x1 = torch.randn(n, c1, h, w, generator=g).to(_dev())
+    x2 = torch.randn(n, c2, h, w, generator=g).to(_dev()) if c2 else None
+    wt = (torch.randn(cout, c1 + c2, ks, ks, generator=g) / (3.0 * (c1 + c2) ** 0.5)).to(_dev())
+    bias = torch.randn(cout, generator=g).to(_dev()) if use_bias else None
+    xin = bf(x1) if x2 is None else torch.cat([bf(x1), bf(x2)], 1)
+    ref = F.conv2d(xin.double(), bf(wt).double(), bias.double() if use_bias else None, padding=ks // 2).float()
+    gs = cout // 8
+    rg = ref.view(n, 8, gs * h * w).double()
+    ref_mean, ref_rstd = rg.mean(2), 1.0 / torch.sqrt(rg.var(2, unbiased=False) + 1e-5)
+    for engine in (0, 1):
+        out, stats = run_conv(x1, x2, wt, bias, cout, ks, engine, True)
+        e = rel_inf(out, ref)
+        assert e < 6e-3, (engine, shape, e)
+        assert rel_inf(stats[:, :, 0], ref_mean.float()) < 2e-3 or float((stats[:, :, 0] - ref_mean.float()).abs().max()) < 2e-4, (engine, shape)
+        assert rel_inf(stats[:, :, 1], ref_rstd.float()) < 2e-3, (engine, shape)
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv_dgrad_engines(shape):
+    n, h, w, c1, c2, cout, ks, _ = shape
+    cin = c1 + c2
+    if cin not in (16, 32, 64, 128, 256):
+        pytest.skip("dgrad output width must be a supported Cout")
+    g = torch.Generator("cpu").manual_seed(7 + hash(shape) % 1000)
+    dy = torch.randn(n, cout, h, w, generator=g).to(_dev())
+    wt = (torch.randn(cout, cin, ks, ks, generator=g) / (3.0 * cout ** 0.5)).to(_dev())
+    ref = F.conv_transpose2d(bf(dy).double(), bf(wt).double(), padding=ks // 2).float()
+    for engine in (0, 1):
+        out, _ = run_conv(dy, None, wt, None, cin, ks, engine, False, transposed=True)
+        e = rel_inf(out, ref)
+        assert e < 6e-3, (engine, shape, e)
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv_wgrad_engines(shape):
+    n, h, w, c1, c2, cout, ks, _ = shape
+    g = torch.Generator("cpu").manual_seed(11 + hash(shape) % 1000)
+    x1 = torch.randn(n, c1, h, w, generator=g).to(_dev())
+    x2 = torch.randn(n, c2, h, w, generator=g).to(_dev()) if c2 else None
+    dy = torch.randn(n, cout, h, w, generator=g).to(_dev())
+    xin = (bf(x1) if x2 is None else torch.cat([bf(x1), bf(x2)], 1)).double().requires_grad_(False)
+    wref = torch.zeros(cout, c1 + c2, ks, ks, dtype=torch.float64, device=_dev(), requires_grad=True)
+    F.conv2d(xin, wref, None, padding=ks // 2).backward(bf(dy).double())
+    ref = wref.grad.float()
+    for engine in (0, 1):
+        dw = run_wgrad(x1, x2, dy, ks, engine)
+        e = rel_inf(dw, ref)
+        assert e < 2e-3, (engine, shape, e)
