@@ -319,6 +319,13 @@ def run_ours(args):
             step(x_dev, t_dev)
         rep = _native.profile_report()
         _native.profile(False)
+        if args.layer_report:
+            with open(args.layer_report, "w") as fh:
+                for tag, calls, tms in sorted(rep, key=lambda r: -r[2]):
+                    fl = tag_flops(tag, nb) * calls / prof_steps
+                    ms_t = tms / prof_steps
+                    fh.write("%-44s calls/step %3d  ms/step %8.4f  TFLOP/s %s\n" % (
+                        tag, calls // prof_steps, ms_t, ("%.1f" % (fl / (ms_t * 1e-3) / 1e12)) if fl else "-"))
         fam = {}
         for tag, calls, tms in rep:
             name = tag.split(":")[0]
@@ -391,6 +398,7 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="slices per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layer-report", default=None, help="write the per-kernel-tag (per layer shape) timing table here")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
