@@ -99,15 +99,20 @@ int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* ex
  * The implicit-GEMM kernels behind every nn.Conv2d of models/unet_model.py:29,34,72,101,152,168 (and of the VGG19
  * feature stack, utils/losses.py:90-95), exposed one layer at a time: the parity tests call them with both engines.
  * Tensors are [N][H+2][W+2][C] bf16 with a zero one-pixel border (pointer = padded origin); `w` is the reference's fp32
- * [Cout][Cin][ks][ks] weight.  engine: 0 = CUDA cores, 1 = tcgen05/TMEM/TMA.  transposed != 0 computes the data
+ * [Cout][Cin][ks][ks] weight.  engine: 0 = CUDA cores, 1 = tcgen05/TMEM/TMA (NHWC), 2 = tcgen05 planar-8 (below).  transposed != 0 computes the data
  * gradient instead: src1 = dL/d(out) with C1 = forward Cout channels, dst = dL/d(in) with `Cout` = forward Cin channels,
  * `w` still the forward weight [C1][Cout][ks][ks].  stats (nullable): [N][8][2] GroupNorm(8) (mean, rstd) of dst.
  * Border pixels of dst are never written (they must already be zero). */
+/* engine 2 = tcgen05 sliding-window kernels over the planar-8 layout (narrow high-resolution layers): every tensor pointer
+ * is then the START of a planar allocation of C/8 planes x plane_pixels x 8 channels, in which padded-linear pixel 0 sits
+ * guard_pixels into each plane (mrisr_planar_geometry; guard contents are read but never influence stored outputs). */
+int mrisr_planar_geometry(int N, int H, int W, long long* host_guard_pixels, long long* host_plane_pixels);
 size_t mrisr_conv2d_scratch_bytes(int N, int H, int W, int C1, int C2, int Cout, int ks);
 int mrisr_conv2d_bf16(const void* src1, int C1, const void* src2, int C2, const float* w, const float* bias, void* dst,
                       float* stats, void* scratch, size_t scratch_bytes, int N, int H, int W, int Cout, int ks,
                       int transposed, int engine, void* stream);
-/* dw: fp32 [Cout][C1+C2][ks][ks], overwritten with sum over pixels of in (x) dy; dy must have a zero border. */
+/* dw: fp32 [Cout][C1+C2][ks][ks], overwritten with sum over pixels of in (x) dy; dy must have a zero border (and, for
+ * engine 2, zero guard pixels: the reduction runs over whole 128-pixel blocks; the guards of src1/src2 must be finite). */
 int mrisr_conv2d_wgrad_bf16(const void* src1, int C1, const void* src2, int C2, const void* dy, float* dw, void* scratch,
                             size_t scratch_bytes, int N, int H, int W, int Cout, int ks, int engine, void* stream);
 

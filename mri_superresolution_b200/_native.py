@@ -39,6 +39,7 @@ SIGNATURES = {
                                    c_int, c_float, c_float, c_void_p]),
     "mrisr_unet_debug_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_void_p]),
+    "mrisr_planar_geometry": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),
     "mrisr_conv2d_scratch_bytes": (c_size_t, [c_int] * 7),
     "mrisr_conv2d_bf16": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_size_t, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),

@@ -42,17 +42,34 @@ struct ProfScope {
 
 // Padded NHWC activation view: [N][H+2][W+2][C], zero one-pixel border kept as an invariant.
 // `p` points at the padded origin (n=0, row -1, col -1, c=0).
+//
+// Two memory layouts share this view (element (pixel P, channel c) lives at  P * ps + (c >> 3) * cs + (c & 7)):
+//   NHWC      ps = C, cs = 8            rows of C channels              (TMA / swizzled K-major tcgen05 kernels, conv_tc.cu)
+//   planar-8  ps = 8, cs = 8 * plane    C/8 planes of [pixel][8 ch]     (bulk-copy / no-swizzle tcgen05 kernels, conv_ring.cu)
+// where P = n * (H+2)*(W+2) + (y+1)*(W+2) + (x+1) is the padded-linear pixel index and `plane` the pixels per plane
+// (all samples plus guard pixels).  ps == 0 (aggregate-initialised views) means NHWC.
 template <typename T>
 struct Act {
     T* p;
     int N, H, W, C;
+    int ps = 0;             // pixel stride in elements (0 -> C)
+    int64_t cs = 8;         // stride between 8-channel chunks in elements
     __host__ __device__ __forceinline__ int pw() const { return W + 2; }
-    __host__ __device__ __forceinline__ int64_t sample_stride() const { return (int64_t)(H + 2) * (W + 2) * C; }
-    // offset of interior pixel (y, x) in [0,H) x [0,W)
-    __host__ __device__ __forceinline__ int64_t off(int n, int y, int x) const {
-        return n * sample_stride() + ((int64_t)(y + 1) * (W + 2) + (x + 1)) * C;
+    __host__ __device__ __forceinline__ int64_t sample_pixels() const { return (int64_t)(H + 2) * (W + 2); }
+    __host__ __device__ __forceinline__ int64_t rows() const { return (int64_t)N * sample_pixels(); }
+    __host__ __device__ __forceinline__ bool planar() const { return ps == 8 && C > 8; }
+    // padded-linear index of interior pixel (y, x) in [0,H) x [0,W)  (y, x = -1 / H, W address the zero border)
+    __host__ __device__ __forceinline__ int64_t pix(int n, int y, int x) const {
+        return n * sample_pixels() + (int64_t)(y + 1) * (W + 2) + (x + 1);
+    }
+    __host__ __device__ __forceinline__ T* at(int n, int y, int x, int c) const {
+        return p + pix(n, y, x) * (ps ? ps : C) + (int64_t)(c >> 3) * cs + (c & 7);
     }
 };
+
+// planar-8 geometry: pixels of guard on each side of a plane and pixels per plane (rows = N*(H+2)*(W+2))
+inline int64_t planar_guard(int W) { return (((int64_t)W + 4 + 127) / 128) * 128 + 128; }
+inline int64_t planar_plane(int64_t rows, int W) { return ((rows + 127) / 128) * 128 + 2 * planar_guard(W); }
 
 __device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : kSlope * z; }
 __device__ __forceinline__ float lrelu_grad(float z) { return z > 0.f ? 1.f : kSlope; }

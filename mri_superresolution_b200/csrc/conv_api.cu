@@ -27,14 +27,35 @@ struct Scratch {
             const size_t t = wgrad_tc_scratch_elems(N, H, W, C1, C2, Cout, ks);
             we = we > t ? we : t;
         }
+        if (wgrad_ring_supported(H, W, C1, C2, Cout, ks)) {
+            const size_t t = wgrad_ring_scratch_elems(N, H, W, C1 + C2, Cout, ks);
+            we = we > t ? we : t;
+        }
         part = (float*)c.take((pe > we ? pe : we) * sizeof(float));
         bytes = c.used;
     }
 };
-Act<bf16> act(const void* p, int N, int H, int W, int C) { return Act<bf16>{(bf16*)p, N, H, W, C}; }
+// engine 0 / 1: `p` is the padded origin of an NHWC tensor.  engine 2: `p` is the start of a planar-8 allocation
+// (C/8 planes of planar_plane() pixels x 8 channels, pixel 0 sits planar_guard() pixels into each plane).
+Act<bf16> act(const void* p, int N, int H, int W, int C, int engine = 0) {
+    Act<bf16> a{(bf16*)p, N, H, W, C};
+    if (engine == 2) {
+        a.ps = 8;
+        a.cs = planar_plane(a.rows(), W) * 8;
+        a.p = (bf16*)p + planar_guard(W) * 8;
+    }
+    return a;
+}
 }  // namespace
 
 extern "C" {
+
+int mrisr_planar_geometry(int N, int H, int W, long long* guard_pixels, long long* plane_pixels) {
+    if (N <= 0 || H <= 0 || W <= 0 || !guard_pixels || !plane_pixels) { set_error("planar_geometry: bad argument"); return MRISR_E_BADARG; }
+    *guard_pixels = planar_guard(W);
+    *plane_pixels = planar_plane((int64_t)N * (H + 2) * (W + 2), W);
+    return 0;
+}
 
 size_t mrisr_conv2d_scratch_bytes(int N, int H, int W, int C1, int C2, int Cout, int ks) {
     if (N <= 0 || H <= 0 || W <= 0 || C1 <= 0 || C2 < 0 || Cout <= 0 || (ks != 1 && ks != 3)) return 0;
@@ -55,10 +76,17 @@ int mrisr_conv2d_bf16(const void* src1, int C1, const void* src2, int C2, const 
     // forward weight dims: [Cout][Cin] normally; for dgrad the caller passes the FORWARD weight [Cin_here = C1][Cout_here]
     const int wCout = transposed ? C1 : Cout, wCin = transposed ? Cout : Cin;
     ConvArgs<bf16> a;
-    a.src1 = act(src1, N, H, W, C1);
-    a.src2 = src2 ? act(src2, N, H, W, C2) : Act<bf16>{nullptr, 0, 0, 0, 0};
-    a.bias = bias; a.dst = act(dst, N, H, W, Cout); a.stat_part = stats ? sc.part : nullptr; a.ks = ks;
+    a.src1 = act(src1, N, H, W, C1, engine);
+    a.src2 = src2 ? act(src2, N, H, W, C2, engine) : Act<bf16>{nullptr, 0, 0, 0, 0};
+    a.bias = bias; a.dst = act(dst, N, H, W, Cout, engine); a.stat_part = stats ? sc.part : nullptr; a.ks = ks;
     int rc;
+    if (engine == 2) {
+        if ((rc = launch_pack_weights_ring(w, sc.wf, sc.wd, wCout, wCin, ks, s))) return rc;
+        a.w = transposed ? sc.wd : sc.wf;
+        if ((rc = launch_conv_ring(a, s))) return rc;
+        if (stats) return launch_gn_finalize_tc(sc.part, stats, N, H, W, (double)(Cout / kGroups) * H * W, s);
+        return 0;
+    }
     if (engine == 1) {
         if ((rc = launch_pack_weights_tc(w, sc.wf, sc.wd, wCout, wCin, ks, s))) return rc;
         a.w = transposed ? sc.wd : sc.wf;
@@ -80,9 +108,10 @@ int mrisr_conv2d_wgrad_bf16(const void* src1, int C1, const void* src2, int C2, 
     Scratch sc(scratch, N, H, W, C1, src2 ? C2 : 0, Cout, ks);
     if (sc.bytes > scratch_bytes) { set_error("wgrad: scratch too small (%zu > %zu)", sc.bytes, scratch_bytes); return MRISR_E_WORKSPACE; }
     WgradArgs<bf16> a;
-    a.src1 = act(src1, N, H, W, C1);
-    a.src2 = src2 ? act(src2, N, H, W, C2) : Act<bf16>{nullptr, 0, 0, 0, 0};
-    a.dy = act(dy, N, H, W, Cout); a.dw = dw; a.partial = sc.part; a.ks = ks;
+    a.src1 = act(src1, N, H, W, C1, engine);
+    a.src2 = src2 ? act(src2, N, H, W, C2, engine) : Act<bf16>{nullptr, 0, 0, 0, 0};
+    a.dy = act(dy, N, H, W, Cout, engine); a.dw = dw; a.partial = sc.part; a.ks = ks;
+    if (engine == 2) return launch_wgrad_ring(a, s);
     return engine == 1 ? launch_wgrad_tc(a, s) : launch_wgrad_generic<bf16>(a, s);
 }
 

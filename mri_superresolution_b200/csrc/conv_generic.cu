@@ -46,10 +46,10 @@ __global__ void __launch_bounds__(NTHR) conv_generic_kernel(ConvArgs<T> a) {
             for (int k = 0; k < 8; ++k) v[k] = 0.f;
             if (y <= H && x <= W) {
                 if (Cin >= 8) {
-                    if (c0 < C1) load8(a.src1.p + a.src1.off(n, y, x) + c0, v);
-                    else load8(a.src2.p + a.src2.off(n, y, x) + (c0 - C1), v);
+                    if (c0 < C1) load8(a.src1.at(n, y, x, c0), v);
+                    else load8(a.src2.at(n, y, x, (c0 - C1)), v);
                 } else {
-                    for (int k = 0; k < Cin; ++k) v[k] = to_f(a.src1.p[a.src1.off(n, y, x) + k]);
+                    for (int k = 0; k < Cin; ++k) v[k] = to_f(*a.src1.at(n, y, x, k));
                 }
             }
 #pragma unroll
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(NTHR) conv_generic_kernel(ConvArgs<T> a) {
         const int p = pt + j * NPT;
         const int y = ty0 + p / TW, x = tx0 + p % TW;
         if (y < H && x < W) {
-            T* o = a.dst.p + a.dst.off(n, y, x) + cbase + ct * 4;
+            T* o = a.dst.at(n, y, x, cbase + ct * 4);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float v = acc[j][k] + b4[k];

@@ -40,10 +40,10 @@ __global__ void __launch_bounds__(NTHR) wgrad_generic_kernel(WgradArgs<T> a, int
             for (int k = 0; k < 8; ++k) v[k] = 0.f;
             if (y <= H && x <= W) {
                 if (Cin >= 8) {
-                    if (ci0 < C1) load8(a.src1.p + a.src1.off(n, y, x) + ci0, v);
-                    else load8(a.src2.p + a.src2.off(n, y, x) + (ci0 - C1), v);
+                    if (ci0 < C1) load8(a.src1.at(n, y, x, ci0), v);
+                    else load8(a.src2.at(n, y, x, (ci0 - C1)), v);
                 } else {
-                    for (int k = 0; k < Cin; ++k) v[k] = to_f(a.src1.p[a.src1.off(n, y, x) + k]);
+                    for (int k = 0; k < Cin; ++k) v[k] = to_f(*a.src1.at(n, y, x, k));
                 }
             }
 #pragma unroll
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(NTHR) wgrad_generic_kernel(WgradArgs<T> a, int
             float v[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = 0.f;
-            if (y < H && x < W && co0 + cv * 8 < Cout) load8(a.dy.p + a.dy.off(n, y, x) + co0 + cv * 8, v);
+            if (y < H && x < W && co0 + cv * 8 < Cout) load8(a.dy.at(n, y, x, co0 + cv * 8), v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) s_dy[p][cv * 8 + k] = v[k];
         }

@@ -43,7 +43,7 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
     for (int q = 0; q < P; ++q) {
         const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
         float v[8];
-        load8(a.r.p + a.r.off(n, y, x) + cv * 8, v);
+        load8(a.r.at(n, y, x, cv * 8), v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             xh[q][k] = (v[k] - c.mean[k]) * c.rstd[k];
@@ -51,10 +51,10 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
         }
         float dA[8];
         if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
-            load8(a.g.p + a.g.off(n, y, x) + a.coff + cv * 8, dA);
+            load8(a.g.at(n, y, x, a.coff + cv * 8), dA);
         } else if (KIND == SRC_BLEND_BIL) {
             const float al = 1.f / (1.f + __expf(-a.alpha[0]));
-            load8(a.g.p + a.g.off(n, y, x) + cv * 8, dA);
+            load8(a.g.at(n, y, x, cv * 8), dA);
 #pragma unroll
             for (int k = 0; k < 8; ++k) dA[k] *= al;
         } else if (KIND == SRC_BLEND_PS) {
@@ -62,7 +62,7 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const int ch = cv * 8 + k, cs = ch >> 2, i = (ch >> 1) & 1, j = ch & 1;
-                dA[k] = om * to_f(a.g.p[a.g.off(n, 2 * y + i, 2 * x + j) + cs]);
+                dA[k] = om * to_f(*a.g.at(n, 2 * y + i, 2 * x + j, cs));
             }
         } else if (KIND == SRC_OUTER) {
             const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
@@ -85,7 +85,7 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
         // route the pooled gradient to the first maximum in scan order (ATen max_pool2d uses '>'),
         // comparing the activations as stored by the forward pass (rounded to T)
         float gp[8];
-        load8(a.gpool.p + a.gpool.off(n, uy, ux) + cv * 8, gp);
+        load8(a.gpool.at(n, uy, ux, cv * 8), gp);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             int best = 0;
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a) {
             float o[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) o[k] = c.rstd[k] * (c.gam[k] * dz[q][k] - m1[k] - xh[q][k] * m2[k]);
-            store8(a.dr.p + a.dr.off(n, y, x) + cv * 8, o);
+            store8(a.dr.at(n, y, x, cv * 8), o);
         }
     }
 }

@@ -15,7 +15,7 @@ __device__ __forceinline__ void branch_values(const BlendArgs<T>& a, int n, int 
                                               float (&xp)[8]) {
     const int Ch = a.r_bil.C, gsb = Ch / kGroups;          // Ch >= 8
     float v[8];
-    load8(a.r_bil.p + a.r_bil.off(n, Y, X) + cv * 8, v);
+    load8(a.r_bil.at(n, Y, X, cv * 8), v);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const int c = cv * 8 + k, g = c / gsb;
@@ -25,12 +25,11 @@ __device__ __forceinline__ void branch_values(const BlendArgs<T>& a, int n, int 
     // PixelShuffle(2): shuffled[n, c, 2y+i, 2x+j] = raw[n, 4c+2i+j, y, x]   (models/unet_model.py:102,111)
     const int y = Y >> 1, x = X >> 1, ij = ((Y & 1) << 1) | (X & 1);
     const int Craw = a.r_ps.C, gsp = Craw / kGroups;
-    const T* rp = a.r_ps.p + a.r_ps.off(n, y, x);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const int c = cv * 8 + k, craw = 4 * c + ij, g = craw / gsp;
         const float mean = a.st_ps[(n * kGroups + g) * 2], rstd = a.st_ps[(n * kGroups + g) * 2 + 1];
-        xp[k] = lrelu((to_f(rp[craw]) - mean) * rstd * a.g_ps[c] + a.b_ps[c]);
+        xp[k] = lrelu((to_f(*a.r_ps.at(n, y, x, craw)) - mean) * rstd * a.g_ps[c] + a.b_ps[c]);
     }
 }
 
@@ -47,7 +46,7 @@ __global__ void __launch_bounds__(NTHR) head_blend_kernel(BlendArgs<T> a) {
         branch_values(a, n, Y, X, cv, xb, xp);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[k] = al * xb[k] + (1.f - al) * xp[k];
-        store8(a.xm.p + a.xm.off(n, Y, X) + cv * 8, o);
+        store8(a.xm.at(n, Y, X, cv * 8), o);
     }
 }
 
@@ -63,7 +62,7 @@ __global__ void __launch_bounds__(NTHR) blend_dalpha_kernel(BlendArgs<T> a, Act<
         const int n = (int)(i / ((int64_t)nv * a.xm.W * a.xm.H));
         float xb[8], xp[8], g[8];
         branch_values(a, n, Y, X, cv, xb, xp);
-        load8(dxm.p + dxm.off(n, Y, X) + cv * 8, g);
+        load8(dxm.at(n, Y, X, cv * 8), g);
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc = fmaf(g[k], xb[k] - xp[k], acc);
     }
@@ -100,11 +99,10 @@ __global__ void __launch_bounds__(NTHR) final_head_kernel(Act<T> r, const float*
     const int64_t total = (int64_t)r.N * r.H * r.W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int X = (int)(i % r.W), Y = (int)((i / r.W) % r.H), n = (int)(i / ((int64_t)r.W * r.H));
-        const T* rp = r.p + r.off(n, Y, X);
         float acc = b1x1[0];
         for (int cv = 0; cv < nv; ++cv) {
             float v[8];
-            load8(rp + cv * 8, v);
+            load8(r.at(n, Y, X, cv * 8), v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const int c = cv * 8 + k, g = c / gs;
@@ -129,7 +127,7 @@ __global__ void __launch_bounds__(NTHR) colsum_kernel(Act<T> t, float* __restric
         const int p_end = min(HW, (int)(blockIdx.x + 1) * pix_per_block);
         for (int p = blockIdx.x * pix_per_block + pl; p < p_end; p += PL) {
             float v[8];
-            load8(t.p + t.off(n, p / t.W, p % t.W) + cv * 8, v);
+            load8(t.at(n, p / t.W, p % t.W, cv * 8), v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) s1[k] += v[k];
         }

@@ -42,6 +42,13 @@ int conv_tc_stat_elems(int N, int H, int W);
 int launch_conv_tc(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s);
 int launch_gn_finalize_tc(const float* part, float* stats, int N, int H, int W, double count, cudaStream_t s);
 int launch_pack_weights_tc(const float* w, __nv_bfloat16* wf, __nv_bfloat16* wd, int Cout, int Cin, int ks, cudaStream_t s);
+// planar-8 sliding-window kernels for narrow high-resolution layers (conv_ring.cu); weights packed by launch_pack_weights_ring
+bool conv_ring_supported(int H, int W, int C1, int C2, int Cout, int ks);
+int launch_conv_ring(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s);
+int launch_pack_weights_ring(const float* w, __nv_bfloat16* wf, __nv_bfloat16* wd, int Cout, int Cin, int ks, cudaStream_t s);
+bool wgrad_ring_supported(int H, int W, int C1, int C2, int Cout, int ks);
+size_t wgrad_ring_scratch_elems(int N, int H, int W, int Cin, int Cout, int ks);
+int launch_wgrad_ring(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
 bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks);
 size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks);
 int launch_wgrad_tc(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);

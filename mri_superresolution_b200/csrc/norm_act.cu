@@ -13,7 +13,7 @@ __global__ void pack_input_kernel(const float* __restrict__ x, Act<T> dst) {
     const int64_t total = (int64_t)dst.N * dst.H * dst.W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int xx = (int)(i % dst.W), yy = (int)((i / dst.W) % dst.H), n = (int)(i / ((int64_t)dst.W * dst.H));
-        dst.p[dst.off(n, yy, xx)] = from_f<T>(x[i]);
+        *dst.at(n, yy, xx, 0) = from_f<T>(x[i]);
     }
 }
 
@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(NTHR) gn_stats_kernel(Act<T> r, float* __restr
         const int p_end = min(HW, (int)(blockIdx.x + 1) * pix_per_block);
         for (int p = blockIdx.x * pix_per_block + pl; p < p_end; p += PL) {
             float v[8];
-            load8(r.p + r.off(n, p / r.W, p % r.W) + cv * 8, v);
+            load8(r.at(n, p / r.W, p % r.W, cv * 8), v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) { s1[k] += v[k]; s2[k] += v[k] * v[k]; }
         }
@@ -99,20 +99,20 @@ __global__ void __launch_bounds__(NTHR) gn_apply_kernel(Act<T> r, const float* _
         }
         if (!POOL) {
             float v[8];
-            load8(r.p + r.off(n, wy, wx) + cv * 8, v);
+            load8(r.at(n, wy, wx, cv * 8), v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-            store8(a.p + a.off(n, wy, wx) + cv * 8, v);
+            store8(a.at(n, wy, wx, cv * 8), v);
         } else {
             float m[8];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int y = 2 * wy + (q >> 1), x = 2 * wx + (q & 1);
                 float v[8];
-                load8(r.p + r.off(n, y, x) + cv * 8, v);
+                load8(r.at(n, y, x, cv * 8), v);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-                store8(a.p + a.off(n, y, x) + cv * 8, v);
+                store8(a.at(n, y, x, cv * 8), v);
                 // max over the values as stored (rounded to T) so backward's argmax recomputation agrees
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(NTHR) gn_apply_kernel(Act<T> r, const float* _
                     m[k] = q == 0 ? vr : fmaxf(m[k], vr);
                 }
             }
-            store8(pooled.p + pooled.off(n, wy, wx) + cv * 8, m);
+            store8(pooled.at(n, wy, wx, cv * 8), m);
         }
     }
 }
@@ -136,14 +136,14 @@ __global__ void __launch_bounds__(NTHR) upsample2x_kernel(Act<T> src, Act<T> dst
         const int n = (int)(i / ((int64_t)nv * dst.W * dst.H));
         const Lerp ly = up_coord(Y, src.H, sy), lx = up_coord(X, src.W, sx);
         float v00[8], v01[8], v10[8], v11[8], o[8];
-        load8(src.p + src.off(n, ly.i0, lx.i0) + cv * 8, v00);
-        load8(src.p + src.off(n, ly.i0, lx.i1) + cv * 8, v01);
-        load8(src.p + src.off(n, ly.i1, lx.i0) + cv * 8, v10);
-        load8(src.p + src.off(n, ly.i1, lx.i1) + cv * 8, v11);
+        load8(src.at(n, ly.i0, lx.i0, cv * 8), v00);
+        load8(src.at(n, ly.i0, lx.i1, cv * 8), v01);
+        load8(src.at(n, ly.i1, lx.i0, cv * 8), v10);
+        load8(src.at(n, ly.i1, lx.i1, cv * 8), v11);
         const float h1 = ly.w1, h0 = 1.f - h1, w1 = lx.w1, w0 = 1.f - w1;
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[k] = h0 * (w0 * v00[k] + w1 * v01[k]) + h1 * (w0 * v10[k] + w1 * v11[k]);
-        store8(dst.p + dst.off(n, Y, X) + cv * 8, o);
+        store8(dst.at(n, Y, X, cv * 8), o);
     }
 }
 
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T
         float acc[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-        if (addend.p) load8(addend.p + addend.off(n, y, x) + cv * 8, acc);
+        if (addend.p) load8(addend.at(n, y, x, cv * 8), acc);
         int ylo, yhi, xlo, xhi;
         adj_range(y, dsrc.H, sy, ylo, yhi);
         adj_range(x, dsrc.W, sx, xlo, xhi);
@@ -184,12 +184,12 @@ __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T
                 const float w = wy * adj_weight(X, x, dsrc.W, sx);
                 if (w == 0.f) continue;
                 float v[8];
-                load8(ddst.p + ddst.off(n, Y, X) + cv * 8, v);
+                load8(ddst.at(n, Y, X, cv * 8), v);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
             }
         }
-        store8(dsrc.p + dsrc.off(n, y, x) + cv * 8, acc);
+        store8(dsrc.at(n, y, x, cv * 8), acc);
     }
 }
 

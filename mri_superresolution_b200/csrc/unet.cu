@@ -54,10 +54,21 @@ template <typename T>
 Act<T> Workspace<T>::make_act(Arena& ar, int lvl, int C) {
     Act<T> a;
     a.N = N; a.H = lvl_dim(H, lvl); a.W = lvl_dim(W, lvl); a.C = C;
-    // guard on both sides: the tcgen05 kernels read whole 128-pixel tiles shifted by up to one padded row + 1
+    if (planar_level(lvl) && sizeof(T) == 2 && C >= 16 && C % 8 == 0) {
+        // planar-8: C/8 planes of [guard | N*S pixels rounded to 128 | guard] x 8 channels.  The guards are only ever READ
+        // (the ring kernels fetch whole 128-pixel blocks around a tile, conv_ring.cu); what they hold is irrelevant
+        // because only border outputs depend on them and those are never stored.
+        const int64_t guard = planar_guard(a.W);
+        const int64_t plane = planar_plane(a.rows(), a.W);
+        T* p = (T*)ar.take((size_t)plane * C * sizeof(T));
+        a.ps = 8; a.cs = plane * 8;
+        a.p = p ? p + guard * 8 : nullptr;
+        return a;
+    }
     const size_t guard = (((size_t)(a.W + 2) + 2 + 128) * C + 127) & ~(size_t)127;
-    const size_t elems = (size_t)a.sample_stride() * N + 2 * guard;
+    const size_t elems = (size_t)a.rows() * C + 2 * guard;
     T* p = (T*)ar.take(elems * sizeof(T));
+    a.ps = C; a.cs = 8;
     a.p = p ? p + guard : nullptr;
     return a;
 }
@@ -87,10 +98,12 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         part_max = std::max(part_max, (size_t)conv_tc_stat_elems(N, h, w));
         gnp_max = std::max(gnp_max, (size_t)N * gn_bwd_slots(h, w, c.cout) * 3 * (c.cout + 8));
         wg_max = std::max(wg_max, wgrad_generic_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
-        if (sizeof(T) == 2 && layer_uses_tc(c, l, H, W)) {
+        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_TC) {
             const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin;
             wg_max = std::max(wg_max, wgrad_tc_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c1, c.cin - c1, c.cout, c.ks));
         }
+        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_RING)
+            wg_max = std::max(wg_max, wgrad_ring_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
     }
     UB = make_act(ar, -1, f);
     XM = make_act(ar, -1, f / 2);

@@ -23,15 +23,25 @@ struct ConvDesc {
 void conv_table(int f, ConvDesc (&t)[kNumConv]);
 
 inline int lvl_dim(int d, int lvl) { return lvl < 0 ? 2 * d : d >> lvl; }
+// resolution levels whose bf16 tensors use the planar-8 layout (full resolution and the 2x head)
+inline bool planar_level(int lvl) { return lvl <= 0; }
 inline bool is_concat_conv(int l) { return l == 9 || l == 12 || l == 15; }   // DoubleConv fed by cat([skip, up])
 // bf16 mode: does conv l (forward, data gradient and weight gradient) run on the tcgen05 kernels at input size HxW?
-inline bool layer_uses_tc(const ConvDesc& c, int l, int H, int W) {
+// ENG_TC: NHWC + TMA + swizzled tcgen05 (conv_tc.cu / wgrad_tc.cu), levels >= 1.
+// ENG_RING: planar-8 sliding-window tcgen05 (conv_ring.cu / wgrad_ring.cu), the narrow layers at levels <= 0.
+enum Engine : int { ENG_GENERIC = 0, ENG_TC = 1, ENG_RING = 2 };
+inline int layer_engine(const ConvDesc& c, int l, int H, int W) {
     static const bool disabled = getenv("MRISR_DEBUG_NO_TC") != nullptr;   // debugging aid: all layers on CUDA cores
-    if (disabled) return false;
+    if (disabled) return ENG_GENERIC;
     const int h = lvl_dim(H, c.lvl), w = lvl_dim(W, c.lvl);
     const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin, c2 = c.cin - c1;
+    if (planar_level(c.lvl)) {
+        const bool planar_ok = c1 >= 16 && (c2 == 0 || c2 >= 16) && c.cout >= 16;     // C = 8 tensors stay NHWC
+        return planar_ok && conv_ring_supported(h, w, c1, c2, c.cout, c.ks) && conv_ring_supported(h, w, c.cout, 0, c.cin, c.ks) &&
+                       wgrad_ring_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_RING : ENG_GENERIC;
+    }
     return conv_tc_supported(h, w, c1, c2, c.cout, c.ks) && conv_tc_supported(h, w, c.cout, 0, c.cin, c.ks) &&
-           wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks);
+                   wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_TC : ENG_GENERIC;
 }
 
 // Bump allocator over the caller's workspace (base == nullptr -> size query only).

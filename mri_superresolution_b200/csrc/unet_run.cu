@@ -15,7 +15,7 @@ struct Runner {
     const float* params;
     cudaStream_t s;
     const float* P(int idx) const { return params + pl.off[idx]; }
-    bool tc(int l) const { return sizeof(T) == 2 && layer_uses_tc(ws.conv[l], l, ws.H, ws.W); }
+    int eng(int l) const { return sizeof(T) == 2 ? layer_engine(ws.conv[l], l, ws.H, ws.W) : (int)ENG_GENERIC; }
 
     // conv l: (src1 [, src2]) -> dst, GroupNorm partial statistics when `stats`
     int conv(int l, Act<T> src1, Act<T> src2, Act<T> dst, bool want_stats) {
@@ -25,8 +25,8 @@ struct Runner {
         a.bias = c.bias >= 0 ? P(c.bias) : nullptr;
         a.dst = dst; a.stat_part = want_stats ? ws.stat_part : nullptr; a.ks = c.ks;
         if constexpr (sizeof(T) == 2) {
-            if (tc(l)) {
-                TRY(launch_conv_tc(a, s));
+            if (eng(l) != ENG_GENERIC) {
+                TRY(eng(l) == ENG_RING ? launch_conv_ring(a, s) : launch_conv_tc(a, s));
                 if (want_stats) TRY(launch_gn_finalize_tc(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W,
                                                           (double)(dst.C / kGroups) * dst.H * dst.W, s));
                 return 0;
@@ -73,8 +73,9 @@ struct Runner {
         for (int l = 0; l < kNumConv; ++l) {
             const ConvDesc& c = ws.conv[l];
             if constexpr (sizeof(T) == 2) {
-                if (tc(l)) {
-                    TRY(launch_pack_weights_tc(P(c.w), ws.wf[l], train && l > 0 ? ws.wd[l] : nullptr, c.cout, c.cin, c.ks, s));
+                if (eng(l) != ENG_GENERIC) {
+                    TRY((eng(l) == ENG_RING ? launch_pack_weights_ring : launch_pack_weights_tc)(
+                        P(c.w), ws.wf[l], train && l > 0 ? ws.wd[l] : nullptr, c.cout, c.cin, c.ks, s));
                     continue;
                 }
             }
@@ -127,17 +128,17 @@ struct Runner {
         const Act<T> none{nullptr, 0, 0, 0, 0};
         WgradArgs<T> w;
         w.src1 = src1; w.src2 = src2; w.dy = dy; w.dw = GP(c.w); w.partial = ws.wg_part; w.ks = c.ks;
-        bool use_tc = false;
-        if constexpr (sizeof(T) == 2) use_tc = tc(l);
+        const int e = eng(l);
+        const bool use_tc = e != ENG_GENERIC;
         if constexpr (sizeof(T) == 2) {
-            if (use_tc) TRY(launch_wgrad_tc(w, s));
+            if (use_tc) TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s));
         }
         if (!use_tc) TRY(launch_wgrad_generic<T>(w, s));
         if (want_dgrad) {
             ConvArgs<T> a;
             a.src1 = dy; a.src2 = none; a.w = ws.wd[l]; a.bias = nullptr; a.dst = ws.G[l]; a.stat_part = nullptr; a.ks = c.ks;
             if constexpr (sizeof(T) == 2) {
-                if (use_tc) TRY(launch_conv_tc(a, s));
+                if (use_tc) TRY(e == ENG_RING ? launch_conv_ring(a, s) : launch_conv_tc(a, s));
             }
             if (!use_tc) TRY(launch_conv_generic<T>(a, s));
         }
@@ -221,7 +222,7 @@ __global__ void unpack_act_kernel(Act<T> a, float* __restrict__ out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int x = (int)(i % a.W), y = (int)((i / a.W) % a.H);
         const int c = (int)((i / ((int64_t)a.W * a.H)) % a.C), n = (int)(i / ((int64_t)a.W * a.H * a.C));
-        out[i] = to_f(a.p[a.off(n, y, x) + c]);
+        out[i] = to_f(*a.at(n, y, x, c));
     }
 }
 

@@ -29,6 +29,31 @@ def unpad_nchw(p):
     return p[:, 1:-1, 1:-1, :].permute(0, 3, 1, 2).float().contiguous()
 
 
+def planar_geometry(n, h, w):
+    g, pl = ctypes.c_longlong(), ctypes.c_longlong()
+    _native.check(_native.lib().mrisr_planar_geometry(n, h, w, ctypes.addressof(g), ctypes.addressof(pl)), "planar_geometry")
+    return g.value, pl.value
+
+
+def to_planar(x, fill_guard=True):
+    """NCHW fp32 -> planar-8 allocation [C/8][plane][8] bf16 (engine 2); guards hold junk on purpose."""
+    n, c, h, w = x.shape
+    guard, plane = planar_geometry(n, h, w)
+    rows = n * (h + 2) * (w + 2)
+    out = torch.zeros(c // 8, plane, 8, dtype=torch.bfloat16, device=x.device)
+    if fill_guard:
+        out[:, :guard] = 37.0
+        out[:, guard + rows:] = -53.0
+    out[:, guard:guard + rows] = pad_nhwc(x).view(rows, c // 8, 8).permute(1, 0, 2)
+    return out.contiguous()
+
+
+def from_planar(p, n, c, h, w):
+    guard, plane = planar_geometry(n, h, w)
+    rows = n * (h + 2) * (w + 2)
+    return p[:, guard:guard + rows].permute(1, 0, 2).reshape(n, h + 2, w + 2, c)
+
+
 def rel_inf(a, b):
     return float((a.double() - b.double()).abs().max() / max(float(b.double().abs().max()), 1e-30))
 
@@ -39,15 +64,22 @@ def run_conv(x1, x2, w, bias, cout, ks, engine, want_stats, transposed=False):
     c2 = x2.shape[1] if x2 is not None else 0
     sb = L.mrisr_conv2d_scratch_bytes(n, h, wd, c1, c2, cout, ks)
     scratch = torch.empty(sb, dtype=torch.uint8, device=x1.device)
-    p1 = pad_nhwc(x1)
-    p2 = pad_nhwc(x2) if x2 is not None else None
-    dst = torch.zeros(n, h + 2, wd + 2, cout, dtype=torch.bfloat16, device=x1.device)
+    if engine == 2:
+        p1 = to_planar(x1)
+        p2 = to_planar(x2) if x2 is not None else None
+        dst = to_planar(torch.zeros(n, cout, h, wd, device=x1.device), fill_guard=False)
+    else:
+        p1 = pad_nhwc(x1)
+        p2 = pad_nhwc(x2) if x2 is not None else None
+        dst = torch.zeros(n, h + 2, wd + 2, cout, dtype=torch.bfloat16, device=x1.device)
     stats = torch.zeros(n, 8, 2, device=x1.device) if want_stats else None
     rc = L.mrisr_conv2d_bf16(_native.ptr(p1), c1, _native.ptr(p2), c2, _native.ptr(w), _native.ptr(bias), _native.ptr(dst),
                              _native.ptr(stats), _native.ptr(scratch), sb, n, h, wd, cout, ks, 1 if transposed else 0,
                              engine, _native.stream_ptr())
     _native.check(rc, "conv2d")
     torch.cuda.synchronize()
+    if engine == 2:
+        dst = from_planar(dst, n, cout, h, wd).contiguous()
     border = dst.clone()
     border[:, 1:-1, 1:-1, :] = 0
     assert float(border.float().abs().max()) == 0.0, "border pixels were written"
@@ -61,7 +93,10 @@ def run_wgrad(x1, x2, dy, ks, engine):
     cout = dy.shape[1]
     sb = L.mrisr_conv2d_scratch_bytes(n, h, wd, c1, c2, cout, ks)
     scratch = torch.empty(sb, dtype=torch.uint8, device=x1.device)
-    p1, p2, pdy = pad_nhwc(x1), (pad_nhwc(x2) if x2 is not None else None), pad_nhwc(dy)
+    conv = to_planar if engine == 2 else pad_nhwc
+    p1, p2 = conv(x1), (conv(x2) if x2 is not None else None)
+    # the reduction runs over whole 128-pixel blocks: dY must be zero on its border AND in its guard pixels
+    pdy = to_planar(dy, fill_guard=False) if engine == 2 else pad_nhwc(dy)
     dw = torch.zeros(cout, c1 + c2, ks, ks, device=x1.device)
     rc = L.mrisr_conv2d_wgrad_bf16(_native.ptr(p1), c1, _native.ptr(p2), c2, _native.ptr(pdy), _native.ptr(dw),
                                    _native.ptr(scratch), sb, n, h, wd, cout, ks, engine, _native.stream_ptr())
@@ -142,3 +177,68 @@ def test_conv_wgrad_engines(shape):
         dw = run_wgrad(x1, x2, dy, ks, engine)
         e = rel_inf(dw, ref)
         assert e < 2e-3, (engine, shape, e)
+
+
+# planar-8 sliding-window engine (narrow layers): (N, H, W, C1, C2, Cout, ks, bias)
+RING_SHAPES = [
+    (2, 16, 16, 16, 0, 16, 3, False),
+    (3, 24, 40, 32, 0, 32, 3, False),
+    (2, 40, 24, 32, 32, 32, 3, False),      # skip-concat
+    (2, 32, 32, 32, 0, 64, 3, True),        # pixel-shuffle conv shape, bias
+    (2, 48, 48, 32, 0, 16, 3, False),
+    (1, 128, 128, 16, 0, 16, 3, False),     # long tile runs: ring wraps several times
+    (2, 64, 64, 64, 0, 32, 3, False),
+    (2, 32, 32, 32, 0, 32, 1, False),
+    (5, 32, 16, 48, 16, 64, 3, False),
+]
+
+
+@pytest.mark.parametrize("shape", RING_SHAPES)
+def test_conv_ring_forward(shape):
+    n, h, w, c1, c2, cout, ks, use_bias = shape
+    g = torch.Generator("cpu").manual_seed(3 + hash(shape) % 1000)
+    x1 = torch.randn(n, c1, h, w, generator=g).to(_dev())
+    x2 = torch.randn(n, c2, h, w, generator=g).to(_dev()) if c2 else None
+    wt = (torch.randn(cout, c1 + c2, ks, ks, generator=g) / (3.0 * (c1 + c2) ** 0.5)).to(_dev())
+    bias = torch.randn(cout, generator=g).to(_dev()) if use_bias else None
+    xin = bf(x1) if x2 is None else torch.cat([bf(x1), bf(x2)], 1)
+    ref = F.conv2d(xin.double(), bf(wt).double(), bias.double() if use_bias else None, padding=ks // 2).float()
+    rg = ref.view(n, 8, (cout // 8) * h * w).double()
+    ref_mean, ref_rstd = rg.mean(2), 1.0 / torch.sqrt(rg.var(2, unbiased=False) + 1e-5)
+    out, stats = run_conv(x1, x2, wt, bias, cout, ks, 2, True)
+    e = rel_inf(out, ref)
+    assert e < 6e-3, (shape, e)
+    assert rel_inf(stats[:, :, 0], ref_mean.float()) < 2e-3 or float((stats[:, :, 0] - ref_mean.float()).abs().max()) < 2e-4, shape
+    assert rel_inf(stats[:, :, 1], ref_rstd.float()) < 2e-3, shape
+
+
+@pytest.mark.parametrize("shape", RING_SHAPES)
+def test_conv_ring_dgrad(shape):
+    n, h, w, c1, c2, cout, ks, _ = shape
+    cin = c1 + c2
+    if cin not in (16, 32, 64) or cout % 16:
+        pytest.skip("dgrad output width must be a supported Cout")
+    g = torch.Generator("cpu").manual_seed(5 + hash(shape) % 1000)
+    dy = torch.randn(n, cout, h, w, generator=g).to(_dev())
+    wt = (torch.randn(cout, cin, ks, ks, generator=g) / (3.0 * cout ** 0.5)).to(_dev())
+    ref = F.conv_transpose2d(bf(dy).double(), bf(wt).double(), padding=ks // 2).float()
+    out, _ = run_conv(dy, None, wt, None, cin, ks, 2, False, transposed=True)
+    e = rel_inf(out, ref)
+    assert e < 6e-3, (shape, e)
+
+
+@pytest.mark.parametrize("shape", RING_SHAPES)
+def test_conv_ring_wgrad(shape):
+    n, h, w, c1, c2, cout, ks, _ = shape
+    if cout == 64 and c1 + c2 == 64:
+        pytest.skip("no such layer at full resolution (N side would need 64 columns per tap)")
+    g = torch.Generator("cpu").manual_seed(9 + hash(shape) % 1000)
+    x1 = torch.randn(n, c1, h, w, generator=g).to(_dev())
+    x2 = torch.randn(n, c2, h, w, generator=g).to(_dev()) if c2 else None
+    dy = torch.randn(n, cout, h, w, generator=g).to(_dev())
+    xin = (bf(x1) if x2 is None else torch.cat([bf(x1), bf(x2)], 1)).double()
+    wref = torch.zeros(cout, c1 + c2, ks, ks, dtype=torch.float64, device=_dev(), requires_grad=True)
+    F.conv2d(xin, wref, None, padding=ks // 2).backward(bf(dy).double())
+    dw = run_wgrad(x1, x2, dy, ks, 2)
+    e = rel_inf(dw, wref.grad.float())
+    assert e < 2e-3, (shape, e)
