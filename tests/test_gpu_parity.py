@@ -184,7 +184,13 @@ def test_unet_bf16_matches_golden(golden_dir, name):
         if r.numel() > 1 and float(r.norm()) > 1e-3 * gmax:
             cos = float((g * r).sum() / (g.norm() * r.norm() + 1e-30))
             assert cos > 0.9, (k, cos)
-        assert abs(float(g.norm()) - float(r.norm())) < 0.15 * float(r.norm()) + 2e-3 * gmax, k
+        tol = 0.15 * float(r.norm()) + 2e-3 * gmax
+        if r.numel() == 1 and ("grad:" + k) in d.files:
+            # alpha's gradient is a sum of (xb - xp) * g over every output pixel: cancellation leaves a value far below
+            # its terms, so bf16 operand rounding moves it by more than its own size.  Measure that floor as the distance
+            # between the bf16-storage restatement and the fp32 golden gradient and allow 2x of it.
+            tol += 2.0 * abs(float(r) - float(d["grad:" + k]))
+        assert abs(float(g.norm() if r.numel() > 1 else g) - float(r.norm() if r.numel() > 1 else r)) < tol, k
 
 
 def test_inference_matches_training_forward_and_clamp(golden_dir):
