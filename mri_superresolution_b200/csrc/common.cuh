@@ -68,8 +68,9 @@ struct Act {
 };
 
 // planar-8 geometry: pixels of guard on each side of a plane and pixels per plane (rows = N*(H+2)*(W+2))
-inline int64_t planar_guard(int W) { return (((int64_t)W + 4 + 127) / 128) * 128 + 128; }
-inline int64_t planar_plane(int64_t rows, int W) { return ((rows + 127) / 128) * 128 + 2 * planar_guard(W); }
+// (sized so that the ring kernels may fetch whole 256-pixel blocks around every tile without leaving the allocation)
+inline int64_t planar_guard(int W) { return (((int64_t)W + 4 + 255) / 256) * 256 + 256; }
+inline int64_t planar_plane(int64_t rows, int W) { return ((rows + 255) / 256) * 256 + 2 * planar_guard(W); }
 
 __device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : kSlope * z; }
 __device__ __forceinline__ float lrelu_grad(float z) { return z > 0.f ? 1.f : kSlope; }

@@ -22,6 +22,7 @@ struct Scratch {
         wd = (bf16*)c.take(wel * sizeof(bf16));
         size_t pe = (size_t)N * conv_generic_stat_slots(H, W, Cout) * kGroups * 2;
         pe = pe > (size_t)conv_tc_stat_elems(N, H, W) ? pe : (size_t)conv_tc_stat_elems(N, H, W);
+        pe = pe > (size_t)conv_ring_stat_elems(N, H, W, C1 + C2, Cout) ? pe : (size_t)conv_ring_stat_elems(N, H, W, C1 + C2, Cout);
         size_t we = wgrad_generic_scratch_elems(N, H, W, C1 + C2, Cout, ks);
         if (wgrad_tc_supported(H, W, C1, C2, Cout, ks)) {
             const size_t t = wgrad_tc_scratch_elems(N, H, W, C1, C2, Cout, ks);
@@ -84,7 +85,7 @@ int mrisr_conv2d_bf16(const void* src1, int C1, const void* src2, int C2, const 
         if ((rc = launch_pack_weights_ring(w, sc.wf, sc.wd, wCout, wCin, ks, s))) return rc;
         a.w = transposed ? sc.wd : sc.wf;
         if ((rc = launch_conv_ring(a, s))) return rc;
-        if (stats) return launch_gn_finalize_tc(sc.part, stats, N, H, W, (double)(Cout / kGroups) * H * W, s);
+        if (stats) return launch_gn_finalize_ring(sc.part, stats, N, H, W, Cin, Cout, (double)(Cout / kGroups) * H * W, s);
         return 0;
     }
     if (engine == 1) {

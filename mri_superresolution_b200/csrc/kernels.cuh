@@ -45,6 +45,10 @@ int launch_pack_weights_tc(const float* w, __nv_bfloat16* wf, __nv_bfloat16* wd,
 // planar-8 sliding-window kernels for narrow high-resolution layers (conv_ring.cu); weights packed by launch_pack_weights_ring
 bool conv_ring_supported(int H, int W, int C1, int C2, int Cout, int ks);
 int launch_conv_ring(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s);
+// launch_conv_ring writes per-warp statistics records (conv_ring_stat_elems floats) into ConvArgs::stat_part;
+// launch_gn_finalize_ring turns them into [N][8][2] (mean, rstd)
+int conv_ring_stat_elems(int N, int H, int W, int Cin, int Cout);
+int launch_gn_finalize_ring(const float* rec, float* stats, int N, int H, int W, int Cin, int Cout, double count, cudaStream_t s);
 int launch_pack_weights_ring(const float* w, __nv_bfloat16* wf, __nv_bfloat16* wd, int Cout, int Cin, int ks, cudaStream_t s);
 bool wgrad_ring_supported(int H, int W, int C1, int C2, int Cout, int ks);
 size_t wgrad_ring_scratch_elems(int N, int H, int W, int Cin, int Cout, int ks);

@@ -26,9 +26,14 @@ struct Runner {
         a.dst = dst; a.stat_part = want_stats ? ws.stat_part : nullptr; a.ks = c.ks;
         if constexpr (sizeof(T) == 2) {
             if (eng(l) != ENG_GENERIC) {
-                TRY(eng(l) == ENG_RING ? launch_conv_ring(a, s) : launch_conv_tc(a, s));
-                if (want_stats) TRY(launch_gn_finalize_tc(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W,
-                                                          (double)(dst.C / kGroups) * dst.H * dst.W, s));
+                const double count = (double)(dst.C / kGroups) * dst.H * dst.W;
+                if (eng(l) == ENG_RING) {
+                    TRY(launch_conv_ring(a, s));
+                    if (want_stats) TRY(launch_gn_finalize_ring(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W, c.cin, c.cout, count, s));
+                } else {
+                    TRY(launch_conv_tc(a, s));
+                    if (want_stats) TRY(launch_gn_finalize_tc(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W, count, s));
+                }
                 return 0;
             }
         }

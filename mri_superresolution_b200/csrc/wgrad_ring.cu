@@ -21,6 +21,34 @@ __device__ __forceinline__ void bulk_load_w(void* smem_dst, const void* gsrc, ui
                  : "memory");
 }
 
+
+__device__ __forceinline__ bool elect_one_w() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+// tcgen05.mma with both descriptors given as (lo, hi) halves
+__device__ __forceinline__ void umma_bf16_lohi2(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                                uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n"
+        ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 constexpr int kWRingMaxSlots = 16;
 constexpr int kDySlots = 3;
 
@@ -33,10 +61,11 @@ struct WgradRingParams {
     int N;                                              // GEMM N
     int taps, pw, num_tiles, tiles_per_cta;
     int R, halo_lo, halo_hi;
+    int sh[9];                                          // halo_lo * 128 + pixel shift of tap t (>= 0)
     uint32_t tmem_cols;
 };
 
-__global__ void __launch_bounds__(192, 1) wgrad_ring_kernel(const WgradRingParams p) {
+__global__ void __launch_bounds__(192, 1) wgrad_ring_kernel(const __grid_constant__ WgradRingParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t full_bar[kWRingMaxSlots];
@@ -106,38 +135,74 @@ __global__ void __launch_bounds__(192, 1) wgrad_ring_kernel(const WgradRingParam
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && t_begin < t_end) {
-            const uint32_t xaddr = smem_u32(xring), daddr = smem_u32(dring);
+        // warp-uniform issue loop, fully unrolled over (K step, tap): a descriptor is one integer add (the mirror slot
+        // covers the 112-pixel reach of the K steps, so only the per-tile tap offsets need the ring wrap)
+        if (t_begin < t_end) {
+            const uint32_t ring_px = (uint32_t)p.R * 128u;
+            const uint32_t x_base = (8u << 16) | (smem_u32(xring) >> 4);          // LBO = 128 B (next 8 pixels)
+            const uint32_t d_base = (8u << 16) | (smem_u32(dring) >> 4);
+            const uint32_t x_hi = (PLSX >> 4) | (1u << 14);                       // SBO = plane stride (next 8 channels)
+            const uint32_t d_hi = (PLSD >> 4) | (1u << 14);
             const uint32_t idesc = make_idesc_bf16(64, p.N, 1, 1);
-            int ready = 0, released = 0, it = 0;
-            for (int tile = t_begin; tile < t_end; ++tile, ++it) {
-                const int need = tile + p.halo_hi - b0;
+            const uint32_t ncol = (uint32_t)p.N;
+            const bool a_is_x = p.a_is_x != 0;
+            uint32_t sh[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) sh[t] = (uint32_t)p.sh[t];
+            const int first_need = p.halo_lo + p.halo_hi;
+            int ready = 0, rslot = 0, eslot = 0, dslot = 0;
+            uint32_t rphase = 0, dphase = 0, tb = 0;
+            const int n_tiles = t_end - t_begin;
+            for (int it = 0; it < n_tiles; ++it) {
+                const int need = it + first_need;
                 while (ready <= need) {
-                    mbar_wait(&full_bar[ready % p.R], (ready / p.R) & 1);
+                    mbar_wait(&full_bar[rslot], rphase);
                     ++ready;
+                    if (++rslot == p.R) { rslot = 0; rphase ^= 1u; }
                 }
-                const int dslot = it % kDySlots;
-                mbar_wait(&dfull_bar[dslot], (it / kDySlots) & 1);
+                mbar_wait(&dfull_bar[dslot], dphase);
                 tc_fence_after_sync();
-                for (int k = 0; k < 8; ++k) {                              // 8 K steps of 16 pixels
-                    const uint32_t d_start = daddr + (uint32_t)dslot * 2048u + (uint32_t)k * 256u;
-                    const uint64_t ddesc = make_smem_desc(d_start, 128u, PLSD, 0u);
-                    for (int tap = 0; tap < p.taps; ++tap) {
-                        const int shift = p.taps == 9 ? (tap / 3 - 1) * p.pw + (tap % 3 - 1) : 0;
-                        const int P0 = (tile - b0) * 128 + k * 16 + shift;
-                        const int jb = P0 >> 7, o = P0 & 127;
-                        const uint32_t x_start = xaddr + (uint32_t)(jb % p.R) * 2048u + (uint32_t)o * 16u;
-                        const uint64_t xdesc = make_smem_desc(x_start, 128u, PLSX, 0u);
+                const bool leader = elect_one_w();
+                uint32_t off[9];
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    off[t] = tb + sh[t];
+                    if (off[t] >= ring_px) off[t] -= ring_px;
+                }
+                const uint32_t dlo0 = d_base + (uint32_t)dslot * 128u;
+                if (!leader) {
+                } else if (p.taps == 9) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {                          // 8 K steps of 16 pixels
+#pragma unroll
+                        for (int tap = 0; tap < 9; ++tap) {
+                            const uint32_t xlo = x_base + off[tap] + (uint32_t)(k * 16);
+                            const uint32_t dlo = dlo0 + (uint32_t)(k * 16);
+                            const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
+                            if (a_is_x) umma_bf16_lohi2(tmem_base + (uint32_t)tap * ncol, xlo, x_hi, dlo, d_hi, idesc, acc);
+                            else umma_bf16_lohi2(tmem_base + (uint32_t)tap * ncol, dlo, d_hi, xlo, x_hi, idesc, acc);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const uint32_t xlo = x_base + off[0] + (uint32_t)(k * 16);
+                        const uint32_t dlo = dlo0 + (uint32_t)(k * 16);
                         const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
-                        if (p.a_is_x) umma_bf16(tmem_base + (uint32_t)(tap * p.N), xdesc, ddesc, idesc, acc);
-                        else umma_bf16(tmem_base + (uint32_t)(tap * p.N), ddesc, xdesc, idesc, acc);
+                        if (a_is_x) umma_bf16_lohi2(tmem_base, xlo, x_hi, dlo, d_hi, idesc, acc);
+                        else umma_bf16_lohi2(tmem_base, dlo, d_hi, xlo, x_hi, idesc, acc);
                     }
                 }
-                umma_commit(&dempty_bar[dslot]);
-                const int dead = (tile + 1 - p.halo_lo) - b0;
-                for (; released < dead; ++released) umma_commit(&empty_bar[released % p.R]);
+                if (leader) {
+                    umma_commit(&dempty_bar[dslot]);
+                    umma_commit(&empty_bar[eslot]);                       // X block `it` is below every later window
+                }
+                if (++dslot == kDySlots) { dslot = 0; dphase ^= 1u; }
+                if (++eslot == p.R) eslot = 0;
+                tb += 128u;
+                if (tb >= ring_px) tb -= ring_px;
             }
-            umma_commit(&done_bar);
+            if (elect_one_w()) umma_commit(&done_bar);
         }
     } else if (t_begin < t_end) {
         // epilogue: M = 64 accumulators occupy lanes 0..15 of each TMEM lane quarter (row = 16 * quarter + lane)
@@ -246,6 +311,7 @@ int launch_wgrad_ring(const WgradArgs<bf16>& a, cudaStream_t s) {
     p.num_tiles = (int)((rows + 127) / 128);
     p.tiles_per_cta = ceil_div(p.num_tiles, tc::num_sms());
     p.R = pl.R; p.halo_lo = pl.halo_lo; p.halo_hi = pl.halo_hi; p.tmem_cols = pl.tmem_cols;
+    for (int t = 0; t < 9; ++t) p.sh[t] = pl.halo_lo * 128 + (p.taps == 9 ? (t / 3 - 1) * p.pw + (t % 3 - 1) : 0);
     const int grid = ceil_div(p.num_tiles, p.tiles_per_cta);
     static bool attr_done = false;
     if (!attr_done) {

@@ -185,7 +185,7 @@ def test_unet_bf16_matches_golden(golden_dir, name):
             cos = float((g * r).sum() / (g.norm() * r.norm() + 1e-30))
             assert cos > 0.9, (k, cos)
         tol = 0.15 * float(r.norm()) + 2e-3 * gmax
-        if r.numel() == 1 and ("grad:" + k) in d.files:
+        if r.numel() == 1 and ("grad:" + k) in d:
             # alpha's gradient is a sum of (xb - xp) * g over every output pixel: cancellation leaves a value far below
             # its terms, so bf16 operand rounding moves it by more than its own size.  Measure that floor as the distance
             # between the bf16-storage restatement and the fp32 golden gradient and allow 2x of it.
