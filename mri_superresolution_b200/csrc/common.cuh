@@ -133,6 +133,31 @@ __device__ __forceinline__ Lerp up_coord(int dst, int in_size, float scale) {
     return l;
 }
 
+
+// Thread -> (8-channel vector, column) mapping of the row-wise elementwise kernels (norm_act.cu, gn_bwd.cu, head.cu).
+// Adjacent threads must touch adjacent 16-byte vectors: in a planar-8 tensor those are adjacent PIXELS of one plane, in an
+// NHWC tensor adjacent channel vectors of one pixel.  A thread keeps its channel vector for its whole life (so per-channel
+// constants and per-channel partial sums live in registers) and walks columns x0, x0 + xstep, ...
+struct RowMap { int cv, x0, xstep; bool active; };
+template <typename T>
+__device__ __forceinline__ RowMap row_map(const Act<T>& t, int nthr, int tid) {
+    const int nv = t.C / 8;
+    RowMap m;
+    if (t.planar()) {
+        const int tpp = nthr / nv;                 // threads per plane
+        m.cv = tid / tpp; m.x0 = tid - m.cv * tpp; m.xstep = tpp; m.active = m.cv < nv;
+    } else {
+        const int pl = nthr / nv;                  // pixels per pass
+        m.cv = tid % nv; m.x0 = tid / nv; m.xstep = pl; m.active = m.x0 < pl;
+    }
+    return m;
+}
+// rows of `units_w` columns per block so that a block of nthr threads handles about `per_thread` units per thread
+inline int rows_per_block(int units_w, int nv, int nthr, int per_thread) {
+    const int r = (nthr * per_thread) / (units_w * nv);
+    return r < 1 ? 1 : r;
+}
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

@@ -9,7 +9,7 @@
 namespace mrisr {
 namespace {
 constexpr int NTHR = 256;
-constexpr int UNITS_PER_THREAD = 8;
+constexpr int UNITS_PER_THREAD = 16;
 
 template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
 
@@ -106,50 +106,56 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
 }
 
 // part layout: [N][slots][3][C+8]  (row 0: sum dz, row 1: sum dz*xh, row 2: SRC_OUTER sum dl*act; column C: sum dl)
+// One block = `rows_pb` unit rows of one sample; thread mapping per common.cuh RowMap (coalesced for both layouts).
 template <typename T, int KIND>
-__global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int units_per_block) {
+__global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int rows_pb) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
-    __shared__ float s_red[3][2048];
+    __shared__ float s_red[3][NTHR * 8];
     __shared__ float s_dl[NTHR];
-    const int C = a.r.C, nv = C / 8, PL = NTHR / nv;
-    const int tid = threadIdx.x, cv = tid % nv, pl = tid / nv;
+    const int C = a.r.C, nv = C / 8;
+    const int tid = threadIdx.x;
     const int n = blockIdx.y;
     const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
+    const RowMap m = row_map(a.r, NTHR, tid);
     float s1[8], s2[8], s3[8], sdl = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
-    if (pl < PL) {
+    if (m.active) {
         ChanCtx c;
-        load_ctx<T, KIND>(a, n, cv, c);
-        const int u_end = min(UH * UW, (int)(blockIdx.x + 1) * units_per_block);
-        for (int u = blockIdx.x * units_per_block + pl; u < u_end; u += PL) {
-            float xh[P][8], dz[P][8], act[8], dl = 0.f;
-            unit_grads<T, KIND, P>(a, c, n, u / UW, u % UW, cv, xh, dz, dl, act);
+        load_ctx<T, KIND>(a, n, m.cv, c);
+        const int uy_end = min(UH, (int)(blockIdx.x + 1) * rows_pb);
+        for (int uy = blockIdx.x * rows_pb; uy < uy_end; ++uy) {
+            for (int ux = m.x0; ux < UW; ux += m.xstep) {
+                float xh[P][8], dz[P][8], act[8], dl = 0.f;
+                unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, xh, dz, dl, act);
 #pragma unroll
-            for (int q = 0; q < P; ++q)
+                for (int q = 0; q < P; ++q)
 #pragma unroll
-                for (int k = 0; k < 8; ++k) { s1[k] += dz[q][k]; s2[k] += dz[q][k] * xh[q][k]; }
-            if (KIND == SRC_OUTER) {
+                    for (int k = 0; k < 8; ++k) { s1[k] += dz[q][k]; s2[k] += dz[q][k] * xh[q][k]; }
+                if (KIND == SRC_OUTER) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
-                if (cv == 0) sdl += dl;
+                    for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
+                    if (m.cv == 0) sdl += dl;
+                }
             }
         }
+    }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            s_red[0][pl * C + cv * 8 + k] = s1[k];
-            s_red[1][pl * C + cv * 8 + k] = s2[k];
-            s_red[2][pl * C + cv * 8 + k] = s3[k];
-        }
+    for (int k = 0; k < 8; ++k) {
+        s_red[0][tid * 8 + k] = s1[k];
+        s_red[1][tid * 8 + k] = s2[k];
+        s_red[2][tid * 8 + k] = s3[k];
     }
     s_dl[tid] = sdl;
     __syncthreads();
     const int64_t row = (int64_t)(C + 8);
     float* out = a.part + ((int64_t)n * gridDim.x + blockIdx.x) * 3 * row;
+    const bool planar = a.r.planar();
+    const int cnt = NTHR / nv;                       // threads sharing one channel vector
     for (int i = tid; i < 3 * C; i += NTHR) {
-        const int which = i / C, ch = i % C;
+        const int which = i / C, ch = i % C, cv = ch >> 3, k = ch & 7;
         float t = 0.f;
-        for (int j = 0; j < PL; ++j) t += s_red[which][j * C + ch];
+        for (int j = 0; j < cnt; ++j) t += s_red[which][(planar ? cv * cnt + j : cv + j * nv) * 8 + k];
         out[which * row + ch] = t;
     }
     if (KIND == SRC_OUTER && tid == 0) {
@@ -218,33 +224,35 @@ __global__ void gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_cou
 }
 
 template <typename T, int KIND>
-__global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a) {
+__global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int rows_pb) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
-    const int C = a.r.C, nv = C / 8, gs = C / kGroups;
+    const int C = a.r.C, gs = C / kGroups;
     const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
-    const int64_t total = (int64_t)a.r.N * UH * UW * nv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int ux = (int)((i / nv) % UW), uy = (int)((i / ((int64_t)nv * UW)) % UH);
-        const int n = (int)(i / ((int64_t)nv * UW * UH));
-        ChanCtx c;
-        load_ctx<T, KIND>(a, n, cv, c);
-        float xh[P][8], dz[P][8], act[8], dl;
-        unit_grads<T, KIND, P>(a, c, n, uy, ux, cv, xh, dz, dl, act);
-        float m1[8], m2[8];
+    const int n = blockIdx.y;
+    const RowMap m = row_map(a.r, NTHR, threadIdx.x);
+    if (!m.active) return;
+    ChanCtx c;
+    load_ctx<T, KIND>(a, n, m.cv, c);
+    float m1[8], m2[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int g = (cv * 8 + k) / gs;
-            m1[k] = a.mstat[(n * kGroups + g) * 2];
-            m2[k] = a.mstat[(n * kGroups + g) * 2 + 1];
-        }
+    for (int k = 0; k < 8; ++k) {
+        const int g = (m.cv * 8 + k) / gs;
+        m1[k] = a.mstat[(n * kGroups + g) * 2];
+        m2[k] = a.mstat[(n * kGroups + g) * 2 + 1];
+    }
+    const int uy_end = min(UH, (int)(blockIdx.x + 1) * rows_pb);
+    for (int uy = blockIdx.x * rows_pb; uy < uy_end; ++uy) {
+        for (int ux = m.x0; ux < UW; ux += m.xstep) {
+            float xh[P][8], dz[P][8], act[8], dl;
+            unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, xh, dz, dl, act);
 #pragma unroll
-        for (int q = 0; q < P; ++q) {
-            const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-            float o[8];
+            for (int q = 0; q < P; ++q) {
+                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+                float o[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = c.rstd[k] * (c.gam[k] * dz[q][k] - m1[k] - xh[q][k] * m2[k]);
-            store8(a.dr.at(n, y, x, cv * 8), o);
+                for (int k = 0; k < 8; ++k) o[k] = c.rstd[k] * (c.gam[k] * dz[q][k] - m1[k] - xh[q][k] * m2[k]);
+                store8(a.dr.at(n, y, x, m.cv * 8), o);
+            }
         }
     }
 }
@@ -252,29 +260,31 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a) {
 template <typename T, int KIND>
 int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
-    const int C = a.r.C, nv = C / 8, PL = NTHR / nv;
-    const int units = (a.r.H / (P == 4 ? 2 : 1)) * (a.r.W / (P == 4 ? 2 : 1));
-    const int upb = PL * UNITS_PER_THREAD;
-    const int slots = ceil_div(units, upb);
+    const int C = a.r.C, nv = C / 8;
+    if (nv > NTHR) { set_error("gn_bwd: C = %d is too wide", C); return -1; }
+    const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
+    const int rows_pb = rows_per_block(UW, nv, NTHR, UNITS_PER_THREAD);
+    const int slots = ceil_div(UH, rows_pb);
     dim3 grid(slots, a.r.N);
-    gn_bwd_reduce_kernel<T, KIND><<<grid, NTHR, 0, s>>>(a, upb);
+    gn_bwd_reduce_kernel<T, KIND><<<grid, NTHR, 0, s>>>(a, rows_pb);
     MRISR_LAUNCH_CHECK();
     const int pcs = KIND == SRC_BLEND_PS ? C / 4 : C;
     const double inv_count = 1.0 / ((double)(C / kGroups) * a.r.H * a.r.W);
     gn_bwd_finalize_kernel<T, KIND><<<a.r.N * kGroups + pcs, 32, 0, s>>>(a, slots, inv_count);
     MRISR_LAUNCH_CHECK();
-    int64_t total = (int64_t)a.r.N * units * nv;
-    int64_t blocks = ceil_div64(total, NTHR);
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    gn_bwd_apply_kernel<T, KIND><<<(unsigned)blocks, NTHR, 0, s>>>(a);
+    const int rows_ap = rows_per_block(UW, nv, NTHR, 4);
+    dim3 grid2(ceil_div(UH, rows_ap), a.r.N);
+    gn_bwd_apply_kernel<T, KIND><<<grid2, NTHR, 0, s>>>(a, rows_ap);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
 }  // namespace
 
 int gn_bwd_slots(int H, int W, int C) {
-    const int PL = NTHR / (C / 8);
-    return ceil_div(H * W, PL * UNITS_PER_THREAD);   // upper bound (pool kinds use a quarter of the units)
+    // upper bound over both unit shapes (pool kinds use half the rows and half the columns)
+    const int full = ceil_div(H, rows_per_block(W, C / 8, NTHR, UNITS_PER_THREAD));
+    const int pool = ceil_div(H / 2, rows_per_block(W / 2, C / 8, NTHR, UNITS_PER_THREAD));
+    return full > pool ? full : pool;
 }
 
 template <typename T>

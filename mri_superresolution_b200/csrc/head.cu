@@ -9,62 +9,99 @@ constexpr int NTHR = 256;
 
 __device__ __forceinline__ float sigmoidf_(float v) { return 1.f / (1.f + __expf(-v)); }
 
-// xb / xp (8 channels of the blended-resolution pixel (n, Y, X)) recomputed from the raw conv outputs
+// Per-thread constants of the two branches for one 8-channel vector of the blended tensor: GroupNorm folded into
+// scale/shift (z = r * sc + sh).  PixelShuffle(2): shuffled[n, c, 2y+i, 2x+j] = raw[n, 4c+2i+j, y, x]
+// (models/unet_model.py:102,111), so output channel c at sub-position ij = 2i+j reads raw channel 4c+ij.
+struct BlendCtx {
+    float scb[8], shb[8], scp[4][8], shp[4][8];
+};
 template <typename T>
-__device__ __forceinline__ void branch_values(const BlendArgs<T>& a, int n, int Y, int X, int cv, float (&xb)[8],
-                                              float (&xp)[8]) {
-    const int Ch = a.r_bil.C, gsb = Ch / kGroups;          // Ch >= 8
-    float v[8];
-    load8(a.r_bil.at(n, Y, X, cv * 8), v);
+__device__ __forceinline__ void load_blend_ctx(const BlendArgs<T>& a, int n, int cv, BlendCtx& c) {
+    const int gsb = a.r_bil.C / kGroups, gsp = a.r_ps.C / kGroups;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const int c = cv * 8 + k, g = c / gsb;
+        const int ch = cv * 8 + k, g = ch / gsb;
         const float mean = a.st_bil[(n * kGroups + g) * 2], rstd = a.st_bil[(n * kGroups + g) * 2 + 1];
-        xb[k] = lrelu((v[k] - mean) * rstd * a.g_bil[c] + a.b_bil[c]);
-    }
-    // PixelShuffle(2): shuffled[n, c, 2y+i, 2x+j] = raw[n, 4c+2i+j, y, x]   (models/unet_model.py:102,111)
-    const int y = Y >> 1, x = X >> 1, ij = ((Y & 1) << 1) | (X & 1);
-    const int Craw = a.r_ps.C, gsp = Craw / kGroups;
+        c.scb[k] = rstd * a.g_bil[ch];
+        c.shb[k] = a.b_bil[ch] - mean * c.scb[k];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int c = cv * 8 + k, craw = 4 * c + ij, g = craw / gsp;
-        const float mean = a.st_ps[(n * kGroups + g) * 2], rstd = a.st_ps[(n * kGroups + g) * 2 + 1];
-        xp[k] = lrelu((to_f(*a.r_ps.at(n, y, x, craw)) - mean) * rstd * a.g_ps[c] + a.b_ps[c]);
+        for (int ij = 0; ij < 4; ++ij) {
+            const int gp = (4 * ch + ij) / gsp;
+            const float mp = a.st_ps[(n * kGroups + gp) * 2], rp = a.st_ps[(n * kGroups + gp) * 2 + 1];
+            c.scp[ij][k] = rp * a.g_ps[ch];
+            c.shp[ij][k] = a.b_ps[ch] - mp * c.scp[ij][k];
+        }
+    }
+}
+// xb / xp of the 2x2 output quad of low-resolution pixel (n, y, x), 8 channels: the quad needs exactly the 32 raw
+// pixel-shuffle channels [32 cv, 32 cv + 32) of that pixel (four 8-channel vectors) and four vectors of the bilinear branch
+template <typename T>
+__device__ __forceinline__ void quad_values(const BlendArgs<T>& a, const BlendCtx& c, int n, int y, int x, int cv,
+                                            float (&xb)[4][8], float (&xp)[4][8]) {
+    float raw[4][8];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) load8(a.r_ps.at(n, y, x, (4 * cv + p) * 8), raw[p]);
+#pragma unroll
+    for (int ij = 0; ij < 4; ++ij) {
+        float v[8];
+        load8(a.r_bil.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), cv * 8), v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            xb[ij][k] = lrelu(fmaf(v[k], c.scb[k], c.shb[k]));
+            xp[ij][k] = lrelu(fmaf(raw[k >> 1][(k & 1) * 4 + ij], c.scp[ij][k], c.shp[ij][k]));
+        }
     }
 }
 
+// one block = `rows_pb` LOW-resolution rows of one sample; a thread owns one channel vector and walks 2x2 output quads
 template <typename T>
-__global__ void __launch_bounds__(NTHR) head_blend_kernel(BlendArgs<T> a) {
-    const int nv = a.xm.C / 8;
+__global__ void __launch_bounds__(NTHR) head_blend_kernel(BlendArgs<T> a, int rows_pb) {
+    const int n = blockIdx.y;
+    const RowMap m = row_map(a.xm, NTHR, threadIdx.x);
+    if (!m.active) return;
     const float al = sigmoidf_(a.alpha[0]);
-    const int64_t total = (int64_t)a.xm.N * a.xm.H * a.xm.W * nv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int X = (int)((i / nv) % a.xm.W), Y = (int)((i / ((int64_t)nv * a.xm.W)) % a.xm.H);
-        const int n = (int)(i / ((int64_t)nv * a.xm.W * a.xm.H));
-        float xb[8], xp[8], o[8];
-        branch_values(a, n, Y, X, cv, xb, xp);
+    BlendCtx c;
+    load_blend_ctx(a, n, m.cv, c);
+    const int h = a.r_ps.H, w = a.r_ps.W;
+    const int y_end = min(h, (int)(blockIdx.x + 1) * rows_pb);
+    for (int y = blockIdx.x * rows_pb; y < y_end; ++y)
+        for (int x = m.x0; x < w; x += m.xstep) {
+            float xb[4][8], xp[4][8];
+            quad_values(a, c, n, y, x, m.cv, xb, xp);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = al * xb[k] + (1.f - al) * xp[k];
-        store8(a.xm.at(n, Y, X, cv * 8), o);
-    }
+            for (int ij = 0; ij < 4; ++ij) {
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = al * xb[ij][k] + (1.f - al) * xp[ij][k];
+                store8(a.xm.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), m.cv * 8), o);
+            }
+        }
 }
 
+// scratch[n * gridDim.x + blockIdx.x] = sum over the block's quads of dxm * (xb - xp)
 template <typename T>
-__global__ void __launch_bounds__(NTHR) blend_dalpha_kernel(BlendArgs<T> a, Act<T> dxm, float* __restrict__ scratch) {
+__global__ void __launch_bounds__(NTHR) blend_dalpha_kernel(BlendArgs<T> a, Act<T> dxm, float* __restrict__ scratch, int rows_pb) {
     __shared__ float s_w[NTHR / 32];
-    const int nv = a.xm.C / 8;
-    const int64_t total = (int64_t)a.xm.N * a.xm.H * a.xm.W * nv;
+    const int n = blockIdx.y;
+    const RowMap m = row_map(a.xm, NTHR, threadIdx.x);
     float acc = 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int X = (int)((i / nv) % a.xm.W), Y = (int)((i / ((int64_t)nv * a.xm.W)) % a.xm.H);
-        const int n = (int)(i / ((int64_t)nv * a.xm.W * a.xm.H));
-        float xb[8], xp[8], g[8];
-        branch_values(a, n, Y, X, cv, xb, xp);
-        load8(dxm.at(n, Y, X, cv * 8), g);
+    if (m.active) {
+        BlendCtx c;
+        load_blend_ctx(a, n, m.cv, c);
+        const int h = a.r_ps.H, w = a.r_ps.W;
+        const int y_end = min(h, (int)(blockIdx.x + 1) * rows_pb);
+        for (int y = blockIdx.x * rows_pb; y < y_end; ++y)
+            for (int x = m.x0; x < w; x += m.xstep) {
+                float xb[4][8], xp[4][8];
+                quad_values(a, c, n, y, x, m.cv, xb, xp);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc = fmaf(g[k], xb[k] - xp[k], acc);
+                for (int ij = 0; ij < 4; ++ij) {
+                    float g[8];
+                    load8(dxm.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), m.cv * 8), g);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc = fmaf(g[k], xb[ij][k] - xp[ij][k], acc);
+                }
+            }
     }
     acc = warp_sum(acc);
     if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
@@ -72,7 +109,7 @@ __global__ void __launch_bounds__(NTHR) blend_dalpha_kernel(BlendArgs<T> a, Act<
     if (threadIdx.x == 0) {
         float t = 0.f;
         for (int w = 0; w < NTHR / 32; ++w) t += s_w[w];
-        scratch[blockIdx.x] = t;
+        scratch[(int64_t)n * gridDim.x + blockIdx.x] = t;
     }
 }
 
@@ -88,56 +125,69 @@ __global__ void dalpha_finalize_kernel(const float* __restrict__ scratch, int nb
     }
 }
 
-// one thread per output pixel: all Ch channels (Ch = f/2: 8 or 16 ... up to 64)
+// one thread per output pixel: all Ch channels (Ch = f/2: 8 or 16 ... up to 64); one block = rows of ONE sample so the
+// folded GroupNorm scale/shift and the 1x1 weights sit in shared memory
 template <typename T>
 __global__ void __launch_bounds__(NTHR) final_head_kernel(Act<T> r, const float* __restrict__ stats,
                                                           const float* __restrict__ gamma,
                                                           const float* __restrict__ beta,
                                                           const float* __restrict__ w1x1,
-                                                          const float* __restrict__ b1x1, float* __restrict__ y) {
+                                                          const float* __restrict__ b1x1, float* __restrict__ y, int rows_pb) {
+    __shared__ float s_sc[256], s_sh[256], s_w[256];
     const int C = r.C, nv = C / 8, gs = C / kGroups;
-    const int64_t total = (int64_t)r.N * r.H * r.W;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int X = (int)(i % r.W), Y = (int)((i / r.W) % r.H), n = (int)(i / ((int64_t)r.W * r.H));
-        float acc = b1x1[0];
-        for (int cv = 0; cv < nv; ++cv) {
-            float v[8];
-            load8(r.at(n, Y, X, cv * 8), v);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const int c = cv * 8 + k, g = c / gs;
-                const float mean = stats[(n * kGroups + g) * 2], rstd = stats[(n * kGroups + g) * 2 + 1];
-                acc = fmaf(w1x1[c], lrelu((v[k] - mean) * rstd * gamma[c] + beta[c]), acc);
-            }
-        }
-        y[i] = 1.f / (1.f + expf(-acc));
+    const int n = blockIdx.y;
+    for (int c = threadIdx.x; c < C; c += NTHR) {
+        const int g = c / gs;
+        const float mean = stats[(n * kGroups + g) * 2], rstd = stats[(n * kGroups + g) * 2 + 1];
+        s_sc[c] = rstd * gamma[c];
+        s_sh[c] = beta[c] - mean * s_sc[c];
+        s_w[c] = w1x1[c];
     }
+    __syncthreads();
+    const float b0 = b1x1[0];
+    const int y_end = min(r.H, (int)(blockIdx.x + 1) * rows_pb);
+    for (int Y = blockIdx.x * rows_pb; Y < y_end; ++Y)
+        for (int X = threadIdx.x; X < r.W; X += NTHR) {
+            float acc = b0;
+            for (int cv = 0; cv < nv; ++cv) {
+                float v[8];
+                load8(r.at(n, Y, X, cv * 8), v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc = fmaf(s_w[cv * 8 + k], lrelu(fmaf(v[k], s_sc[cv * 8 + k], s_sh[cv * 8 + k])), acc);
+            }
+            y[((int64_t)n * r.H + Y) * r.W + X] = 1.f / (1.f + expf(-acc));
+        }
 }
 
 template <typename T>
-__global__ void __launch_bounds__(NTHR) colsum_kernel(Act<T> t, float* __restrict__ scratch, int pix_per_block) {
-    __shared__ float s_red[2048];
-    const int C = t.C, nv = C / 8, PL = NTHR / nv;
-    const int tid = threadIdx.x, cv = tid % nv, pl = tid / nv;
-    const int n = blockIdx.y, HW = t.H * t.W;
+__global__ void __launch_bounds__(NTHR) colsum_kernel(Act<T> t, float* __restrict__ scratch, int rows_pb) {
+    __shared__ float s_red[NTHR * 8];
+    const int C = t.C, nv = C / 8;
+    const int tid = threadIdx.x;
+    const int n = blockIdx.y;
+    const RowMap m = row_map(t, NTHR, tid);
     float s1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = 0.f;
-    if (pl < PL) {
-        const int p_end = min(HW, (int)(blockIdx.x + 1) * pix_per_block);
-        for (int p = blockIdx.x * pix_per_block + pl; p < p_end; p += PL) {
-            float v[8];
-            load8(t.at(n, p / t.W, p % t.W, cv * 8), v);
+    if (m.active) {
+        const int y_end = min(t.H, (int)(blockIdx.x + 1) * rows_pb);
+        for (int y = blockIdx.x * rows_pb; y < y_end; ++y)
+            for (int x = m.x0; x < t.W; x += m.xstep) {
+                float v[8];
+                load8(t.at(n, y, x, m.cv * 8), v);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) s1[k] += v[k];
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s_red[pl * C + cv * 8 + k] = s1[k];
+                for (int k = 0; k < 8; ++k) s1[k] += v[k];
+            }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s_red[tid * 8 + k] = s1[k];
     __syncthreads();
+    const bool planar = t.planar();
+    const int cnt = NTHR / nv;
     for (int c = tid; c < C; c += NTHR) {
+        const int cv = c >> 3, k = c & 7;
         float v = 0.f;
-        for (int j = 0; j < PL; ++j) v += s_red[j * C + c];
+        for (int j = 0; j < cnt; ++j) v += s_red[(planar ? cv * cnt + j : cv + j * nv) * 8 + k];
         scratch[((int64_t)n * gridDim.x + blockIdx.x) * C + c] = v;
     }
 }
@@ -150,32 +200,31 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ scratch, float*
     if (threadIdx.x == 0) out[c] = (float)t;
 }
 
-inline int grid_for(int64_t total) {
-    int64_t b = ceil_div64(total, NTHR);
-    if (b > 148 * 16) b = 148 * 16;
-    if (b < 1) b = 1;
-    return (int)b;
-}
-constexpr int COLSUM_PPT = 32;
 }  // namespace
 
 template <typename T>
 int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s) {
     ProfScope prof_("head_blend", s);
-    head_blend_kernel<T><<<grid_for((int64_t)a.xm.N * a.xm.H * a.xm.W * (a.xm.C / 8)), NTHR, 0, s>>>(a);
+    const int rpb = rows_per_block(a.r_ps.W, a.xm.C / 8, NTHR, 2);
+    head_blend_kernel<T><<<dim3(ceil_div(a.r_ps.H, rpb), a.xm.N), NTHR, 0, s>>>(a, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
 
-size_t blend_dalpha_scratch_elems(int, int, int) { return 148 * 16; }
+static inline int dalpha_rows(int W, int nv) { return rows_per_block(W, nv, NTHR, 4); }
+size_t blend_dalpha_scratch_elems(int N, int H2, int W2) {
+    // one partial per (sample, block of low-resolution rows); nv >= 1 gives the upper bound on the block count
+    return (size_t)N * ceil_div(H2 / 2, dalpha_rows(W2 / 2, 32));
+}
 
 template <typename T>
 int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float* scratch, cudaStream_t s) {
     ProfScope prof_("blend_dalpha", s);
-    const int nb = grid_for((int64_t)a.xm.N * a.xm.H * a.xm.W * (a.xm.C / 8));
-    blend_dalpha_kernel<T><<<nb, NTHR, 0, s>>>(a, dxm, scratch);
+    const int rpb = dalpha_rows(a.r_ps.W, a.xm.C / 8);
+    const int slots = ceil_div(a.r_ps.H, rpb);
+    blend_dalpha_kernel<T><<<dim3(slots, a.xm.N), NTHR, 0, s>>>(a, dxm, scratch, rpb);
     MRISR_LAUNCH_CHECK();
-    dalpha_finalize_kernel<<<1, 32, 0, s>>>(scratch, nb, a.alpha, dalpha);
+    dalpha_finalize_kernel<<<1, 32, 0, s>>>(scratch, slots * a.xm.N, a.alpha, dalpha);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -184,22 +233,24 @@ template <typename T>
 int launch_final_head(Act<T> r, const float* stats, const float* gamma, const float* beta, const float* w1x1,
                       const float* b1x1, float* y, cudaStream_t s) {
     ProfScope prof_("final_head", s);
-    final_head_kernel<T><<<grid_for((int64_t)r.N * r.H * r.W), NTHR, 0, s>>>(r, stats, gamma, beta, w1x1, b1x1, y);
+    if (r.C > 256) { set_error("final_head: C = %d is too wide", r.C); return -1; }
+    const int rpb = rows_per_block(r.W, 1, NTHR, 8);
+    final_head_kernel<T><<<dim3(ceil_div(r.H, rpb), r.N), NTHR, 0, s>>>(r, stats, gamma, beta, w1x1, b1x1, y, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
 
+constexpr int COLSUM_UPT = 32;
 size_t colsum_scratch_elems(int N, int H, int W, int C) {
-    const int PL = NTHR / (C / 8);
-    return (size_t)N * ceil_div(H * W, PL * COLSUM_PPT) * C;
+    return (size_t)N * ceil_div(H, rows_per_block(W, C / 8, NTHR, COLSUM_UPT)) * C;
 }
 
 template <typename T>
 int launch_colsum(Act<T> t, float* out, float* scratch, cudaStream_t s) {
     ProfScope prof_("colsum", s);
-    const int PL = NTHR / (t.C / 8);
-    const int slots = ceil_div(t.H * t.W, PL * COLSUM_PPT);
-    colsum_kernel<T><<<dim3(slots, t.N), NTHR, 0, s>>>(t, scratch, PL * COLSUM_PPT);
+    const int rpb = rows_per_block(t.W, t.C / 8, NTHR, COLSUM_UPT);
+    const int slots = ceil_div(t.H, rpb);
+    colsum_kernel<T><<<dim3(slots, t.N), NTHR, 0, s>>>(t, scratch, rpb);
     MRISR_LAUNCH_CHECK();
     colsum_finalize_kernel<<<t.C, 32, 0, s>>>(scratch, out, t.N * slots, t.C);
     MRISR_LAUNCH_CHECK();

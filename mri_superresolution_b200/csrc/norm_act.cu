@@ -18,38 +18,44 @@ __global__ void pack_input_kernel(const float* __restrict__ x, Act<T> dst) {
 }
 
 // ---- statistics: per (n, slot, group) partial sum / sum of squares -------------------------
+// One block = `rows_pb` rows of one sample; thread mapping per common.cuh RowMap.
 template <typename T>
-__global__ void __launch_bounds__(NTHR) gn_stats_kernel(Act<T> r, float* __restrict__ part, int pix_per_block) {
-    __shared__ float s_red[2][2048];
-    const int C = r.C, nv = C / 8, PL = NTHR / nv;
-    const int tid = threadIdx.x, cv = tid % nv, pl = tid / nv;
-    const int n = blockIdx.y, HW = r.H * r.W;
+__global__ void __launch_bounds__(NTHR) gn_stats_kernel(Act<T> r, float* __restrict__ part, int rows_pb) {
+    __shared__ float s_red[2][NTHR * 8];
+    __shared__ float s_ch[2][2048];
+    const int C = r.C, nv = C / 8;
+    const int tid = threadIdx.x;
+    const int n = blockIdx.y;
+    const RowMap m = row_map(r, NTHR, tid);
     float s1[8], s2[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-    if (pl < PL) {
-        const int p_end = min(HW, (int)(blockIdx.x + 1) * pix_per_block);
-        for (int p = blockIdx.x * pix_per_block + pl; p < p_end; p += PL) {
-            float v[8];
-            load8(r.at(n, p / r.W, p % r.W, cv * 8), v);
+    if (m.active) {
+        const int y_end = min(r.H, (int)(blockIdx.x + 1) * rows_pb);
+        for (int y = blockIdx.x * rows_pb; y < y_end; ++y)
+            for (int x = m.x0; x < r.W; x += m.xstep) {
+                float v[8];
+                load8(r.at(n, y, x, m.cv * 8), v);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { s1[k] += v[k]; s2[k] += v[k] * v[k]; }
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { s_red[0][pl * C + cv * 8 + k] = s1[k]; s_red[1][pl * C + cv * 8 + k] = s2[k]; }
+                for (int k = 0; k < 8; ++k) { s1[k] += v[k]; s2[k] += v[k] * v[k]; }
+            }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s_red[0][tid * 8 + k] = s1[k]; s_red[1][tid * 8 + k] = s2[k]; }
     __syncthreads();
+    const bool planar = r.planar();
+    const int cnt = NTHR / nv;
     for (int i = tid; i < 2 * C; i += NTHR) {
-        const int which = i / C, c = i % C;
+        const int which = i / C, c = i % C, cv = c >> 3, k = c & 7;
         float t = 0.f;
-        for (int j = 0; j < PL; ++j) t += s_red[which][j * C + c];
-        s_red[which][c] = t;           // row 0 reuse: safe, each thread only touches its own column
+        for (int j = 0; j < cnt; ++j) t += s_red[which][(planar ? cv * cnt + j : cv + j * nv) * 8 + k];
+        s_ch[which][c] = t;
     }
     __syncthreads();
     if (tid < 2 * kGroups) {
         const int which = tid / kGroups, g = tid % kGroups, gs = C / kGroups;
         float t = 0.f;
-        for (int c = g * gs; c < (g + 1) * gs; ++c) t += s_red[which][c];
+        for (int c = g * gs; c < (g + 1) * gs; ++c) t += s_ch[which][c];
         part[(((int64_t)n * gridDim.x + blockIdx.x) * kGroups + g) * 2 + which] = t;
     }
 }
@@ -78,72 +84,81 @@ __global__ void gn_finalize_kernel(const float* __restrict__ part, float* __rest
 }
 
 // ---- apply: a = lrelu(gamma * (r - mean) * rstd + beta), optional 2x2 max-pool --------------
+// One block = `rows_pb` (window) rows of one sample; a thread keeps one channel vector (scale/shift in registers).
 template <typename T, bool POOL>
 __global__ void __launch_bounds__(NTHR) gn_apply_kernel(Act<T> r, const float* __restrict__ stats,
                                                         const float* __restrict__ gamma,
-                                                        const float* __restrict__ beta, Act<T> a, Act<T> pooled) {
-    const int C = r.C, nv = C / 8, gs = C / kGroups;
+                                                        const float* __restrict__ beta, Act<T> a, Act<T> pooled, int rows_pb) {
+    const int C = r.C, gs = C / kGroups;
     const int WH = POOL ? r.H / 2 : r.H, WW = POOL ? r.W / 2 : r.W;
-    const int64_t total = (int64_t)r.N * WH * WW * nv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int wx = (int)((i / nv) % WW), wy = (int)((i / ((int64_t)nv * WW)) % WH);
-        const int n = (int)(i / ((int64_t)nv * WW * WH));
-        float sc[8], sh[8];
+    const int n = blockIdx.y;
+    const RowMap m = row_map(r, NTHR, threadIdx.x);
+    if (!m.active) return;
+    const int cv = m.cv;
+    float sc[8], sh[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int c = cv * 8 + k, g = c / gs;
-            const float mean = stats[(n * kGroups + g) * 2], rstd = stats[(n * kGroups + g) * 2 + 1];
-            sc[k] = gamma[c] * rstd;
-            sh[k] = beta[c] - mean * sc[k];
-        }
-        if (!POOL) {
-            float v[8];
-            load8(r.at(n, wy, wx, cv * 8), v);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-            store8(a.at(n, wy, wx, cv * 8), v);
-        } else {
-            float m[8];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int y = 2 * wy + (q >> 1), x = 2 * wx + (q & 1);
+    for (int k = 0; k < 8; ++k) {
+        const int c = cv * 8 + k, g = c / gs;
+        const float mean = stats[(n * kGroups + g) * 2], rstd = stats[(n * kGroups + g) * 2 + 1];
+        sc[k] = gamma[c] * rstd;
+        sh[k] = beta[c] - mean * sc[k];
+    }
+    const int wy_end = min(WH, (int)(blockIdx.x + 1) * rows_pb);
+    for (int wy = blockIdx.x * rows_pb; wy < wy_end; ++wy) {
+        for (int wx = m.x0; wx < WW; wx += m.xstep) {
+            if (!POOL) {
                 float v[8];
-                load8(r.at(n, y, x, cv * 8), v);
+                load8(r.at(n, wy, wx, cv * 8), v);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-                store8(a.at(n, y, x, cv * 8), v);
-                // max over the values as stored (rounded to T) so backward's argmax recomputation agrees
+                store8(a.at(n, wy, wx, cv * 8), v);
+            } else {
+                float mx[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const float vr = to_f(from_f<T>(v[k]));
-                    m[k] = q == 0 ? vr : fmaxf(m[k], vr);
+                for (int q = 0; q < 4; ++q) {
+                    const int y = 2 * wy + (q >> 1), x = 2 * wx + (q & 1);
+                    float v[8];
+                    load8(r.at(n, y, x, cv * 8), v);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
+                    store8(a.at(n, y, x, cv * 8), v);
+                    // max over the values as stored (rounded to T) so backward's argmax recomputation agrees
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float vr = to_f(from_f<T>(v[k]));
+                        mx[k] = q == 0 ? vr : fmaxf(mx[k], vr);
+                    }
                 }
+                store8(pooled.at(n, wy, wx, cv * 8), mx);
             }
-            store8(pooled.at(n, wy, wx, cv * 8), m);
         }
     }
 }
 
 // ---- bilinear x2, align_corners=True ------------------------------------------------------
+// One block = `rows_pb` destination rows of one sample; mapped by the DESTINATION layout.
 template <typename T>
-__global__ void __launch_bounds__(NTHR) upsample2x_kernel(Act<T> src, Act<T> dst, float sy, float sx) {
-    const int nv = src.C / 8;
-    const int64_t total = (int64_t)dst.N * dst.H * dst.W * nv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int X = (int)((i / nv) % dst.W), Y = (int)((i / ((int64_t)nv * dst.W)) % dst.H);
-        const int n = (int)(i / ((int64_t)nv * dst.W * dst.H));
-        const Lerp ly = up_coord(Y, src.H, sy), lx = up_coord(X, src.W, sx);
-        float v00[8], v01[8], v10[8], v11[8], o[8];
-        load8(src.at(n, ly.i0, lx.i0, cv * 8), v00);
-        load8(src.at(n, ly.i0, lx.i1, cv * 8), v01);
-        load8(src.at(n, ly.i1, lx.i0, cv * 8), v10);
-        load8(src.at(n, ly.i1, lx.i1, cv * 8), v11);
-        const float h1 = ly.w1, h0 = 1.f - h1, w1 = lx.w1, w0 = 1.f - w1;
+__global__ void __launch_bounds__(NTHR) upsample2x_kernel(Act<T> src, Act<T> dst, float sy, float sx, int rows_pb) {
+    const int n = blockIdx.y;
+    const RowMap m = row_map(dst, NTHR, threadIdx.x);
+    if (!m.active) return;
+    const int cv = m.cv;
+    const int y_end = min(dst.H, (int)(blockIdx.x + 1) * rows_pb);
+    for (int Y = blockIdx.x * rows_pb; Y < y_end; ++Y) {
+        const Lerp ly = up_coord(Y, src.H, sy);
+        const float h1 = ly.w1, h0 = 1.f - h1;
+        for (int X = m.x0; X < dst.W; X += m.xstep) {
+            const Lerp lx = up_coord(X, src.W, sx);
+            float v00[8], v01[8], v10[8], v11[8], o[8];
+            load8(src.at(n, ly.i0, lx.i0, cv * 8), v00);
+            load8(src.at(n, ly.i0, lx.i1, cv * 8), v01);
+            load8(src.at(n, ly.i1, lx.i0, cv * 8), v10);
+            load8(src.at(n, ly.i1, lx.i1, cv * 8), v11);
+            const float w1 = lx.w1, w0 = 1.f - w1;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = h0 * (w0 * v00[k] + w1 * v01[k]) + h1 * (w0 * v10[k] + w1 * v11[k]);
-        store8(dst.at(n, Y, X, cv * 8), o);
+            for (int k = 0; k < 8; ++k) o[k] = h0 * (w0 * v00[k] + w1 * v01[k]) + h1 * (w0 * v10[k] + w1 * v11[k]);
+            store8(dst.at(n, Y, X, cv * 8), o);
+        }
     }
 }
 
@@ -160,36 +175,40 @@ __device__ __forceinline__ float adj_weight(int dst, int i, int in_size, float s
     return (l.i0 == i ? 1.f - l.w1 : 0.f) + (l.i1 == i ? l.w1 : 0.f);
 }
 
-// gather form of the adjoint: deterministic, no atomics
+// gather form of the adjoint: deterministic, no atomics.  One block = `rows_pb` source rows of one sample, mapped by the
+// layout of the (4x larger) gradient tensor being read.
 template <typename T>
 __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T> addend, Act<T> dsrc, float sy,
-                                                              float sx) {
-    const int nv = dsrc.C / 8;
-    const int64_t total = (int64_t)dsrc.N * dsrc.H * dsrc.W * nv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int cv = (int)(i % nv);
-        const int x = (int)((i / nv) % dsrc.W), y = (int)((i / ((int64_t)nv * dsrc.W)) % dsrc.H);
-        const int n = (int)(i / ((int64_t)nv * dsrc.W * dsrc.H));
-        float acc[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-        if (addend.p) load8(addend.at(n, y, x, cv * 8), acc);
-        int ylo, yhi, xlo, xhi;
+                                                              float sx, int rows_pb) {
+    const int n = blockIdx.y;
+    const RowMap m = row_map(ddst, NTHR, threadIdx.x);
+    if (!m.active) return;
+    const int cv = m.cv;
+    const int y_end = min(dsrc.H, (int)(blockIdx.x + 1) * rows_pb);
+    for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
+        int ylo, yhi;
         adj_range(y, dsrc.H, sy, ylo, yhi);
-        adj_range(x, dsrc.W, sx, xlo, xhi);
-        for (int Y = ylo; Y <= yhi; ++Y) {
-            const float wy = adj_weight(Y, y, dsrc.H, sy);
-            if (wy == 0.f) continue;
-            for (int X = xlo; X <= xhi; ++X) {
-                const float w = wy * adj_weight(X, x, dsrc.W, sx);
-                if (w == 0.f) continue;
-                float v[8];
-                load8(ddst.at(n, Y, X, cv * 8), v);
+        for (int x = m.x0; x < dsrc.W; x += m.xstep) {
+            float acc[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+            if (addend.p) load8(addend.at(n, y, x, cv * 8), acc);
+            int xlo, xhi;
+            adj_range(x, dsrc.W, sx, xlo, xhi);
+            for (int Y = ylo; Y <= yhi; ++Y) {
+                const float wy = adj_weight(Y, y, dsrc.H, sy);
+                if (wy == 0.f) continue;
+                for (int X = xlo; X <= xhi; ++X) {
+                    const float w = wy * adj_weight(X, x, dsrc.W, sx);
+                    if (w == 0.f) continue;
+                    float v[8];
+                    load8(ddst.at(n, Y, X, cv * 8), v);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+                }
             }
+            store8(dsrc.at(n, y, x, cv * 8), acc);
         }
-        store8(dsrc.at(n, y, x, cv * 8), acc);
     }
 }
 
@@ -210,16 +229,14 @@ int launch_pack_input(const float* x, Act<T> dst, cudaStream_t s) {
 }
 
 int stat_slots_generic(int H, int W, int C) {
-    const int PL = NTHR / (C / 8);
-    return ceil_div(H * W, PL * PIX_PER_THREAD);
+    return ceil_div(H, rows_per_block(W, C / 8, NTHR, PIX_PER_THREAD));
 }
 
 template <typename T>
 int launch_gn_stats(Act<T> r, float* part, cudaStream_t s) {
     ProfScope prof_("gn_stats", s);
-    const int PL = NTHR / (r.C / 8);
     dim3 grid(stat_slots_generic(r.H, r.W, r.C), r.N);
-    gn_stats_kernel<T><<<grid, NTHR, 0, s>>>(r, part, PL * PIX_PER_THREAD);
+    gn_stats_kernel<T><<<grid, NTHR, 0, s>>>(r, part, rows_per_block(r.W, r.C / 8, NTHR, PIX_PER_THREAD));
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -237,11 +254,13 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
     ProfScope prof_("gn_apply", s);
     const int nv = r.C / 8;
     if (pooled.p) {
-        gn_apply_kernel<T, true><<<grid_for((int64_t)r.N * (r.H / 2) * (r.W / 2) * nv), NTHR, 0, s>>>(r, stats, gamma,
-                                                                                                     beta, a, pooled);
+        const int rpb = rows_per_block(r.W / 2, nv, NTHR, 2);
+        dim3 grid(ceil_div(r.H / 2, rpb), r.N);
+        gn_apply_kernel<T, true><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     } else {
-        gn_apply_kernel<T, false><<<grid_for((int64_t)r.N * r.H * r.W * nv), NTHR, 0, s>>>(r, stats, gamma, beta, a,
-                                                                                          pooled);
+        const int rpb = rows_per_block(r.W, nv, NTHR, 4);
+        dim3 grid(ceil_div(r.H, rpb), r.N);
+        gn_apply_kernel<T, false><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     }
     MRISR_LAUNCH_CHECK();
     return 0;
@@ -250,8 +269,9 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     ProfScope prof_("upsample2x", s);
-    upsample2x_kernel<T><<<grid_for((int64_t)dst.N * dst.H * dst.W * (src.C / 8)), NTHR, 0, s>>>(
-        src, dst, up_scale(src.H), up_scale(src.W));
+    const int rpb = rows_per_block(dst.W, dst.C / 8, NTHR, 4);
+    dim3 grid(ceil_div(dst.H, rpb), dst.N);
+    upsample2x_kernel<T><<<grid, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -259,8 +279,9 @@ int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
 template <typename T>
 int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t s) {
     ProfScope prof_("upsample2x_bwd", s);
-    upsample2x_bwd_kernel<T><<<grid_for((int64_t)dsrc.N * dsrc.H * dsrc.W * (dsrc.C / 8)), NTHR, 0, s>>>(
-        ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W));
+    const int rpb = rows_per_block(dsrc.W, dsrc.C / 8, NTHR, 2);
+    dim3 grid(ceil_div(dsrc.H, rpb), dsrc.N);
+    upsample2x_bwd_kernel<T><<<grid, NTHR, 0, s>>>(ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W), rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }

@@ -185,11 +185,16 @@ def test_unet_bf16_matches_golden(golden_dir, name):
             cos = float((g * r).sum() / (g.norm() * r.norm() + 1e-30))
             assert cos > 0.9, (k, cos)
         tol = 0.15 * float(r.norm()) + 2e-3 * gmax
+        # bf16 noise floor of this gradient: distance between the bf16-storage restatement and the fp32 golden gradient.
+        # alpha's gradient is a sum of (xb - xp) * g over every output pixel (cancellation leaves a value far below its
+        # terms) and the first layers sit at the end of a 20-layer bf16 chain: on these tiny random-init cases operand
+        # rounding alone moves their norms by 20-30 %, so the CUDA path is allowed the same distance.
         if r.numel() == 1 and ("grad:" + k) in d:
-            # alpha's gradient is a sum of (xb - xp) * g over every output pixel: cancellation leaves a value far below
-            # its terms, so bf16 operand rounding moves it by more than its own size.  Measure that floor as the distance
-            # between the bf16-storage restatement and the fp32 golden gradient and allow 2x of it.
             tol += 2.0 * abs(float(r) - float(d["grad:" + k]))
+        elif ("grad:" + k + "@norm") in d:
+            tol += abs(float(r.norm()) - float(d["grad:" + k + "@norm"]))
+        elif ("grad:" + k) in d:
+            tol += abs(float(r.norm()) - float(np.linalg.norm(d["grad:" + k].astype(np.float64))))
         assert abs(float(g.norm() if r.numel() > 1 else g) - float(r.norm() if r.numel() > 1 else r)) < tol, k
 
 
