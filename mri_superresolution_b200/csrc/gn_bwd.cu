@@ -4,18 +4,23 @@
 // The reference has no hand-written backward (autograd of models/unet_model.py:29-37,52,93,110-113,
 // 206-211); formulas: z = gamma*xh + beta, xh = (r-mean)*rstd, dz = dA*lrelu'(z),
 //   dr = rstd * (gamma*dz - mean_g(gamma*dz) - xh * mean_g(gamma*dz*xh)).
+// Kernel form (fewer per-thread constants, more loads in flight): with sc = gamma*rstd, sh = beta - mean*sc the reduce
+// pass accumulates per channel  s1 = sum dz,  s2r = sum dz*r  (raw r);  the finalize forms  sum dz*xh = rstd*(s2r - mean*s1),
+// m1, m2 and the per-(n, group) constants  q = -rstd*m1 + mean*rstd^2*m2,  p = -rstd^2*m2,  and the apply pass is
+//   dr = sc*dz + p*r + q.
 #include "kernels.cuh"
 
 namespace mrisr {
 namespace {
 constexpr int NTHR = 256;
-constexpr int UNITS_PER_THREAD = 16;
+constexpr int UNITS_PER_THREAD = 32;
+constexpr int FTHR = 256;         // threads of the finalize kernel
 
 template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
 
-// Per-thread context for 8 channels of one sample
+// Per-thread context for 8 channels of one sample: GroupNorm folded into z = r * sc + sh
 struct ChanCtx {
-    float sc[8], sh[8], mean[8], rstd[8], gam[8];
+    float sc[8], sh[8];
 };
 
 template <typename T, int KIND>
@@ -25,30 +30,24 @@ __device__ __forceinline__ void load_ctx(const GnBwdArgs<T>& a, int n, int cv, C
     for (int k = 0; k < 8; ++k) {
         const int ch = cv * 8 + k, g = ch / gs;
         const int pc = KIND == SRC_BLEND_PS ? ch / 4 : ch;
-        c.mean[k] = a.stats[(n * kGroups + g) * 2];
-        c.rstd[k] = a.stats[(n * kGroups + g) * 2 + 1];
-        c.gam[k] = a.gamma[pc];
-        c.sc[k] = c.gam[k] * c.rstd[k];
-        c.sh[k] = a.beta[pc] - c.mean[k] * c.sc[k];
+        const float mean = a.stats[(n * kGroups + g) * 2], rstd = a.stats[(n * kGroups + g) * 2 + 1];
+        c.sc[k] = a.gamma[pc] * rstd;
+        c.sh[k] = a.beta[pc] - mean * c.sc[k];
     }
 }
 
-// Computes xh and dz for one unit (1 pixel, or a 2x2 window for the pool kinds).
+// Loads the raw conv outputs rv and computes dz for one unit (1 pixel, or a 2x2 window for the pool kinds).
 // dl_out: (SRC_OUTER) dl of the pixel; act_out: lrelu(z) (SRC_OUTER weight gradient)
 template <typename T, int KIND, int P>
 __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx& c, int n, int uy, int ux, int cv,
-                                           float (&xh)[P][8], float (&dz)[P][8], float& dl_out, float (&act_out)[8]) {
+                                           float (&rv)[P][8], float (&dz)[P][8], float& dl_out, float (&act_out)[8]) {
     float z[P][8];
 #pragma unroll
     for (int q = 0; q < P; ++q) {
         const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-        float v[8];
-        load8(a.r.at(n, y, x, cv * 8), v);
+        load8(a.r.at(n, y, x, cv * 8), rv[q]);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            xh[q][k] = (v[k] - c.mean[k]) * c.rstd[k];
-            z[q][k] = fmaf(v[k], c.sc[k], c.sh[k]);
-        }
+        for (int k = 0; k < 8; ++k) z[q][k] = fmaf(rv[q][k], c.sc[k], c.sh[k]);
         float dA[8];
         if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
             load8(a.g.at(n, y, x, a.coff + cv * 8), dA);
@@ -105,7 +104,7 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
         for (int k = 0; k < 8; ++k) dz[q][k] *= lrelu_grad(z[q][k]);
 }
 
-// part layout: [N][slots][3][C+8]  (row 0: sum dz, row 1: sum dz*xh, row 2: SRC_OUTER sum dl*act; column C: sum dl)
+// part layout: [N][slots][3][C+8]  (row 0: sum dz, row 1: sum dz*r (raw), row 2: SRC_OUTER sum dl*act; column C: sum dl)
 // One block = `rows_pb` unit rows of one sample; thread mapping per common.cuh RowMap (coalesced for both layouts).
 template <typename T, int KIND>
 __global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int rows_pb) {
@@ -124,18 +123,28 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int
         ChanCtx c;
         load_ctx<T, KIND>(a, n, m.cv, c);
         const int uy_end = min(UH, (int)(blockIdx.x + 1) * rows_pb);
+        constexpr int UB = P == 4 ? 1 : 2;             // units in flight per thread (all loads issued before any use)
         for (int uy = blockIdx.x * rows_pb; uy < uy_end; ++uy) {
-            for (int ux = m.x0; ux < UW; ux += m.xstep) {
-                float xh[P][8], dz[P][8], act[8], dl = 0.f;
-                unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, xh, dz, dl, act);
+            for (int ux0 = m.x0; ux0 < UW; ux0 += UB * m.xstep) {
+                float rv[UB][P][8], dz[UB][P][8], act[UB][8], dl[UB];
 #pragma unroll
-                for (int q = 0; q < P; ++q)
+                for (int u = 0; u < UB; ++u) {
+                    dl[u] = 0.f;
+                    const int ux = min(ux0 + u * m.xstep, UW - 1);      // clamped duplicate is discarded below
+                    unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, rv[u], dz[u], dl[u], act[u]);
+                }
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) { s1[k] += dz[q][k]; s2[k] += dz[q][k] * xh[q][k]; }
-                if (KIND == SRC_OUTER) {
+                for (int u = 0; u < UB; ++u) {
+                    if (ux0 + u * m.xstep >= UW) continue;
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
-                    if (m.cv == 0) sdl += dl;
+                    for (int q = 0; q < P; ++q)
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { s1[k] += dz[u][q][k]; s2[k] = fmaf(dz[u][q][k], rv[u][q][k], s2[k]); }
+                    if (KIND == SRC_OUTER) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) s3[k] += dl[u] * act[u][k];
+                        if (m.cv == 0) sdl += dl[u];
+                    }
                 }
             }
         }
@@ -165,41 +174,51 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int
     }
 }
 
-// blocks [0, N*8): m1, m2 per (n, group).  blocks [N*8, N*8 + C): per-channel parameter gradients.
+// blocks [0, N*8): the apply constants (q, p) per (n, group).  blocks [N*8, N*8 + C): per-channel parameter gradients.
 template <typename T, int KIND>
-__global__ void gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_count) {
+__global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_count) {
+    __shared__ double s_w[4][FTHR / 32];
     const int C = a.r.C, gs = C / kGroups, N = a.r.N;
     const int64_t row = (int64_t)(C + 8);
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, tid = threadIdx.x;
     if ((int)blockIdx.x < N * kGroups) {
         const int n = blockIdx.x / kGroups, g = blockIdx.x % kGroups;
+        const double mean = (double)a.stats[blockIdx.x * 2], rstd = (double)a.stats[blockIdx.x * 2 + 1];
         double m1 = 0.0, m2 = 0.0;
-        for (int i = lane; i < slots * gs; i += 32) {
+        for (int i = tid; i < slots * gs; i += FTHR) {
             const int s = i / gs, ch = g * gs + i % gs;
             const float* q = a.part + ((int64_t)n * slots + s) * 3 * row;
             const double gm = (double)a.gamma[KIND == SRC_BLEND_PS ? ch / 4 : ch];
             m1 += gm * (double)q[ch];
-            m2 += gm * (double)q[row + ch];
+            m2 += gm * ((double)q[row + ch] - mean * (double)q[ch]);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             m1 += __shfl_xor_sync(0xffffffffu, m1, o);
             m2 += __shfl_xor_sync(0xffffffffu, m2, o);
         }
-        if (lane == 0) {
-            a.mstat[blockIdx.x * 2] = (float)(m1 * inv_count);
-            a.mstat[blockIdx.x * 2 + 1] = (float)(m2 * inv_count);
+        if (lane == 0) { s_w[0][wid] = m1; s_w[1][wid] = m2; }
+        __syncthreads();
+        if (tid == 0) {
+            m1 = m2 = 0.0;
+            for (int w = 0; w < FTHR / 32; ++w) { m1 += s_w[0][w]; m2 += s_w[1][w]; }
+            m1 *= inv_count;
+            m2 *= rstd * inv_count;                       // mean_g(gamma * dz * xh)
+            a.mstat[blockIdx.x * 2] = (float)(-rstd * m1 + mean * rstd * rstd * m2);      // q
+            a.mstat[blockIdx.x * 2 + 1] = (float)(-rstd * rstd * m2);                      // p
         }
     } else {
         // one block per parameter channel pc; raw channels mapping to it: [pc*rep, (pc+1)*rep)
         const int rep = KIND == SRC_BLEND_PS ? 4 : 1;
         const int pc = blockIdx.x - N * kGroups;
         double d1 = 0.0, d2 = 0.0, d3 = 0.0, d4 = 0.0;
-        for (int i = lane; i < N * slots * rep; i += 32) {
+        for (int i = tid; i < N * slots * rep; i += FTHR) {
             const int ch = pc * rep + i % rep;
-            const float* q = a.part + (int64_t)(i / rep) * 3 * row;
+            const int ns = i / rep, n = ns / slots, g = ch / gs;
+            const float* q = a.part + (int64_t)ns * 3 * row;
+            const double mean = (double)a.stats[(n * kGroups + g) * 2], rstd = (double)a.stats[(n * kGroups + g) * 2 + 1];
             d1 += (double)q[ch];
-            d2 += (double)q[row + ch];
+            d2 += rstd * ((double)q[row + ch] - mean * (double)q[ch]);
             if (KIND == SRC_OUTER) {
                 d3 += (double)q[2 * row + ch];
                 if (pc == 0) d4 += (double)q[C];
@@ -212,7 +231,11 @@ __global__ void gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_cou
             d3 += __shfl_xor_sync(0xffffffffu, d3, o);
             d4 += __shfl_xor_sync(0xffffffffu, d4, o);
         }
-        if (lane == 0) {
+        if (lane == 0) { s_w[0][wid] = d1; s_w[1][wid] = d2; s_w[2][wid] = d3; s_w[3][wid] = d4; }
+        __syncthreads();
+        if (tid == 0) {
+            d1 = d2 = d3 = d4 = 0.0;
+            for (int w = 0; w < FTHR / 32; ++w) { d1 += s_w[0][w]; d2 += s_w[1][w]; d3 += s_w[2][w]; d4 += s_w[3][w]; }
             a.dbeta[pc] = (float)d1;
             a.dgamma[pc] = (float)d2;
             if (KIND == SRC_OUTER) {
@@ -233,25 +256,35 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
     if (!m.active) return;
     ChanCtx c;
     load_ctx<T, KIND>(a, n, m.cv, c);
-    float m1[8], m2[8];
+    float cq[8], cp[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const int g = (m.cv * 8 + k) / gs;
-        m1[k] = a.mstat[(n * kGroups + g) * 2];
-        m2[k] = a.mstat[(n * kGroups + g) * 2 + 1];
+        cq[k] = a.mstat[(n * kGroups + g) * 2];
+        cp[k] = a.mstat[(n * kGroups + g) * 2 + 1];
     }
     const int uy_end = min(UH, (int)(blockIdx.x + 1) * rows_pb);
+    constexpr int UB = P == 4 ? 1 : 2;
     for (int uy = blockIdx.x * rows_pb; uy < uy_end; ++uy) {
-        for (int ux = m.x0; ux < UW; ux += m.xstep) {
-            float xh[P][8], dz[P][8], act[8], dl;
-            unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, xh, dz, dl, act);
+        for (int ux0 = m.x0; ux0 < UW; ux0 += UB * m.xstep) {
+            float rv[UB][P][8], dz[UB][P][8], act[8], dl;
 #pragma unroll
-            for (int q = 0; q < P; ++q) {
-                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-                float o[8];
+            for (int u = 0; u < UB; ++u) {
+                const int ux = min(ux0 + u * m.xstep, UW - 1);
+                unit_grads<T, KIND, P>(a, c, n, uy, ux, m.cv, rv[u], dz[u], dl, act);
+            }
 #pragma unroll
-                for (int k = 0; k < 8; ++k) o[k] = c.rstd[k] * (c.gam[k] * dz[q][k] - m1[k] - xh[q][k] * m2[k]);
-                store8(a.dr.at(n, y, x, m.cv * 8), o);
+            for (int u = 0; u < UB; ++u) {
+                const int ux = ux0 + u * m.xstep;
+                if (ux >= UW) continue;
+#pragma unroll
+                for (int q = 0; q < P; ++q) {
+                    const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+                    float o[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[u][q][k], fmaf(cp[k], rv[u][q][k], cq[k]));
+                    store8(a.dr.at(n, y, x, m.cv * 8), o);
+                }
             }
         }
     }
@@ -270,9 +303,9 @@ int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     MRISR_LAUNCH_CHECK();
     const int pcs = KIND == SRC_BLEND_PS ? C / 4 : C;
     const double inv_count = 1.0 / ((double)(C / kGroups) * a.r.H * a.r.W);
-    gn_bwd_finalize_kernel<T, KIND><<<a.r.N * kGroups + pcs, 32, 0, s>>>(a, slots, inv_count);
+    gn_bwd_finalize_kernel<T, KIND><<<a.r.N * kGroups + pcs, FTHR, 0, s>>>(a, slots, inv_count);
     MRISR_LAUNCH_CHECK();
-    const int rows_ap = rows_per_block(UW, nv, NTHR, 4);
+    const int rows_ap = rows_per_block(UW, nv, NTHR, 8);
     dim3 grid2(ceil_div(UH, rows_ap), a.r.N);
     gn_bwd_apply_kernel<T, KIND><<<grid2, NTHR, 0, s>>>(a, rows_ap);
     MRISR_LAUNCH_CHECK();
@@ -289,7 +322,13 @@ int gn_bwd_slots(int H, int W, int C) {
 
 template <typename T>
 int launch_gn_bwd(const GnBwdArgs<T>& a, cudaStream_t s) {
-    ProfScope prof_("gn_bwd", s);
+    const char* tag = "gn_bwd";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "gn_bwd:kind%d:%d@%dx%d", a.kind, a.r.C, a.r.H, a.r.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
     switch (a.kind) {
         case SRC_DIRECT: return run<T, SRC_DIRECT>(a, s);
         case SRC_DIRECT_POOL: return run<T, SRC_DIRECT_POOL>(a, s);

@@ -175,6 +175,24 @@ __device__ __forceinline__ float adj_weight(int dst, int i, int in_size, float s
     return (l.i0 == i ? 1.f - l.w1 : 0.f) + (l.i1 == i ? l.w1 : 0.f);
 }
 
+// Candidate destination indices of source index i and their weights: dst d contributes to i with (1 - w1) if i0(d) == i and
+// with w1 if i1(d) == i.  With scale = (in-1)/(2in-1) < 1/2 at most 5 consecutive d qualify.
+struct AdjTaps { int lo, cnt; float w[6]; };
+__device__ __forceinline__ AdjTaps adj_taps(int i, int in_size, float scale) {
+    AdjTaps t;
+    int lo, hi;
+    adj_range(i, in_size, scale, lo, hi);
+    // shrink to the first / last non-zero weight (the range above is a safe superset)
+    while (lo <= hi && adj_weight(lo, i, in_size, scale) == 0.f) ++lo;
+    while (hi >= lo && adj_weight(hi, i, in_size, scale) == 0.f) --hi;
+    t.lo = lo;
+    t.cnt = hi - lo + 1;
+    if (t.cnt > 6) t.cnt = 6;                       // cannot happen for scale < 1/2 (kept as a bound for the register array)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) t.w[j] = j < t.cnt ? adj_weight(lo + j, i, in_size, scale) : 0.f;
+    return t;
+}
+
 // gather form of the adjoint: deterministic, no atomics.  One block = `rows_pb` source rows of one sample, mapped by the
 // layout of the (4x larger) gradient tensor being read.
 template <typename T>
@@ -186,25 +204,28 @@ __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T
     const int cv = m.cv;
     const int y_end = min(dsrc.H, (int)(blockIdx.x + 1) * rows_pb);
     for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
-        int ylo, yhi;
-        adj_range(y, dsrc.H, sy, ylo, yhi);
+        const AdjTaps ty = adj_taps(y, dsrc.H, sy);
         for (int x = m.x0; x < dsrc.W; x += m.xstep) {
+            const AdjTaps tx = adj_taps(x, dsrc.W, sx);
             float acc[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] = 0.f;
             if (addend.p) load8(addend.at(n, y, x, cv * 8), acc);
-            int xlo, xhi;
-            adj_range(x, dsrc.W, sx, xlo, xhi);
-            for (int Y = ylo; Y <= yhi; ++Y) {
-                const float wy = adj_weight(Y, y, dsrc.H, sy);
-                if (wy == 0.f) continue;
-                for (int X = xlo; X <= xhi; ++X) {
-                    const float w = wy * adj_weight(X, x, dsrc.W, sx);
-                    if (w == 0.f) continue;
-                    float v[8];
-                    load8(ddst.at(n, Y, X, cv * 8), v);
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+            for (int jy = 0; jy < 6; ++jy) {
+                if (jy >= ty.cnt) continue;
+                const float wy = ty.w[jy];
+                const T* rowp = ddst.at(n, ty.lo + jy, tx.lo, cv * 8);
+                const int ps = ddst.ps ? ddst.ps : ddst.C;
+#pragma unroll
+                for (int jx = 0; jx < 6; ++jx) {
+                    if (jx < tx.cnt) {
+                        float v[8];
+                        load8(rowp + (int64_t)jx * ps, v);
+                        const float w = wy * tx.w[jx];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+                    }
                 }
             }
             store8(dsrc.at(n, y, x, cv * 8), acc);
@@ -251,7 +272,13 @@ int launch_gn_finalize(const float* part, float* stats, int N, int slots, double
 template <typename T>
 int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const float* beta, Act<T> a, Act<T> pooled,
                     cudaStream_t s) {
-    ProfScope prof_("gn_apply", s);
+    const char* tag = "gn_apply";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "gn_apply:pool%d:%d@%dx%d", pooled.p ? 1 : 0, r.C, r.H, r.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
     const int nv = r.C / 8;
     if (pooled.p) {
         const int rpb = rows_per_block(r.W / 2, nv, NTHR, 2);
@@ -278,7 +305,13 @@ int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
 
 template <typename T>
 int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t s) {
-    ProfScope prof_("upsample2x_bwd", s);
+    const char* tag = "upsample2x_bwd";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "upsample2x_bwd:add%d:%d@%dx%d", addend.p ? 1 : 0, dsrc.C, dsrc.H, dsrc.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
     const int rpb = rows_per_block(dsrc.W, dsrc.C / 8, NTHR, 2);
     dim3 grid(ceil_div(dsrc.H, rpb), dsrc.N);
     upsample2x_bwd_kernel<T><<<grid, NTHR, 0, s>>>(ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W), rpb);
