@@ -197,9 +197,10 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(mode: str, world: int, per_gpu_batch: int):
-    return {"workload": (f"BASELINE.json configs[1]: U-Net(base_filters={BASE_FILTERS}) "
-                         f"{'training step, L1+SSIM(0.4) loss, Adam' if mode == 'train' else 'inference forward'}, "
+def workload_config(mode: str, world: int, per_gpu_batch: int, perceptual: float = 0.0):
+    loss = "L1+SSIM(0.4)" if perceptual <= 0 else f"L1+SSIM(0.4)+VGG19 perceptual({perceptual})"
+    return {"workload": (f"BASELINE.json configs[{1 if perceptual <= 0 else 2}]: U-Net(base_filters={BASE_FILTERS}) "
+                         f"{'training step, ' + loss + ' loss, Adam' if mode == 'train' else 'inference forward'}, "
                          f"batch {per_gpu_batch}/GPU, {H}x{W} input -> {2 * H}x{2 * W} output"),
             "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * world, "input": [H, W],
             "parallelism": f"dp{world}", "l2": "working set per step (>= 8 GB of activations) >> 126 MB L2; inputs re-read from HBM"}
@@ -230,7 +231,11 @@ def run_ours(args):
 
     torch.manual_seed(SEED)
     model = UNetSuperRes(base_filters=BASE_FILTERS, precision=args.precision).to(dev)
-    crit = CombinedLoss(ssim_weight=SSIM_WEIGHT)
+    if args.perceptual > 0:
+        from mri_superresolution_b200.utils.synthetic import make_vgg19_weights
+        crit = CombinedLoss(ssim_weight=SSIM_WEIGHT, perceptual_weight=args.perceptual, vgg_weights=make_vgg19_weights())
+    else:
+        crit = CombinedLoss(ssim_weight=SSIM_WEIGHT)
     opt = FusedAdam(model, lr=LR, weight_decay=WD)
     buckets = GradientBuckets(model) if world > 1 else None
     x_cpu, t_cpu = make_pairs(nb, H, W, seed=SEED, rank=rank)
@@ -377,7 +382,7 @@ def run_ours(args):
             "metric": METRIC if mode == "train" else INFER_METRIC, "value": value, "unit": "slices/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-            "config": workload_config(mode, world, nb),
+            "config": workload_config(mode, world, nb, args.perceptual),
             "e2e": {"value": e2e_value, "unit": "slices/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h[0],
                     "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
@@ -398,6 +403,8 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="slices per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--perceptual", type=float, default=0.0,
+                    help="weight of the VGG19[:36] perceptual term (BASELINE.json configs[2] uses 0.1); 0 = configs[1]")
     ap.add_argument("--layer-report", default=None, help="write the per-kernel-tag (per layer shape) timing table here")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

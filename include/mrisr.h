@@ -88,6 +88,28 @@ int mrisr_l1_ssim_fwd_bwd(const float* pred, const float* target, float* dpred, 
 int mrisr_ssim_forward(const float* img1, const float* img2, float* per_sample, void* scratch,
                        int N, int H, int W, int window_size, float sigma, float val_range, void* stream);
 
+/* ---- VGG perceptual term (replaces VGGFeatureExtractor / PerceptualLoss, utils/losses.py:83-151) ----------------
+ * The feature network is a config list on the HOST: channels per 3x3 conv (+bias, +ReLU), -1 = MaxPool2d(2); the list must
+ * end on a conv (vgg19.features[:36] = {64,64,-1,128,128,-1,256,256,256,256,-1,512,512,512,512,-1,512,512,512,512}).
+ * `weights`: flat fp32 DEVICE arena (w0 [C0][3][3][3], b0 [C0], w1 [C1][C0][3][3], b1, ...) of mrisr_vgg_weight_elems()
+ * elements, i.e. torchvision's conv weights in order; they are frozen (utils/losses.py:98-99).  `packed`: bf16 operand copies
+ * made once by mrisr_vgg_pack_weights.  Images are N x 1 x H x W fp32 in [0,1]; the gray -> 3 channel repeat and the ImageNet
+ * normalisation (utils/losses.py:107-114) happen inside.  bf16 operands, fp32 accumulation (tcgen05); H, W multiples of
+ * 2^pools.  The workspace must be zero-filled once before its first use with a shape (zero-border invariant). */
+int64_t mrisr_vgg_weight_elems(const int* host_cfg, int ncfg);
+size_t  mrisr_vgg_packed_bytes(const int* host_cfg, int ncfg);
+int     mrisr_vgg_pack_weights(const float* weights, const int* host_cfg, int ncfg, void* packed, size_t packed_bytes, void* stream);
+size_t  mrisr_vgg_workspace_bytes(int N, int H, int W, const int* host_cfg, int ncfg, int grad);
+/* feat: N x C_last x H/2^pools x W/2^pools fp32 (VGGFeatureExtractor.forward) */
+int     mrisr_vgg_features(const void* packed, const float* weights, const float* img, float* feat, void* workspace,
+                           size_t workspace_bytes, int N, int H, int W, const int* host_cfg, int ncfg, void* stream);
+/* out1[0] = mean |f(pred) - f(target)| (loss_type 1) or mean (f(pred) - f(target))^2 (loss_type 2).
+ * dpred_accum (nullable): dpred_accum += grad_scale * d(out1)/d(pred), N x 1 x H x W fp32; NULL skips the backward chain and
+ * the workspace may then be sized with grad = 0. */
+int     mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, const float* pred, const float* target,
+                                     float* dpred_accum, float* out1, void* workspace, size_t workspace_bytes, int N, int H,
+                                     int W, const int* host_cfg, int ncfg, int loss_type, float grad_scale, void* stream);
+
 /* ---- fused Adam (replaces torch.optim.Adam(lr, weight_decay) of scripts/train.py:186,318) -- */
 /* L2 weight decay folded into the gradient (torch.optim.Adam semantics, not AdamW);
  * grad_scale multiplies g first (1/world_size for data parallel, 1/loss_scale for AMP). */

@@ -45,6 +45,14 @@ SIGNATURES = {
                                   c_size_t, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mrisr_conv2d_wgrad_bf16": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
                                         c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_vgg_weight_elems": (c_int64, [c_void_p, c_int]),
+    "mrisr_vgg_packed_bytes": (c_size_t, [c_void_p, c_int]),
+    "mrisr_vgg_pack_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
+    "mrisr_vgg_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_void_p, c_int, c_int]),
+    "mrisr_vgg_features": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                   c_void_p, c_int, c_void_p]),
+    "mrisr_vgg_perceptual_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                             c_int, c_int, c_int, c_void_p, c_int, c_int, c_float, c_void_p]),
     "mrisr_launch_count": (ctypes.c_longlong, []),
     "mrisr_prof_enable": (c_int, [c_int]),
     "mrisr_prof_report": (c_int, [c_char_p, c_size_t]),

@@ -67,7 +67,11 @@ struct ConvTcParams {
     int S;                  // padded pixels per sample (H + 2) * (W + 2)
     int H, W;
     int total_rows;         // N * S
-    int num_tiles;
+    int num_tiles;          // M tiles x n_blocks
+    int n_blocks;           // Cout / BN (> 1 only for Cout = 512: two 256-column blocks per pixel tile)
+    int ldc;                // channels per output row (= Cout)
+    int relu;               // epilogue: out = max(out, 0)                         (VGG conv + ReLU, utils/losses.py:95)
+    const __nv_bfloat16* mask;   // epilogue: out = mask > 0 ? out : 0, same layout as dst (ReLU backward fused into dgrad)
 };
 
 template <int BN, int BK>
@@ -125,7 +129,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                const int m0 = tile * 128;
+                const int m0 = (tile / p.n_blocks) * 128;
+                const int nb = tile % p.n_blocks;
                 for (int tap = 0; tap < p.taps; ++tap) {
                     const int shift = p.taps == 9 ? (tap / 3 - 1) * p.pw + (tap % 3 - 1) : 0;
                     for (int c = 0; c < cpt; ++c) {
@@ -134,7 +139,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                         uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
                         if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, m0 + shift);
                         else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, m0 + shift);
-                        tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * BN);
+                        tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * p.ldc + nb * BN);
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -177,13 +182,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             const int buf = it & 1;
             mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
             tc_fence_after_sync();
-            const int row = tile * 128 + q * 32 + lane;
+            const int mtile = tile / p.n_blocks, nb = tile - mtile * p.n_blocks;
+            const int row = mtile * 128 + q * 32 + lane;
             const int n = row / p.S;
             const int rem = row - n * p.S;
             const int y = rem / p.pw, x = rem - y * p.pw;
             const bool valid = row < p.total_rows && y >= 1 && y <= p.H && x >= 1 && x <= p.W;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
-            __nv_bfloat16* out = p.dst + (int64_t)row * BN;
+            __nv_bfloat16* out = p.dst + (int64_t)row * p.ldc + nb * BN;
+            const __nv_bfloat16* msk = p.mask ? p.mask + (int64_t)row * p.ldc + nb * BN : nullptr;
+            const float* bias = p.bias ? p.bias + nb * BN : nullptr;
             float s1[8], s2[8];
 #pragma unroll
             for (int g = 0; g < 8; ++g) s1[g] = s2[g] = 0.f;
@@ -191,9 +199,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             for (int c0 = 0; c0 < BN; c0 += 16) {
                 float v[16];
                 tmem_ld16(taddr + c0, v);
-                if (p.bias) {
+                if (bias) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += __ldg(p.bias + c0 + i);
+                    for (int i = 0; i < 16; ++i) v[i] += __ldg(bias + c0 + i);
+                }
+                if (p.relu) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+                }
+                if (msk && valid) {
+                    float m0[8], m1[8];
+                    load8(msk + c0, m0);
+                    load8(msk + c0 + 8, m1);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { v[i] = m0[i] > 0.f ? v[i] : 0.f; v[8 + i] = m1[i] > 0.f ? v[8 + i] : 0.f; }
                 }
                 if (valid) {
 #pragma unroll
@@ -326,8 +345,10 @@ int num_sms() {
 using bf16 = __nv_bfloat16;
 
 bool conv_tc_supported(int H, int W, int C1, int C2, int Cout, int ks) {
-    const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256;
-    return cout_ok && C1 >= 16 && C1 % 16 == 0 && C2 % 16 == 0 && (ks == 1 || ks == 3) && (int64_t)(H + 2) * (W + 2) >= 128;
+    const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256 || Cout == 512;
+    // (H+2)*(W+2) >= 128 is only needed by the GroupNorm-statistics epilogue (at most two samples per tile); the launcher
+    // rejects stat_part on smaller images
+    return cout_ok && C1 >= 16 && C1 % 16 == 0 && C2 % 16 == 0 && (ks == 1 || ks == 3) && H >= 1 && W >= 1;
 }
 
 int conv_tc_stat_elems(int N, int H, int W) {
@@ -358,15 +379,21 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     if (rc) return rc;
     if (C2) { rc = tc::make_tmap_2d_bf16(&tA2, a.src2.p, (uint64_t)rows, (uint64_t)C2, 128, (uint32_t)bk); if (rc) return rc; }
     else tA2 = tA1;
-    rc = tc::make_tmap_2d_bf16(&tB, a.w, (uint64_t)taps * Cout, (uint64_t)Cin, (uint32_t)Cout, (uint32_t)bk);
+    const int BN = Cout > 256 ? 256 : Cout;
+    rc = tc::make_tmap_2d_bf16(&tB, a.w, (uint64_t)taps * Cout, (uint64_t)Cin, (uint32_t)BN, (uint32_t)bk);
     if (rc) return rc;
+    if (a.stat_part && ((int64_t)(H + 2) * (W + 2) < 128 || Cout > 256)) {
+        set_error("conv_tc: GroupNorm statistics need (H+2)*(W+2) >= 128 and Cout <= 256");
+        return -2;
+    }
     tc::ConvTcParams p;
     p.dst = a.dst.p; p.bias = a.bias; p.stat_part = a.stat_part;
+    p.n_blocks = Cout / BN; p.ldc = Cout; p.relu = a.relu ? 1 : 0; p.mask = a.mask;
     p.chunks1 = C1 / bk; p.chunks2 = C2 / bk; p.taps = taps;
     p.pw = W + 2; p.S = (H + 2) * (W + 2); p.H = H; p.W = W;
-    p.total_rows = (int)rows; p.num_tiles = (int)((rows + 127) / 128);
+    p.total_rows = (int)rows; p.num_tiles = (int)((rows + 127) / 128) * p.n_blocks;
     const int grid = p.num_tiles < tc::num_sms() ? p.num_tiles : tc::num_sms();
-    switch (Cout) {
+    switch (BN) {
         case 16: return tc::launch_bn<16>(bk, tA1, tA2, tB, p, grid, s);
         case 32: return tc::launch_bn<32>(bk, tA1, tA2, tB, p, grid, s);
         case 64: return tc::launch_bn<64>(bk, tA1, tA2, tB, p, grid, s);

@@ -14,6 +14,8 @@ struct ConvArgs {
     Act<T> dst;           // C == Cout
     float* stat_part;     // [N][slots][8][2] partial (sum, sumsq) per GroupNorm group, or nullptr
     int ks;               // 1 or 3
+    bool relu = false;    // conv_tc only: ReLU in the epilogue (VGG conv + ReLU)
+    const T* mask = nullptr;   // conv_tc only: zero the output where mask <= 0 (same layout as dst; ReLU backward in dgrad)
 };
 // slots written per sample by launch_conv_generic for this shape
 int conv_generic_stat_slots(int H, int W, int Cout);

@@ -40,6 +40,7 @@ inline int layer_engine(const ConvDesc& c, int l, int H, int W) {
         return planar_ok && conv_ring_supported(h, w, c1, c2, c.cout, c.ks) && conv_ring_supported(h, w, c.cout, 0, c.cin, c.ks) &&
                        wgrad_ring_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_RING : ENG_GENERIC;
     }
+    if ((int64_t)(h + 2) * (w + 2) < 128 || c.cout > 256 || c.cin > 256) return ENG_GENERIC;   // GroupNorm-statistics epilogue: <= 2 samples per tile
     return conv_tc_supported(h, w, c1, c2, c.cout, c.ks) && conv_tc_supported(h, w, c.cout, 0, c.cin, c.ks) &&
                    wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_TC : ENG_GENERIC;
 }

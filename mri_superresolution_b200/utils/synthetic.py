@@ -16,3 +16,19 @@ def make_pairs(n: int, h: int, w: int, seed: int = 1234, rank: int = 0, device="
     hr = (hr - lo) / (hi - lo)
     lr = (F.avg_pool2d(hr, 2) + 0.02 * torch.randn(n, 1, h, w, generator=g)).clamp(0, 1)
     return lr.contiguous().to(device), hr.contiguous().to(device)
+
+
+VGG19_CONV_CHANNELS = [64, 64, 128, 128, 256, 256, 256, 256, 512, 512, 512, 512, 512, 512, 512, 512]
+
+
+def make_vgg19_weights(seed: int = 1235):
+    """Random stand-in for torchvision's ImageNet VGG19 convolution weights (the .pth is not on disk and there is no
+    network): torchvision's own ``vgg19(weights=None)`` initialisation (kaiming_normal_(fan_out, relu)), seeded.
+    Used by bench.py for the perceptual-loss workload (BASELINE.json configs[2]); same shapes, same FLOPs."""
+    g = torch.Generator("cpu").manual_seed(seed)
+    out, cin = [], 3
+    for cout in VGG19_CONV_CHANNELS:
+        std = (2.0 / (cout * 9)) ** 0.5
+        out.append((torch.randn((cout, cin, 3, 3), generator=g) * std, 0.05 * torch.randn((cout,), generator=g)))
+        cin = cout
+    return out

@@ -78,6 +78,28 @@ def vgg_features(vgg_params: Sequence[Tuple[torch.Tensor, torch.Tensor]], x: tor
     return x
 
 
+def vgg_features_bf16_storage(vgg_params: Sequence[Tuple[torch.Tensor, torch.Tensor]], x: torch.Tensor,
+                              cfg: Sequence = VGG19_CFG) -> torch.Tensor:
+    """vgg_features with every stored tensor (normalised input, weights, each conv + ReLU output) rounded to bf16 and fp32
+    arithmetic in between: the operand rounding of the tensor-core path, used by the GPU tests to measure the bf16 noise
+    floor of the perceptual gradient (test infrastructure only)."""
+    from oracle.unet_oracle import _q
+    if x.shape[1] == 1:
+        x = x.repeat(1, 3, 1, 1)
+    mean = torch.tensor(VGG_MEAN, dtype=x.dtype, device=x.device).view(1, 3, 1, 1)
+    std = torch.tensor(VGG_STD, dtype=x.dtype, device=x.device).view(1, 3, 1, 1)
+    x = _q((x - mean) / std)
+    i = 0
+    for item in cfg:
+        if item == "M":
+            x = F.max_pool2d(x, 2)
+        else:
+            w, b = vgg_params[i]
+            i += 1
+            x = _q(F.relu(F.conv2d(x, _q(w), b, padding=1)))
+    return x
+
+
 def make_vgg_params(seed: int = 1235, cfg: Sequence = VGG19_CFG) -> List[Tuple[torch.Tensor, torch.Tensor]]:
     """Random stand-in for the ImageNet VGG19 weights (the .pth is not on disk and there is no
     network): torchvision's own init for ``vgg19(weights=None)`` --

@@ -319,3 +319,74 @@ def test_full_size_forward_properties():
     # not bit-equal: the GroupNorm partial sums are grouped by 128-pixel tile, and a sample's tile alignment
     # depends on its position in the batch
     assert float((y[1:2] - y1).abs().max()) < 1e-2
+
+
+# ------------------------------------------------------------------ VGG19 perceptual branch (bf16 tensor-core path)
+def _feat_check(d, feat):
+    """feat against the golden summary (head values, norm, sum) written by oracle/make_golden.py:_store_tensor."""
+    f = feat.detach().double().cpu().reshape(-1)
+    head = torch.from_numpy(d["feat@head"]).double()
+    assert abs(float(f.norm()) - float(d["feat@norm"])) < 2e-2 * float(d["feat@norm"])
+    assert abs(float(f.sum()) - float(d["feat@sum"])) < 2e-2 * abs(float(d["feat@sum"])) + 1e-3 * float(d["feat@norm"])
+    assert float((f[: head.numel()] - head).abs().max()) < 3e-2 * max(float(head.abs().max()), float(f.abs().max()) * 0.1)
+
+
+def test_vgg_features_match_golden(golden_dir):
+    from mri_superresolution_b200.utils.perceptual import VGGFeatureExtractor
+    d = _golden(golden_dir, "perceptual")
+    vggp = LO.make_vgg_params(seed=1235)
+    ext = VGGFeatureExtractor(35, weights=vggp)
+    pred = torch.from_numpy(d["pred"]).to(_dev())
+    feat = ext(pred)
+    ref = LO.vgg_features(vggp, torch.from_numpy(d["pred"]))
+    assert feat.shape == ref.shape
+    # bf16 operands through 16 convolutions: relative L2 of the feature tensor
+    e = float((feat.cpu().double() - ref.double()).norm() / ref.double().norm())
+    assert e < 3e-2, e
+    _feat_check(d, feat)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_combined_loss_with_perceptual_matches_golden(golden_dir, tag):
+    """CombinedLoss with the perceptual term (utils/losses.py:229-236) against the reference run recorded in
+    tests/golden/perceptual.npz (same seeded VGG19 weights): loss within 1e-2 relative (bf16 mode tolerance), gradient
+    direction and size against the reference autograd gradient."""
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    d = _golden(golden_dir, "perceptual")
+    sw, pw, typ = [float(v) for v in d[f"{tag}:cfg"]]
+    crit = CombinedLoss(ssim_weight=sw, perceptual_weight=pw, perceptual_loss_type="l1" if typ == 1 else "mse",
+                        vgg_weights=LO.make_vgg_params(seed=1235))
+    p = torch.from_numpy(d["pred"]).to(_dev()).requires_grad_(True)
+    tgt = torch.from_numpy(d["target"]).to(_dev())
+    loss = crit(p, tgt)
+    loss.backward()
+    assert abs(loss.item() - float(d[f"{tag}:loss"])) < 1e-2 * abs(float(d[f"{tag}:loss"]))
+    g, r = p.grad.double().cpu().reshape(-1), torch.from_numpy(d[f"{tag}:grad"]).double().reshape(-1)
+    cos = float((g * r).sum() / (g.norm() * r.norm()))
+    # bf16 noise floor of this gradient: the same loss with bf16-rounded VGG operands (oracle restatement, fp32 arithmetic)
+    vggp = LO.make_vgg_params(seed=1235)
+    pq = torch.from_numpy(d["pred"]).clone().requires_grad_(True)
+    tq = torch.from_numpy(d["target"])
+    fq, ftq = LO.vgg_features_bf16_storage(vggp, pq), LO.vgg_features_bf16_storage(vggp, tq).detach()
+    perc_q = (fq - ftq).abs().mean() if typ == 1 else ((fq - ftq) ** 2).mean()
+    ((1 - sw - pw) * (pq - tq).abs().mean() + sw * (1 - LO.ssim(pq, tq).clamp(0, 1)) + pw * perc_q).backward()
+    gq = pq.grad.double().reshape(-1)
+    floor = float((gq * r).sum() / (gq.norm() * r.norm()))
+    assert cos > min(0.97, floor - 0.02), (cos, floor)
+    cos_q = float((g * gq).sum() / (g.norm() * gq.norm()))
+    assert cos_q > 0.9, cos_q                      # same operand rounding: only accumulation order / tie routing differ
+    assert abs(float(g.norm()) - float(r.norm())) < 0.1 * float(r.norm())
+
+
+def test_perceptual_target_branch_has_no_gradient_and_l2_alias(golden_dir):
+    from mri_superresolution_b200.utils.perceptual import PerceptualLoss
+    d = _golden(golden_dir, "perceptual")
+    vggp = LO.make_vgg_params(seed=1235)
+    pl2, pmse = PerceptualLoss(35, "l2", vgg_weights=vggp), PerceptualLoss(35, "mse", vgg_weights=vggp)
+    p = torch.from_numpy(d["pred"]).to(_dev()).requires_grad_(True)
+    t = torch.from_numpy(d["target"]).to(_dev()).requires_grad_(True)
+    a = pl2(p, t)
+    a.backward()
+    assert t.grad is None and p.grad is not None                  # utils/losses.py:146-147
+    assert abs(a.item() - pmse(p.detach(), t.detach()).item()) < 1e-6 * abs(a.item())   # :130 'l2' == 'mse'
+    assert pl2(p.detach(), p.detach()).item() == 0.0

@@ -158,3 +158,36 @@ def test_data_parallel_bucketed_allreduce_gloo_world2():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_perceptual_argument_validation_mirrors_reference():
+    """utils/losses.py:133 raises ValueError for an unknown perceptual loss type; the mirror also refuses feature stacks
+    that do not end on conv + ReLU (the reference default, idx 35 = relu5_4, does)."""
+    from oracle import losses_oracle as LO
+    from mri_superresolution_b200.utils.perceptual import PerceptualLoss, VGGFeatureExtractor
+    vggp = LO.make_vgg_params(seed=1235)
+    with pytest.raises(ValueError):
+        PerceptualLoss(35, "huber", vgg_weights=vggp)
+    with pytest.raises(ValueError):
+        VGGFeatureExtractor(36, weights=vggp)                     # ends on the last MaxPool
+    ext = VGGFeatureExtractor(35, weights=vggp)
+    assert ext.cfg == [64, 64, -1, 128, 128, -1, 256, 256, 256, 256, -1, 512, 512, 512, 512, -1, 512, 512, 512, 512]
+    assert len(ext.features) == 36 and not any(p.requires_grad for p in ext.features.parameters())
+    assert tuple(ext.mean.shape) == (1, 3, 1, 1) and tuple(ext.std.shape) == (1, 3, 1, 1)
+    with pytest.raises(RuntimeError):
+        ext(torch.zeros(1, 1, 32, 32))                            # CPU tensor: no fallback
+
+
+def test_vgg_abi_size_queries():
+    import ctypes
+    from mri_superresolution_b200 import _native
+    L = _native.lib()
+    cfg = [64, 64, -1, 128, 128, -1, 256, 256, 256, 256, -1, 512, 512, 512, 512, -1, 512, 512, 512, 512]
+    arr = (ctypes.c_int * len(cfg))(*cfg)
+    n_w = sum(co * ci * 9 + co for ci, co in zip([3] + [c for c in cfg if c > 0][:-1], [c for c in cfg if c > 0]))
+    assert L.mrisr_vgg_weight_elems(arr, len(cfg)) == n_w
+    assert L.mrisr_vgg_packed_bytes(arr, len(cfg)) > 2 * 2 * (n_w - sum(c for c in cfg if c > 0)) - 1
+    assert L.mrisr_vgg_workspace_bytes(2, 64, 64, arr, len(cfg), 1) > L.mrisr_vgg_workspace_bytes(2, 64, 64, arr, len(cfg), 0) > 0
+    assert L.mrisr_vgg_workspace_bytes(2, 40, 64, arr, len(cfg), 1) == 0             # H % 16 != 0
+    bad = (ctypes.c_int * 2)(64, -1)
+    assert L.mrisr_vgg_packed_bytes(bad, 2) == 0                                      # must end on a conv
