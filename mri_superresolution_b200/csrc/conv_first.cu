@@ -1,0 +1,184 @@
+// First convolution of the network, inc.double_conv.0 (models/unet_model.py:29,137): 3x3, ONE input channel -> f channels.
+// K = 9 is not a tensor-core shape and the layer is HBM-bound by its OUTPUT (2 B in, 2*f B out per pixel), so it runs on
+// CUDA cores with the planar-8 thread mapping of common.cuh (RowMap): a thread owns 8 output channels, keeps their 72
+// weights in registers and walks pixels; GroupNorm partial statistics come out of the same pass.  The weight gradient
+//   dW[co][tap] = sum_p X[p + shift(tap)] * dY[p][co]
+// uses the same mapping with 72 accumulators per thread and a fixed-order block / grid reduction (deterministic).
+// bf16 + planar output only; the fp32 parity mode keeps conv_generic.cu.
+#include "kernels.cuh"
+
+namespace mrisr {
+namespace {
+using bf16 = __nv_bfloat16;
+constexpr int NTHR = 256;
+constexpr int kUnitsFwd = 16, kUnitsBwd = 64;
+
+// x: [N][H+2][W+2][1] (zero border), w: packed [tap][1][Cout] bf16, dst planar-8 [Cout]
+__global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf16* __restrict__ w, Act<bf16> dst,
+                                                          float* __restrict__ stat_part, int rows_pb) {
+    __shared__ float s_red[2][NTHR * 8];
+    __shared__ float s_ch[2][512];
+    const int C = dst.C, nv = C / 8, tid = threadIdx.x, n = blockIdx.y;
+    const RowMap m = row_map(dst, NTHR, tid);
+    float s1[8], s2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+    if (m.active) {
+        float wr[9][8];
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) wr[t][k] = to_f(w[t * C + m.cv * 8 + k]);
+        const int pw = x.W + 2;
+        const int y_end = min(dst.H, (int)(blockIdx.x + 1) * rows_pb);
+        for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
+            const bf16* xr = x.p + x.pix(n, y, 0);                  // padded-linear index of (y, 0); taps read +-1 row / col
+            for (int xx = m.x0; xx < dst.W; xx += m.xstep) {
+                float v[9];
+#pragma unroll
+                for (int t = 0; t < 9; ++t) v[t] = to_f(xr[xx + (t / 3 - 1) * pw + (t % 3 - 1)]);
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    float acc = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 9; ++t) acc = fmaf(v[t], wr[t][k], acc);
+                    o[k] = acc;
+                    s1[k] += acc;
+                    s2[k] = fmaf(acc, acc, s2[k]);
+                }
+                store8(dst.at(n, y, xx, m.cv * 8), o);
+            }
+        }
+    }
+    if (!stat_part) return;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s_red[0][tid * 8 + k] = s1[k]; s_red[1][tid * 8 + k] = s2[k]; }
+    __syncthreads();
+    const int cnt = NTHR / nv;                                       // planar mapping: threads [cv*cnt, (cv+1)*cnt) share cv
+    for (int i = tid; i < 2 * C; i += NTHR) {
+        const int which = i / C, c = i % C, cv = c >> 3, k = c & 7;
+        float t = 0.f;
+        for (int j = 0; j < cnt; ++j) t += s_red[which][(cv * cnt + j) * 8 + k];
+        s_ch[which][c] = t;
+    }
+    __syncthreads();
+    if (tid < 2 * kGroups) {
+        const int which = tid / kGroups, g = tid % kGroups, gs = C / kGroups;
+        float t = 0.f;
+        for (int c = g * gs; c < (g + 1) * gs; ++c) t += s_ch[which][c];
+        stat_part[(((int64_t)n * gridDim.x + blockIdx.x) * kGroups + g) * 2 + which] = t;
+    }
+}
+
+// partial[(n * slots + slot)][tap][C] = block sums of X[p + shift(tap)] * dY[p][c]
+__global__ void __launch_bounds__(NTHR) wgrad_first_kernel(Act<bf16> x, Act<bf16> dy, float* __restrict__ partial, int rows_pb) {
+    __shared__ float s_w[NTHR / 32][72];
+    const int C = dy.C, nv = C / 8, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n = blockIdx.y;
+    const RowMap m = row_map(dy, NTHR, tid);
+    float acc[9][8];
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[t][k] = 0.f;
+    if (m.active) {
+        const int pw = x.W + 2;
+        const int y_end = min(dy.H, (int)(blockIdx.x + 1) * rows_pb);
+        for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
+            const bf16* xr = x.p + x.pix(n, y, 0);
+            for (int xx = m.x0; xx < dy.W; xx += m.xstep) {
+                float g[8], v[9];
+                load8(dy.at(n, y, xx, m.cv * 8), g);
+#pragma unroll
+                for (int t = 0; t < 9; ++t) v[t] = to_f(xr[xx + (t / 3 - 1) * pw + (t % 3 - 1)]);
+#pragma unroll
+                for (int t = 0; t < 9; ++t)
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[t][k] = fmaf(v[t], g[k], acc[t][k]);
+            }
+        }
+    }
+    // a warp's lanes share the channel vector (threads per plane is a multiple of 32): butterfly, then across warps
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float v = acc[t][k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) s_w[wid][t * 8 + k] = v;
+        }
+    __syncthreads();
+    const int wpc = (NTHR / 32) / nv;                                // warps per channel vector
+    float* out = partial + ((int64_t)n * gridDim.x + blockIdx.x) * 9 * C;
+    for (int i = tid; i < 9 * C; i += NTHR) {
+        const int t = i / C, c = i % C, cv = c >> 3, k = c & 7;
+        float v = 0.f;
+        for (int j = 0; j < wpc; ++j) v += s_w[cv * wpc + j][t * 8 + k];
+        out[t * C + c] = v;
+    }
+}
+
+// dw[co][0][tap] = sum over blocks of partial[b][tap][co]
+__global__ void __launch_bounds__(256) wgrad_first_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw,
+                                                                 int nblocks, int C) {
+    __shared__ double s_w[8];
+    const int i = blockIdx.x;                                        // tap * C + co
+    double t = 0.0;
+    for (int b = threadIdx.x; b < nblocks; b += 256) t += (double)partial[(int64_t)b * 9 * C + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double v = 0.0;
+        for (int w = 0; w < 8; ++w) v += s_w[w];
+        const int tap = i / C, co = i % C;
+        dw[co * 9 + tap] = (float)v;
+    }
+}
+}  // namespace
+
+bool conv_first_supported(const Act<__nv_bfloat16>& src, const Act<__nv_bfloat16>& dst, int ks) {
+    const int nv = dst.C / 8;
+    return ks == 3 && src.C == 1 && dst.planar() && dst.C % 8 == 0 && dst.C <= 64 && (NTHR / nv) % 32 == 0 && NTHR % nv == 0;
+}
+int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsFwd)); }
+size_t wgrad_first_scratch_elems(int N, int H, int W, int Cout) {
+    return (size_t)N * ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsBwd)) * 9 * Cout;
+}
+
+int launch_conv_first(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s) {
+    if (!conv_first_supported(a.src1, a.dst, a.ks) || a.src2.p || a.bias) { set_error("conv_first: unsupported arguments"); return -2; }
+    const char* tag = "conv_first";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "conv_first:k3:1>%d@%dx%d", a.dst.C, a.dst.H, a.dst.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
+    const int rpb = rows_per_block(a.dst.W, a.dst.C / 8, NTHR, kUnitsFwd);
+    conv_first_kernel<<<dim3(ceil_div(a.dst.H, rpb), a.dst.N), NTHR, 0, s>>>(a.src1, a.w, a.dst, a.stat_part, rpb);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_wgrad_first(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s) {
+    if (!conv_first_supported(a.src1, a.dy, a.ks) || a.src2.p) { set_error("wgrad_first: unsupported arguments"); return -2; }
+    const char* tag = "wgrad_first";
+    char tbuf[96];
+    if (prof_on()) {
+        snprintf(tbuf, sizeof(tbuf), "wgrad_first:k3:1>%d@%dx%d", a.dy.C, a.dy.H, a.dy.W);
+        tag = prof_intern(tbuf);
+    }
+    ProfScope prof_(tag, s);
+    const int rpb = rows_per_block(a.dy.W, a.dy.C / 8, NTHR, kUnitsBwd);
+    const int slots = ceil_div(a.dy.H, rpb);
+    wgrad_first_kernel<<<dim3(slots, a.dy.N), NTHR, 0, s>>>(a.src1, a.dy, a.partial, rpb);
+    MRISR_LAUNCH_CHECK();
+    wgrad_first_reduce_kernel<<<9 * a.dy.C, 256, 0, s>>>(a.partial, a.dw, slots * a.dy.N, a.dy.C);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mrisr

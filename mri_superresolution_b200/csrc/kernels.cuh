@@ -36,6 +36,14 @@ template <typename T> int launch_wgrad_generic(const WgradArgs<T>& a, cudaStream
 template <typename T>
 int launch_pack_weights(const float* w, T* w_fwd, T* w_dgrad, int Cout, int Cin, int ks, cudaStream_t s);
 
+// ---------------------------------------------------------------- first layer, 1 -> f channels (conv_first.cu), bf16 + planar output
+// ConvArgs::w is the generic pack [tap][1][Cout]; stat_part receives [N][conv_first_stat_slots][8][2] for launch_gn_finalize
+bool conv_first_supported(const Act<__nv_bfloat16>& src, const Act<__nv_bfloat16>& dst, int ks);
+int conv_first_stat_slots(int H, int W, int Cout);
+size_t wgrad_first_scratch_elems(int N, int H, int W, int Cout);
+int launch_conv_first(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s);
+int launch_wgrad_first(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
+
 // ---------------------------------------------------------------- tcgen05 convolution (conv_tc.cu, wgrad_tc.cu), bf16 only
 // ConvArgs::w is the K-major pack of launch_pack_weights_tc ([tap][Cout][Cin] forward, [tap'][Cin][Cout] dgrad);
 // ConvArgs::stat_part receives [tiles][2][8][2] partials (conv_tc_stat_elems floats) consumed by launch_gn_finalize_tc.

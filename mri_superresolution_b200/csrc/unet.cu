@@ -97,6 +97,10 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         part_max = std::max(part_max, (size_t)N * slots * kGroups * 2);
         part_max = std::max(part_max, (size_t)conv_tc_stat_elems(N, h, w));
         part_max = std::max(part_max, (size_t)conv_ring_stat_elems(N, h, w, c.cin, c.cout));
+        if (l == 0) {
+            part_max = std::max(part_max, (size_t)N * conv_first_stat_slots(h, w, c.cout) * kGroups * 2);
+            wg_max = std::max(wg_max, wgrad_first_scratch_elems(N, h, w, c.cout));
+        }
         gnp_max = std::max(gnp_max, (size_t)N * gn_bwd_slots(h, w, c.cout) * 3 * (c.cout + 8));
         wg_max = std::max(wg_max, wgrad_generic_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
         if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_TC) {

@@ -25,6 +25,12 @@ struct Runner {
         a.bias = c.bias >= 0 ? P(c.bias) : nullptr;
         a.dst = dst; a.stat_part = want_stats ? ws.stat_part : nullptr; a.ks = c.ks;
         if constexpr (sizeof(T) == 2) {
+            if (l == 0 && conv_first_supported(src1, dst, c.ks)) {
+                TRY(launch_conv_first(a, s));
+                if (want_stats) TRY(launch_gn_finalize(ws.stat_part, ws.stats[l], ws.N, conv_first_stat_slots(dst.H, dst.W, dst.C),
+                                                       (double)(dst.C / kGroups) * dst.H * dst.W, s));
+                return 0;
+            }
             if (eng(l) != ENG_GENERIC) {
                 const double count = (double)(dst.C / kGroups) * dst.H * dst.W;
                 if (eng(l) == ENG_RING) {
@@ -135,10 +141,12 @@ struct Runner {
         w.src1 = src1; w.src2 = src2; w.dy = dy; w.dw = GP(c.w); w.partial = ws.wg_part; w.ks = c.ks;
         const int e = eng(l);
         const bool use_tc = e != ENG_GENERIC;
+        bool done = false;
         if constexpr (sizeof(T) == 2) {
-            if (use_tc) TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s));
+            if (use_tc) { TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s)); done = true; }
+            else if (l == 0 && conv_first_supported(src1, dy, c.ks)) { TRY(launch_wgrad_first(w, s)); done = true; }
         }
-        if (!use_tc) TRY(launch_wgrad_generic<T>(w, s));
+        if (!done) TRY(launch_wgrad_generic<T>(w, s));
         if (want_dgrad) {
             ConvArgs<T> a;
             a.src1 = dy; a.src2 = none; a.w = ws.wd[l]; a.bias = nullptr; a.dst = ws.G[l]; a.stat_part = nullptr; a.ks = c.ks;
