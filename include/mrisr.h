@@ -133,7 +133,8 @@ size_t mrisr_conv2d_scratch_bytes(int N, int H, int W, int C1, int C2, int Cout,
 int mrisr_conv2d_bf16(const void* src1, int C1, const void* src2, int C2, const float* w, const float* bias, void* dst,
                       float* stats, void* scratch, size_t scratch_bytes, int N, int H, int W, int Cout, int ks,
                       int transposed, int engine, void* stream);
-/* dw: fp32 [Cout][C1+C2][ks][ks], overwritten with sum over pixels of in (x) dy; dy must have a zero border (and, for
+/* engine 3 (weight gradient only): row-structured tcgen05 kernel over the same planar-8 allocations as engine 2.
+ * dw: fp32 [Cout][C1+C2][ks][ks], overwritten with sum over pixels of in (x) dy; dy must have a zero border (and, for
  * engine 2, zero guard pixels: the reduction runs over whole 128-pixel blocks; the guards of src1/src2 must be finite). */
 int mrisr_conv2d_wgrad_bf16(const void* src1, int C1, const void* src2, int C2, const void* dy, float* dw, void* scratch,
                             size_t scratch_bytes, int N, int H, int W, int Cout, int ks, int engine, void* stream);

@@ -32,6 +32,10 @@ struct Scratch {
             const size_t t = wgrad_ring_scratch_elems(N, H, W, C1 + C2, Cout, ks);
             we = we > t ? we : t;
         }
+        if (wgrad_rows_supported(N, H, W, C1, C2, Cout, ks)) {
+            const size_t t = wgrad_rows_scratch_elems(N, H, W, C1 + C2, Cout);
+            we = we > t ? we : t;
+        }
         part = (float*)c.take((pe > we ? pe : we) * sizeof(float));
         bytes = c.used;
     }
@@ -40,7 +44,7 @@ struct Scratch {
 // (C/8 planes of planar_plane() pixels x 8 channels, pixel 0 sits planar_guard() pixels into each plane).
 Act<bf16> act(const void* p, int N, int H, int W, int C, int engine = 0) {
     Act<bf16> a{(bf16*)p, N, H, W, C};
-    if (engine == 2) {
+    if (engine == 2 || engine == 3) {
         a.ps = 8;
         a.cs = planar_plane(a.rows(), W) * 8;
         a.p = (bf16*)p + planar_guard(W) * 8;
@@ -112,6 +116,7 @@ int mrisr_conv2d_wgrad_bf16(const void* src1, int C1, const void* src2, int C2, 
     a.src1 = act(src1, N, H, W, C1, engine);
     a.src2 = src2 ? act(src2, N, H, W, C2, engine) : Act<bf16>{nullptr, 0, 0, 0, 0};
     a.dy = act(dy, N, H, W, Cout, engine); a.dw = dw; a.partial = sc.part; a.ks = ks;
+    if (engine == 3) return launch_wgrad_rows(a, s);          // row-structured weight gradient (planar-8, as engine 2)
     if (engine == 2) return launch_wgrad_ring(a, s);
     return engine == 1 ? launch_wgrad_tc(a, s) : launch_wgrad_generic<bf16>(a, s);
 }

@@ -63,6 +63,10 @@ int launch_pack_weights_ring(const float* w, __nv_bfloat16* wf, __nv_bfloat16* w
 bool wgrad_ring_supported(int H, int W, int C1, int C2, int Cout, int ks);
 size_t wgrad_ring_scratch_elems(int N, int H, int W, int Cin, int Cout, int ks);
 int launch_wgrad_ring(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
+// row-structured weight gradient (wgrad_rows.cu): vertical taps folded into M; preferred over wgrad_ring when supported
+bool wgrad_rows_supported(int N, int H, int W, int C1, int C2, int Cout, int ks);
+size_t wgrad_rows_scratch_elems(int N, int H, int W, int Cin, int Cout);
+int launch_wgrad_rows(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
 bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks);
 size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks);
 int launch_wgrad_tc(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);

@@ -107,8 +107,10 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
             const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin;
             wg_max = std::max(wg_max, wgrad_tc_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c1, c.cin - c1, c.cout, c.ks));
         }
-        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_RING)
+        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_RING) {
             wg_max = std::max(wg_max, wgrad_ring_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
+            wg_max = std::max(wg_max, wgrad_rows_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout));
+        }
     }
     UB = make_act(ar, -1, f);
     XM = make_act(ar, -1, f / 2);

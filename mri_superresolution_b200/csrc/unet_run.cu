@@ -143,7 +143,12 @@ struct Runner {
         const bool use_tc = e != ENG_GENERIC;
         bool done = false;
         if constexpr (sizeof(T) == 2) {
-            if (use_tc) { TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s)); done = true; }
+            if (use_tc) {
+                const int c2 = src2.p ? src2.C : 0;
+                if (e == ENG_RING && wgrad_rows_supported(dy.N, dy.H, dy.W, src1.C, c2, dy.C, c.ks)) TRY(launch_wgrad_rows(w, s));
+                else TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s));
+                done = true;
+            }
             else if (l == 0 && conv_first_supported(src1, dy, c.ks)) { TRY(launch_wgrad_first(w, s)); done = true; }
         }
         if (!done) TRY(launch_wgrad_generic<T>(w, s));

@@ -93,10 +93,10 @@ def run_wgrad(x1, x2, dy, ks, engine):
     cout = dy.shape[1]
     sb = L.mrisr_conv2d_scratch_bytes(n, h, wd, c1, c2, cout, ks)
     scratch = torch.empty(sb, dtype=torch.uint8, device=x1.device)
-    conv = to_planar if engine == 2 else pad_nhwc
+    conv = to_planar if engine >= 2 else pad_nhwc
     p1, p2 = conv(x1), (conv(x2) if x2 is not None else None)
     # the reduction runs over whole 128-pixel blocks: dY must be zero on its border AND in its guard pixels
-    pdy = to_planar(dy, fill_guard=False) if engine == 2 else pad_nhwc(dy)
+    pdy = to_planar(dy, fill_guard=False) if engine >= 2 else pad_nhwc(dy)
     dw = torch.zeros(cout, c1 + c2, ks, ks, device=x1.device)
     rc = L.mrisr_conv2d_wgrad_bf16(_native.ptr(p1), c1, _native.ptr(p2), c2, _native.ptr(pdy), _native.ptr(dw),
                                    _native.ptr(scratch), sb, n, h, wd, cout, ks, engine, _native.stream_ptr())
@@ -247,5 +247,36 @@ def test_conv_ring_wgrad(shape):
     wref = torch.zeros(cout, c1 + c2, ks, ks, dtype=torch.float64, device=_dev(), requires_grad=True)
     F.conv2d(xin, wref, None, padding=ks // 2).backward(bf(dy).double())
     dw = run_wgrad(x1, x2, dy, ks, 2)
+    e = rel_inf(dw, wref.grad.float())
+    assert e < 2e-3, (shape, e)
+
+
+# row-structured weight gradient (engine 3): (N, H, W, C1, C2, Cout)
+ROWS_SHAPES = [
+    (2, 16, 16, 16, 0, 16),
+    (3, 24, 40, 32, 0, 32),
+    (2, 40, 24, 32, 32, 32),       # skip-concat: two plane groups
+    (2, 32, 32, 32, 0, 64),
+    (2, 48, 48, 32, 0, 16),
+    (1, 128, 128, 16, 0, 16),
+    (2, 64, 64, 64, 0, 32),        # 64-channel source: two groups of four planes
+    (5, 32, 16, 16, 16, 64),
+    (1, 64, 256, 16, 0, 16),       # two 128-pixel tiles per row segment
+    (1, 24, 512, 32, 0, 16),       # two column strips
+    (70, 16, 16, 16, 0, 32),       # many units per CTA
+]
+
+
+@pytest.mark.parametrize("shape", ROWS_SHAPES)
+def test_wgrad_rows(shape):
+    n, h, w, c1, c2, cout = shape
+    g = torch.Generator("cpu").manual_seed(11 + hash(shape) % 1000)
+    x1 = torch.randn(n, c1, h, w, generator=g).to(_dev())
+    x2 = torch.randn(n, c2, h, w, generator=g).to(_dev()) if c2 else None
+    dy = torch.randn(n, cout, h, w, generator=g).to(_dev())
+    xin = (bf(x1) if x2 is None else torch.cat([bf(x1), bf(x2)], 1)).double()
+    wref = torch.zeros(cout, c1 + c2, 3, 3, dtype=torch.float64, device=_dev(), requires_grad=True)
+    F.conv2d(xin, wref, None, padding=1).backward(bf(dy).double())
+    dw = run_wgrad(x1, x2, dy, 3, 3)
     e = rel_inf(dw, wref.grad.float())
     assert e < 2e-3, (shape, e)
