@@ -57,6 +57,32 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
 }
 
 // ---------------------------------------------------------------- device
+__device__ __forceinline__ bool elect_one_c() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void umma_lohi_c(uint32_t tmem_d, uint32_t alo, uint32_t blo, uint32_t hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 p, %5, 0;\n"
+        "mov.b64 da, {%1, %3};\n"
+        "mov.b64 db, {%2, %3};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+        "}\n"
+        ::"r"(tmem_d), "r"(alo), "r"(blo), "r"(hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 struct ConvTcParams {
     __nv_bfloat16* dst;     // padded origin of the output tensor (Cout = BN channels per row)
     const float* bias;      // [BN] or nullptr
@@ -146,32 +172,31 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-                const int buf = it & 1;
-                mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
+        // ===== MMA issuer: warp-uniform loop, one elected lane issues; descriptor = constant hi word + (base lo + one add) =====
+        constexpr uint32_t DESC_HI = ((SBO >> 4) & 0x3FFFu) | (1u << 14) | ((LT & 7u) << 29);
+        const uint32_t a_lo0 = (1u << 16) | (smem_u32(smem) >> 4);                       // LBO = 16 B (unused for swizzled K-major)
+        const uint32_t b_lo0 = a_lo0 + (Cfg::A_BYTES >> 4);
+        int stage = 0;
+        uint32_t phase = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t d = tmem_base + (uint32_t)(buf * BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
                 tc_fence_after_sync();
-                const uint32_t d = tmem_base + (uint32_t)(buf * BN);
-                for (int kb = 0; kb < num_kb; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after_sync();
-                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-                    const uint32_t b_addr = a_addr + Cfg::A_BYTES;
+                if (elect_one_c()) {
+                    const uint32_t so = (uint32_t)stage * (uint32_t)(Cfg::STAGE_BYTES >> 4);
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
-                        const uint64_t adesc = make_smem_desc(a_addr + k * 32, 16, SBO, LT);
-                        const uint64_t bdesc = make_smem_desc(b_addr + k * 32, 16, SBO, LT);
-                        umma_bf16(d, adesc, bdesc, IDESC, (kb | k) != 0 ? 1u : 0u);
-                    }
+                    for (int k = 0; k < BK / 16; ++k)
+                        umma_lohi_c(d, a_lo0 + so + (uint32_t)(k * 2), b_lo0 + so + (uint32_t)(k * 2), DESC_HI, IDESC, (kb | k) != 0 ? 1u : 0u);
                     umma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs have read it
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tfull_bar[buf]);                // accumulator complete -> epilogue
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
+            if (elect_one_c()) umma_commit(&tfull_bar[buf]);    // accumulator complete -> epilogue
         }
     } else {
         // ===== epilogue: 4 warps, warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32) =====

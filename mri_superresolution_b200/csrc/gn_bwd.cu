@@ -8,6 +8,7 @@
 // pass accumulates per channel  s1 = sum dz,  s2r = sum dz*r  (raw r);  the finalize forms  sum dz*xh = rstd*(s2r - mean*s1),
 // m1, m2 and the per-(n, group) constants  q = -rstd*m1 + mean*rstd^2*m2,  p = -rstd^2*m2,  and the apply pass is
 //   dr = sc*dz + p*r + q.
+#include <stdlib.h>
 #include "kernels.cuh"
 
 namespace mrisr {
@@ -15,6 +16,20 @@ namespace {
 constexpr int NTHR = 256;
 constexpr int UNITS_PER_THREAD = 32;
 constexpr int FTHR = 256;         // threads of the finalize kernel
+
+// Optional chunking of the batch (MRISR_GNBWD_CHUNK_MB > 0): reduce + apply run per chunk of samples whose (r, g, dr) fit
+// the given size, hoping for L2 hits in the apply pass.  Measured on B200 (batch 64, profiles/r01_gn_bwd_chunking.md): every
+// chunk size was SLOWER than one pass over the whole batch (launch gaps and tails of the short kernels outweigh the saved
+// HBM reads), so the default is off; the knob stays for experiments.
+inline double gn_bwd_chunk_bytes() {
+    static double v = -1.0;
+    if (v < 0.0) {
+        const char* e = getenv("MRISR_GNBWD_CHUNK_MB");
+        v = e ? atof(e) * 1048576.0 : 0.0;
+        if (v <= 0.0) v = 1e15;
+    }
+    return v;
+}
 
 template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
 
@@ -107,13 +122,13 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
 // part layout: [N][slots][3][C+8]  (row 0: sum dz, row 1: sum dz*r (raw), row 2: SRC_OUTER sum dl*act; column C: sum dl)
 // One block = `rows_pb` unit rows of one sample; thread mapping per common.cuh RowMap (coalesced for both layouts).
 template <typename T, int KIND>
-__global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int rows_pb) {
+__global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int rows_pb, int n0) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
     __shared__ float s_red[3][NTHR * 8];
     __shared__ float s_dl[NTHR];
     const int C = a.r.C, nv = C / 8;
     const int tid = threadIdx.x;
-    const int n = blockIdx.y;
+    const int n = n0 + blockIdx.y;
     const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
     const RowMap m = row_map(a.r, NTHR, tid);
     float s1[8], s2[8], s3[8], sdl = 0.f;
@@ -176,14 +191,16 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int
 
 // blocks [0, N*8): the apply constants (q, p) per (n, group).  blocks [N*8, N*8 + C): per-channel parameter gradients.
 template <typename T, int KIND>
-__global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_count) {
+__global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, int slots, double inv_count, int n0, int nn, int do_params) {
     __shared__ double s_w[4][FTHR / 32];
     const int C = a.r.C, gs = C / kGroups, N = a.r.N;
     const int64_t row = (int64_t)(C + 8);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, tid = threadIdx.x;
-    if ((int)blockIdx.x < N * kGroups) {
-        const int n = blockIdx.x / kGroups, g = blockIdx.x % kGroups;
-        const double mean = (double)a.stats[blockIdx.x * 2], rstd = (double)a.stats[blockIdx.x * 2 + 1];
+    if (!do_params) {
+        const int n = n0 + blockIdx.x / kGroups, g = blockIdx.x % kGroups;
+        const int ng = n * kGroups + g;
+        if (n >= n0 + nn) return;
+        const double mean = (double)a.stats[ng * 2], rstd = (double)a.stats[ng * 2 + 1];
         double m1 = 0.0, m2 = 0.0;
         for (int i = tid; i < slots * gs; i += FTHR) {
             const int s = i / gs, ch = g * gs + i % gs;
@@ -204,13 +221,13 @@ __global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, i
             for (int w = 0; w < FTHR / 32; ++w) { m1 += s_w[0][w]; m2 += s_w[1][w]; }
             m1 *= inv_count;
             m2 *= rstd * inv_count;                       // mean_g(gamma * dz * xh)
-            a.mstat[blockIdx.x * 2] = (float)(-rstd * m1 + mean * rstd * rstd * m2);      // q
-            a.mstat[blockIdx.x * 2 + 1] = (float)(-rstd * rstd * m2);                      // p
+            a.mstat[ng * 2] = (float)(-rstd * m1 + mean * rstd * rstd * m2);      // q
+            a.mstat[ng * 2 + 1] = (float)(-rstd * rstd * m2);                      // p
         }
     } else {
         // one block per parameter channel pc; raw channels mapping to it: [pc*rep, (pc+1)*rep)
         const int rep = KIND == SRC_BLEND_PS ? 4 : 1;
-        const int pc = blockIdx.x - N * kGroups;
+        const int pc = blockIdx.x;
         double d1 = 0.0, d2 = 0.0, d3 = 0.0, d4 = 0.0;
         for (int i = tid; i < N * slots * rep; i += FTHR) {
             const int ch = pc * rep + i % rep;
@@ -247,11 +264,11 @@ __global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, i
 }
 
 template <typename T, int KIND>
-__global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int rows_pb) {
+__global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int rows_pb, int n0) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
     const int C = a.r.C, gs = C / kGroups;
     const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
-    const int n = blockIdx.y;
+    const int n = n0 + blockIdx.y;
     const RowMap m = row_map(a.r, NTHR, threadIdx.x);
     if (!m.active) return;
     ChanCtx c;
@@ -298,16 +315,25 @@ int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
     const int rows_pb = rows_per_block(UW, nv, NTHR, UNITS_PER_THREAD);
     const int slots = ceil_div(UH, rows_pb);
-    dim3 grid(slots, a.r.N);
-    gn_bwd_reduce_kernel<T, KIND><<<grid, NTHR, 0, s>>>(a, rows_pb);
-    MRISR_LAUNCH_CHECK();
     const int pcs = KIND == SRC_BLEND_PS ? C / 4 : C;
     const double inv_count = 1.0 / ((double)(C / kGroups) * a.r.H * a.r.W);
-    gn_bwd_finalize_kernel<T, KIND><<<a.r.N * kGroups + pcs, FTHR, 0, s>>>(a, slots, inv_count);
-    MRISR_LAUNCH_CHECK();
     const int rows_ap = rows_per_block(UW, nv, NTHR, 8);
-    dim3 grid2(ceil_div(UH, rows_ap), a.r.N);
-    gn_bwd_apply_kernel<T, KIND><<<grid2, NTHR, 0, s>>>(a, rows_ap);
+    // Samples are processed in chunks small enough for the r / g tensors of a chunk to stay in L2 between the reduce pass
+    // and the apply pass (GroupNorm couples a whole sample, so the two passes cannot be one): 5 -> 3 HBM passes.
+    const double sample_bytes = 3.0 * sizeof(T) * (double)C * a.r.H * a.r.W;          // r + g read, dr written
+    const double chunk_d = gn_bwd_chunk_bytes() / sample_bytes;
+    int chunk = chunk_d >= (double)a.r.N ? a.r.N : (int)chunk_d;
+    if (chunk < 1) chunk = 1;
+    for (int n0 = 0; n0 < a.r.N; n0 += chunk) {
+        const int nn = a.r.N - n0 < chunk ? a.r.N - n0 : chunk;
+        gn_bwd_reduce_kernel<T, KIND><<<dim3(slots, nn), NTHR, 0, s>>>(a, rows_pb, n0);
+        MRISR_LAUNCH_CHECK();
+        gn_bwd_finalize_kernel<T, KIND><<<nn * kGroups, FTHR, 0, s>>>(a, slots, inv_count, n0, nn, 0);
+        MRISR_LAUNCH_CHECK();
+        gn_bwd_apply_kernel<T, KIND><<<dim3(ceil_div(UH, rows_ap), nn), NTHR, 0, s>>>(a, rows_ap, n0);
+        MRISR_LAUNCH_CHECK();
+    }
+    gn_bwd_finalize_kernel<T, KIND><<<pcs, FTHR, 0, s>>>(a, slots, inv_count, 0, a.r.N, 1);
     MRISR_LAUNCH_CHECK();
     return 0;
 }

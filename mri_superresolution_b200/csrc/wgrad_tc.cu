@@ -16,6 +16,33 @@ namespace tc {
 
 int num_sms();
 
+
+__device__ __forceinline__ bool elect_one_t() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void umma_lohi_t(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                            uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n"
+        ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 constexpr int kBKP = 64;          // pixels (GEMM K) per pipeline stage
 
 struct WgradTcParams {
@@ -93,29 +120,36 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kb = kb_begin; kb < kb_end; ++kb) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after_sync();
-                const uint32_t a_base = smem_u32(smem + (size_t)stage * p.stage_bytes);
-                const uint32_t b_base = a_base + (uint32_t)p.MT * p.a_tile_bytes;
+        // warp-uniform issue loop; a descriptor is (constant hi word, lo word = base + one add)
+        const uint32_t a_hi = ((p.sbo_a >> 4) & 0x3FFFu) | (1u << 14) | ((p.lt_a & 7u) << 29);
+        const uint32_t b_hi = ((p.sbo_b >> 4) & 0x3FFFu) | (1u << 14) | ((p.lt_b & 7u) << 29);
+        const uint32_t a_lo0 = (((p.lbo_a >> 4) & 0x3FFFu) << 16) | (smem_u32(smem) >> 4);
+        const uint32_t b_lo0 = (((p.lbo_b >> 4) & 0x3FFFu) << 16) | ((smem_u32(smem) + (uint32_t)p.MT * p.a_tile_bytes) >> 4);
+        const uint32_t stage16 = p.stage_bytes >> 4, tile16 = p.a_tile_bytes >> 4;
+        const uint32_t ka16 = (2u * p.sbo_a) >> 4, kb16 = (2u * p.sbo_b) >> 4;
+        int mt_valid = 0;
+        for (int j = 0; j < p.MT; ++j) if ((tile0 + j) * SPT < p.num_slabs) ++mt_valid;
+        const uint32_t bn = (uint32_t)p.BN, idesc = p.idesc;
+        int stage = 0;
+        uint32_t phase = 0, acc = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after_sync();
+            if (elect_one_t()) {
+                const uint32_t a0 = a_lo0 + (uint32_t)stage * stage16, b0 = b_lo0 + (uint32_t)stage * stage16;
 #pragma unroll
                 for (int k = 0; k < kBKP / 16; ++k) {
-                    const uint64_t bdesc = make_smem_desc(b_base + (uint32_t)k * 2u * p.sbo_b, p.lbo_b, p.sbo_b, p.lt_b);
-                    for (int j = 0; j < p.MT; ++j) {
-                        if ((tile0 + j) * SPT >= p.num_slabs) break;
-                        const uint64_t adesc = make_smem_desc(a_base + (uint32_t)j * p.a_tile_bytes + (uint32_t)k * 2u * p.sbo_a,
-                                                              p.lbo_a, p.sbo_a, p.lt_a);
-                        umma_bf16(tmem_base + (uint32_t)(j * p.BN), adesc, bdesc, p.idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
-                    }
+                    const uint32_t blo = b0 + (uint32_t)k * kb16;
+                    for (int j = 0; j < mt_valid; ++j)
+                        umma_lohi_t(tmem_base + (uint32_t)j * bn, a0 + (uint32_t)j * tile16 + (uint32_t)k * ka16, a_hi, blo, b_hi, idesc, acc);
+                    acc = 1u;
                 }
                 umma_commit(&empty_bar[stage]);
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&done_bar);
+            acc = 1u;
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
+        if (elect_one_t()) umma_commit(&done_bar);
     } else {
         const int q = warp & 3;
         mbar_wait(&done_bar, 0);
