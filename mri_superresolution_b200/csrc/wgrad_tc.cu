@@ -202,9 +202,12 @@ static WgradPlan make_plan(int N, int H, int W, int C1, int C2, int Cout, int ks
     pl.num_slabs = taps * ((C1 + C2) / pl.CS);
     const int SPT = 128 / pl.CS;
     pl.Mtiles = ceil_div(pl.num_slabs, SPT);
-    int mt_max = Cout >= 128 ? 2 : 4;
-    pl.MT = pl.Mtiles < mt_max ? pl.Mtiles : mt_max;
-    pl.groups = ceil_div(pl.Mtiles, pl.MT);
+    // M-tiles per CTA: as many as TMEM holds (MT * Cout <= 512 columns) and one 2-stage pipeline fits, then spread the
+    // M-tiles EVENLY over the CTA groups (an uneven last group idles its share of the SMs: all groups get the same K split)
+    int mt_max = 512 / Cout;
+    while (mt_max > 1 && 2u * ((uint32_t)mt_max * 16384u + (uint32_t)Cout * kBKP * 2u) > 200u * 1024u) --mt_max;
+    pl.groups = ceil_div(pl.Mtiles, mt_max);
+    pl.MT = ceil_div(pl.Mtiles, pl.groups);
     pl.stage_bytes = (uint32_t)pl.MT * 16384u + (uint32_t)Cout * kBKP * 2u;
     int st = (int)((200u * 1024u) / pl.stage_bytes);
     pl.stages = st > kMaxStages ? kMaxStages : st;
