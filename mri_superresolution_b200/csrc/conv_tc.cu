@@ -13,6 +13,7 @@
 // warps 2..5 = epilogue (TMEM -> registers -> +bias -> bf16 -> global, GroupNorm partial sums).  Two TMEM accumulator
 // buffers let the epilogue of tile i overlap the MMAs of tile i+1.
 #include <mutex>
+#include <stdlib.h>
 #include "kernels.cuh"
 #include "tc_common.cuh"
 
@@ -83,6 +84,21 @@ __device__ __forceinline__ void umma_lohi_c(uint32_t tmem_d, uint32_t alo, uint3
         : "memory");
 }
 
+__device__ __forceinline__ void umma_lohi2_c(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n"
+        ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 struct ConvTcParams {
     __nv_bfloat16* dst;     // padded origin of the output tensor (Cout = BN channels per row)
     const float* bias;      // [BN] or nullptr
@@ -100,12 +116,20 @@ struct ConvTcParams {
     const __nv_bfloat16* mask;   // epilogue: out = mask > 0 ? out : 0, same layout as dst (ReLU backward fused into dgrad)
 };
 
-template <int BN, int BK>
+// MERGE3: one A tile of 128 + 2 pixel rows per (vertical tap, K chunk) serves the three horizontal taps - the operand
+// descriptor start simply moves by one 128-byte row per tap - so the activation tile is fetched from L2 3x instead of 9x
+// (the 64-channel layers were L2-bound at 9x: 64>64@128^2 0.19 -> 0.107 ms).  The 128-byte swizzle is a function of the
+// absolute shared-memory address, so a row-shifted start needs NO base-offset in the descriptor (measured on B200: base
+// offset 0 is bit-correct, base offset = row phase is wrong).  BK = 64 only.
+template <int BN, int BK, bool MERGE3>
 struct ConvTcCfg {
     static constexpr int BM = 128;
-    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int A_ROWS = MERGE3 ? BM + 2 : BM;
+    static constexpr int A_BYTES = ((A_ROWS * BK * 2) + 1023) / 1024 * 1024;
+    static constexpr int A_TX = A_ROWS * BK * 2;                 // bytes one A load delivers
     static constexpr int B_BYTES = BN * BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int NB = MERGE3 ? 3 : 1;                    // weight tiles per stage
+    static constexpr int STAGE_BYTES = A_BYTES + NB * B_BYTES;
     static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
@@ -113,11 +137,11 @@ struct ConvTcCfg {
     static constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
 };
 
-template <int BN, int BK>
+template <int BN, int BK, bool MERGE3>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
-    using Cfg = ConvTcCfg<BN, BK>;
+    using Cfg = ConvTcCfg<BN, BK, MERGE3>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr uint32_t LT = layout_type_for(Cfg::SWZ);
     constexpr uint32_t SBO = 8 * Cfg::SWZ;
@@ -147,7 +171,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
     tc_fence_after_sync();
     const uint32_t tmem_base = s_tmem;
     const int cpt = p.chunks1 + p.chunks2;            // K chunks per tap
-    const int num_kb = p.taps * cpt;
+    const int num_kb = (MERGE3 ? 3 : p.taps) * cpt;   // pipeline stages per tile
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -157,16 +181,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
                 const int m0 = (tile / p.n_blocks) * 128;
                 const int nb = tile % p.n_blocks;
-                for (int tap = 0; tap < p.taps; ++tap) {
-                    const int shift = p.taps == 9 ? (tap / 3 - 1) * p.pw + (tap % 3 - 1) : 0;
-                    for (int c = 0; c < cpt; ++c) {
-                        mbar_wait(&empty_bar[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-                        uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
-                        if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, m0 + shift);
-                        else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, m0 + shift);
-                        tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * p.ldc + nb * BN);
-                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                if constexpr (MERGE3) {
+                    for (int dy = 0; dy < 3; ++dy) {
+                        const int row0 = m0 + (dy - 1) * p.pw - 1;             // first of the 130 rows: tap (dy, dx = -1)
+                        for (int c = 0; c < cpt; ++c) {
+                            mbar_wait(&empty_bar[stage], phase ^ 1);
+                            mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_TX + 3 * Cfg::B_BYTES);
+                            uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
+                            if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, row0);
+                            else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, row0);
+#pragma unroll
+                            for (int dx = 0; dx < 3; ++dx)
+                                tma_load_2d(a_dst + Cfg::A_BYTES + dx * Cfg::B_BYTES, &tmB, &full_bar[stage], c * BK,
+                                            (dy * 3 + dx) * p.ldc + nb * BN);
+                            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        }
+                    }
+                } else {
+                    for (int tap = 0; tap < p.taps; ++tap) {
+                        const int shift = p.taps == 9 ? (tap / 3 - 1) * p.pw + (tap % 3 - 1) : 0;
+                        for (int c = 0; c < cpt; ++c) {
+                            mbar_wait(&empty_bar[stage], phase ^ 1);
+                            mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                            uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
+                            if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, m0 + shift);
+                            else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, m0 + shift);
+                            tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * p.ldc + nb * BN);
+                            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        }
                     }
                 }
             }
@@ -189,9 +231,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                 tc_fence_after_sync();
                 if (elect_one_c()) {
                     const uint32_t so = (uint32_t)stage * (uint32_t)(Cfg::STAGE_BYTES >> 4);
+                    if constexpr (MERGE3) {
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k)
-                        umma_lohi_c(d, a_lo0 + so + (uint32_t)(k * 2), b_lo0 + so + (uint32_t)(k * 2), DESC_HI, IDESC, (kb | k) != 0 ? 1u : 0u);
+                        for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k)       // A start moves one 128-byte row per dx (base-offset field stays 0)
+                                umma_lohi2_c(d, a_lo0 + so + (uint32_t)(dx * (BK * 2 / 16) + k * 2), DESC_HI,
+                                             b_lo0 + so + (uint32_t)(dx * (Cfg::B_BYTES >> 4) + k * 2), DESC_HI, IDESC,
+                                             (kb | dx | k) != 0 ? 1u : 0u);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k)
+                            umma_lohi_c(d, a_lo0 + so + (uint32_t)(k * 2), b_lo0 + so + (uint32_t)(k * 2), DESC_HI, IDESC, (kb | k) != 0 ? 1u : 0u);
+                    }
                     umma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs have read it
                 }
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -331,27 +383,30 @@ __global__ void pack_weights_tc_kernel(const float* __restrict__ w, __nv_bfloat1
     }
 }
 
-template <int BN, int BK>
+template <int BN, int BK, bool MERGE3>
 static int launch_cfg(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
                       cudaStream_t s) {
-    using Cfg = ConvTcCfg<BN, BK>;
+    using Cfg = ConvTcCfg<BN, BK, MERGE3>;
     static bool attr_done = false;
     if (!attr_done) {
-        MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK, MERGE3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_done = true;
     }
-    conv_tc_kernel<BN, BK><<<grid, 192, Cfg::SMEM_BYTES, s>>>(tA1, tA2, tB, p);
+    conv_tc_kernel<BN, BK, MERGE3><<<grid, 192, Cfg::SMEM_BYTES, s>>>(tA1, tA2, tB, p);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
 
 template <int BN>
-static int launch_bn(int bk, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
-                     cudaStream_t s) {
+static int launch_bn(int bk, bool merge3, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p,
+                     int grid, cudaStream_t s) {
+    if constexpr (BN <= 128) {
+        if (merge3) return launch_cfg<BN, 64, true>(tA1, tA2, tB, p, grid, s);
+    }
     switch (bk) {
-        case 64: return launch_cfg<BN, 64>(tA1, tA2, tB, p, grid, s);
-        case 32: return launch_cfg<BN, 32>(tA1, tA2, tB, p, grid, s);
-        default: return launch_cfg<BN, 16>(tA1, tA2, tB, p, grid, s);
+        case 64: return launch_cfg<BN, 64, false>(tA1, tA2, tB, p, grid, s);
+        case 32: return launch_cfg<BN, 32, false>(tA1, tA2, tB, p, grid, s);
+        default: return launch_cfg<BN, 16, false>(tA1, tA2, tB, p, grid, s);
     }
 }
 
@@ -368,6 +423,13 @@ int num_sms() {
 }  // namespace tc
 
 using bf16 = __nv_bfloat16;
+
+// MRISR_CONV_TC_MERGE3=0 disables the 3-taps-per-tile path (debugging / A-B timing)
+static bool conv_tc_merge3_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("MRISR_CONV_TC_MERGE3"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
 
 bool conv_tc_supported(int H, int W, int C1, int C2, int Cout, int ks) {
     const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256 || Cout == 512;
@@ -399,10 +461,13 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     if (C1 % 64 || C2 % 64) bk = (C1 % 32 || C2 % 32) ? 16 : 32;
     const int64_t rows = (int64_t)N * (H + 2) * (W + 2);
     const int taps = a.ks * a.ks;
+    const int BNsel = Cout > 256 ? 256 : Cout;
+    const bool merge3 = conv_tc_merge3_enabled() && taps == 9 && bk == 64 && BNsel <= 128;
+    const uint32_t a_rows = merge3 ? 130u : 128u;
     CUtensorMap tA1, tA2, tB;
-    int rc = tc::make_tmap_2d_bf16(&tA1, a.src1.p, (uint64_t)rows, (uint64_t)C1, 128, (uint32_t)bk);
+    int rc = tc::make_tmap_2d_bf16(&tA1, a.src1.p, (uint64_t)rows, (uint64_t)C1, a_rows, (uint32_t)bk);
     if (rc) return rc;
-    if (C2) { rc = tc::make_tmap_2d_bf16(&tA2, a.src2.p, (uint64_t)rows, (uint64_t)C2, 128, (uint32_t)bk); if (rc) return rc; }
+    if (C2) { rc = tc::make_tmap_2d_bf16(&tA2, a.src2.p, (uint64_t)rows, (uint64_t)C2, a_rows, (uint32_t)bk); if (rc) return rc; }
     else tA2 = tA1;
     const int BN = Cout > 256 ? 256 : Cout;
     rc = tc::make_tmap_2d_bf16(&tB, a.w, (uint64_t)taps * Cout, (uint64_t)Cin, (uint32_t)BN, (uint32_t)bk);
@@ -419,11 +484,11 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     p.total_rows = (int)rows; p.num_tiles = (int)((rows + 127) / 128) * p.n_blocks;
     const int grid = p.num_tiles < tc::num_sms() ? p.num_tiles : tc::num_sms();
     switch (BN) {
-        case 16: return tc::launch_bn<16>(bk, tA1, tA2, tB, p, grid, s);
-        case 32: return tc::launch_bn<32>(bk, tA1, tA2, tB, p, grid, s);
-        case 64: return tc::launch_bn<64>(bk, tA1, tA2, tB, p, grid, s);
-        case 128: return tc::launch_bn<128>(bk, tA1, tA2, tB, p, grid, s);
-        default: return tc::launch_bn<256>(bk, tA1, tA2, tB, p, grid, s);
+        case 16: return tc::launch_bn<16>(bk, merge3, tA1, tA2, tB, p, grid, s);
+        case 32: return tc::launch_bn<32>(bk, merge3, tA1, tA2, tB, p, grid, s);
+        case 64: return tc::launch_bn<64>(bk, merge3, tA1, tA2, tB, p, grid, s);
+        case 128: return tc::launch_bn<128>(bk, merge3, tA1, tA2, tB, p, grid, s);
+        default: return tc::launch_bn<256>(bk, merge3, tA1, tA2, tB, p, grid, s);
     }
 }
 
