@@ -70,6 +70,10 @@ int launch_wgrad_rows(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
 bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks);
 size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks);
 int launch_wgrad_tc(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
+// wgrad_tc3.cu: horizontal taps merged into one fetched tile (64-channel chunks, Cout 64 / 128); launch_wgrad_tc dispatches
+bool wgrad_tc3_supported(int N, int H, int W, int C1, int C2, int Cout, int ks);
+size_t wgrad_tc3_scratch_elems(int N, int H, int W, int C1, int C2, int Cout);
+int launch_wgrad_tc3(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s);
 
 // ---------------------------------------------------------------- normalisation / activation (norm_act.cu)
 template <typename T> int launch_pack_input(const float* x, Act<T> dst, cudaStream_t s);

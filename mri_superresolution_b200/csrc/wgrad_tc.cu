@@ -233,7 +233,15 @@ bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks) {
 
 size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks) {
     const tc::WgradPlan pl = tc::make_plan(N, H, W, C1, C2, Cout, ks);
-    return (size_t)pl.splits * (size_t)ks * ks * (C1 + C2) * Cout;
+    const size_t own = (size_t)pl.splits * (size_t)ks * ks * (C1 + C2) * Cout;
+    const size_t merged = wgrad_tc3_supported(N, H, W, C1, C2, Cout, ks) ? wgrad_tc3_scratch_elems(N, H, W, C1, C2, Cout) : 0;
+    return own > merged ? own : merged;
+}
+
+// MRISR_WGRAD_TC3=0 keeps the one-box-per-tap kernel for every shape (A/B measurements)
+static bool use_tc3() {
+    static const bool on = [] { const char* e = getenv("MRISR_WGRAD_TC3"); return !(e && e[0] == '0'); }();
+    return on;
 }
 
 int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
@@ -243,6 +251,7 @@ int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
         set_error("wgrad_tc: unsupported shape C1=%d C2=%d Cout=%d ks=%d", C1, C2, Cout, a.ks);
         return -2;
     }
+    if (use_tc3() && wgrad_tc3_supported(N, H, W, C1, C2, Cout, a.ks)) return launch_wgrad_tc3(a, s);
     const char* tag = "wgrad_tc";
     char tbuf[96];
     if (prof_on()) {

@@ -122,6 +122,9 @@ SHAPES = [
     (4, 32, 32, 32, 0, 16, 3, False),       # head shapes
     (2, 64, 64, 32, 0, 64, 3, True),
     (2, 64, 48, 16, 0, 16, 3, False),
+    (2, 20, 28, 128, 0, 64, 3, False),      # merged-tap weight gradient: two slab groups
+    (1, 32, 32, 128, 128, 128, 3, False),   # ... six groups of two slabs, concat
+    (5, 16, 16, 64, 0, 128, 3, False),      # ... odd slab count in the last group
 ]
 
 
