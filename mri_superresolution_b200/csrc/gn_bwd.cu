@@ -307,11 +307,440 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Fused form (bf16): ONE kernel does reduce -> group constants -> apply.  GroupNorm couples all pixels of a (sample, group),
+// so the unit of independence is a sample (NHWC) or one 8-channel plane of a sample (planar-8, C <= 64: groups never straddle
+// planes).  A thread-block CLUSTER owns a unit: every CTA reduces its share of the rows, the per-channel partial sums are
+// exchanged through distributed shared memory (fixed rank order: deterministic), every CTA derives (q, p) of its groups and
+// applies dr = sc*dz + p*r + q to the same rows.  The raw operands a thread loaded in the first phase are kept in shared
+// memory (thread-private slots, as many units as fit) so the second phase does not read HBM again: 5 -> 3 tensor passes.
+constexpr int kFtMax = 512;             // threads per CTA of the fused kernel: 512 (2 CTAs / SM) or 256 (4 CTAs / SM)
+constexpr int kMaxUnitCh = 512;         // channels of one unit
+
+template <int P, bool POOL> struct Raw { uint4 r[P]; uint4 a[P]; uint4 gp; };
+
+__device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+}
+
+template <int KIND, int P>
+__device__ __forceinline__ void load_raw(const GnBwdArgs<__nv_bfloat16>& a, int n, int uy, int ux, int cv, Raw<P, KindTraits<KIND>::pool>& w) {
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+        const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+        w.r[q] = *reinterpret_cast<const uint4*>(a.r.at(n, y, x, cv * 8));
+        if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
+            w.a[q] = *reinterpret_cast<const uint4*>(a.g.at(n, y, x, a.coff + cv * 8));
+        } else if (KIND == SRC_BLEND_BIL) {
+            w.a[q] = *reinterpret_cast<const uint4*>(a.g.at(n, y, x, cv * 8));
+        } else if (KIND == SRC_BLEND_PS) {
+            // channels 8cv..8cv+7 of the unshuffled tensor = channels (2cv, 2cv+1) of g at the four sub-pixels (i, j)
+            uint32_t t[4];
+#pragma unroll
+            for (int ij = 0; ij < 4; ++ij)
+                t[ij] = *reinterpret_cast<const uint32_t*>(a.g.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), 2 * cv));
+            w.a[q] = make_uint4(t[0], t[1], t[2], t[3]);
+        } else if (KIND == SRC_OUTER) {
+            const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
+            const float yy = a.y[pi];
+            w.a[q] = make_uint4(__float_as_uint(a.dy[pi] * yy * (1.f - yy)), 0u, 0u, 0u);
+        }
+    }
+    if (KindTraits<KIND>::pool) w.gp = *reinterpret_cast<const uint4*>(a.gpool.at(n, uy, ux, cv * 8));
+}
+
+// same arithmetic as unit_grads, operands taken from the raw words
+template <int KIND, int P>
+__device__ __forceinline__ void grads_from_raw(const ChanCtx& c, const Raw<P, KindTraits<KIND>::pool>& w, float al, const float (&wv)[8],
+                                               float (&rv)[P][8], float (&dz)[P][8], float& dl_out, float (&act_out)[8]) {
+    using T = __nv_bfloat16;
+    float z[P][8];
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+        unpack8(w.r[q], rv[q]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) z[q][k] = fmaf(rv[q][k], c.sc[k], c.sh[k]);
+        float dA[8];
+        if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
+            unpack8(w.a[q], dA);
+        } else if (KIND == SRC_BLEND_BIL) {
+            unpack8(w.a[q], dA);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dA[k] *= al;
+        } else if (KIND == SRC_BLEND_PS) {
+            const uint32_t t[4] = {w.a[q].x, w.a[q].y, w.a[q].z, w.a[q].w};
+#pragma unroll
+            for (int ij = 0; ij < 4; ++ij) {
+                dA[ij] = al * __uint_as_float(t[ij] << 16);
+                dA[4 + ij] = al * __uint_as_float(t[ij] & 0xffff0000u);
+            }
+        } else if (KIND == SRC_OUTER) {
+            const float dl = __uint_as_float(w.a[q].x);
+            dl_out = dl;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                dA[k] = dl * wv[k];
+                act_out[k] = lrelu(z[q][k]);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dA[k] = 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dz[q][k] = dA[k];
+    }
+    if (KindTraits<KIND>::pool) {
+        float gp[8];
+        unpack8(w.gp, gp);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            int best = 0;
+            float bv = to_f(from_f<T>(lrelu(z[0][k])));
+#pragma unroll
+            for (int q = 1; q < P; ++q) {
+                const float vq = to_f(from_f<T>(lrelu(z[q][k])));
+                if (vq > bv) { bv = vq; best = q; }
+            }
+#pragma unroll
+            for (int q = 0; q < P; ++q) dz[q][k] += (q == best) ? gp[k] : 0.f;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < P; ++q)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dz[q][k] *= lrelu_grad(z[q][k]);
+}
+
+struct FusedParams {
+    int cs;            // CTAs per cluster (= partial-sum slots per sample)
+    int ncv;           // channel vectors per unit (1: one plane of a planar tensor; C/8: a whole NHWC sample)
+    int ups;           // units per sample
+    int rows_pc;       // unit rows per CTA
+    int K;             // units per thread cached in shared memory
+    double inv_count;
+};
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+
+template <int KIND, int FT>
+__global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / FT)) gn_bwd_fused_kernel(GnBwdArgs<__nv_bfloat16> a, FusedParams fp) {
+    using T = __nv_bfloat16;
+    constexpr bool POOL = KindTraits<KIND>::pool;
+    // kinds whose operands are plain 16-byte vectors stream the cached units with cp.async (no registers held while in flight)
+    constexpr bool ASYNC = KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL;
+    constexpr int P = POOL ? 4 : 1;
+    constexpr int RAWV = 2 * P + (POOL ? 1 : 0);
+    constexpr int NW = FT / 32;
+    extern __shared__ uint4 dyn_smem[];
+    __shared__ float s_ch[3][kMaxUnitCh];
+    __shared__ double s_tot[2][kMaxUnitCh];
+    __shared__ float s_q[kGroups], s_p[kGroups], s_wdl[NW];
+    static_assert(FT <= kFtMax, "");
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    uint32_t rank, unit;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(unit));
+    const int ncv = fp.ncv, nchl = ncv * 8;
+    const int n = unit / fp.ups, cv0 = (unit % fp.ups) * ncv;
+    const int C = a.r.C, gs = C / kGroups;
+    const int UW = P == 4 ? a.r.W / 2 : a.r.W, UH = P == 4 ? a.r.H / 2 : a.r.H;
+    const int r0 = min(UH, (int)rank * fp.rows_pc), r1 = min(UH, r0 + fp.rows_pc);
+    const int npx = (r1 - r0) * UW;                    // units of this CTA per channel vector
+    const int cvl = tid % ncv, cv = cv0 + cvl;
+    const int p0 = tid / ncv, pstep = FT / ncv;
+    uint4* cache = dyn_smem;                           // [K][RAWV][FT]
+    float* s_w = reinterpret_cast<float*>(dyn_smem + (size_t)fp.K * RAWV * FT);      // [NW][3][nchl]
+
+    ChanCtx c;
+    load_ctx<T, KIND>(a, n, cv, c);
+    float al = 0.f, wv[8];
+    if (KIND == SRC_BLEND_BIL) al = 1.f / (1.f + __expf(-a.alpha[0]));
+    if (KIND == SRC_BLEND_PS) al = 1.f - 1.f / (1.f + __expf(-a.alpha[0]));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) wv[k] = KIND == SRC_OUTER ? a.wvec[cv * 8 + k] : 0.f;
+
+    // ---- phase 1: partial sums of this CTA's rows
+    float s1[8], s2[8], s3[8], sdl = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
+    constexpr int UB = P == 4 ? 1 : 2;
+    auto accumulate = [&](const Raw<P, POOL>& w) {
+        float rv[P][8], dz[P][8], act[8], dl = 0.f;
+        grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
+#pragma unroll
+        for (int q = 0; q < P; ++q)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { s1[k] += dz[q][k]; s2[k] = fmaf(dz[q][k], rv[q][k], s2[k]); }
+        if (KIND == SRC_OUTER) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
+            if (cvl == 0) sdl += dl;
+        }
+    };
+    if (ASYNC) {
+        for (int i = 0; i < fp.K; ++i) {
+            const int pi = p0 + i * pstep;
+            if (pi >= npx) break;
+            const int uy = r0 + pi / UW, ux = pi % UW;
+            uint4* slot = cache + (size_t)i * RAWV * FT + tid;
+#pragma unroll
+            for (int q = 0; q < P; ++q) {
+                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+                cp_async16(slot + q * FT, a.r.at(n, y, x, cv * 8));
+                cp_async16(slot + (P + q) * FT, a.g.at(n, y, x, (KIND == SRC_BLEND_BIL ? 0 : a.coff) + cv * 8));
+            }
+            if (POOL) cp_async16(slot + 2 * P * FT, a.gpool.at(n, uy, ux, cv * 8));
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    // units that do not fit the cache (all units for the gather kinds, which also fill the cache from registers)
+    for (int i0 = ASYNC ? fp.K : 0; p0 + i0 * pstep < npx; i0 += UB) {
+        Raw<P, POOL> w[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int pi = min(p0 + (i0 + u) * pstep, npx - 1);
+            load_raw<KIND, P>(a, n, r0 + pi / UW, pi % UW, cv, w[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            if (p0 + (i0 + u) * pstep >= npx) continue;
+            if (!ASYNC && i0 + u < fp.K) {
+                uint4* slot = cache + (size_t)(i0 + u) * RAWV * FT + tid;
+#pragma unroll
+                for (int q = 0; q < P; ++q) { slot[q * FT] = w[u].r[q]; slot[(P + q) * FT] = w[u].a[q]; }
+                if (POOL) slot[2 * P * FT] = w[u].gp;
+            }
+            accumulate(w[u]);
+        }
+    }
+    if (ASYNC) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        for (int i = 0; i < fp.K; ++i) {
+            if (p0 + i * pstep >= npx) break;
+            const uint4* slot = cache + (size_t)i * RAWV * FT + tid;
+            Raw<P, POOL> w;
+#pragma unroll
+            for (int q = 0; q < P; ++q) { w.r[q] = slot[q * FT]; w.a[q] = slot[(P + q) * FT]; }
+            if (POOL) w.gp = slot[2 * P * FT];
+            accumulate(w);
+        }
+    }
+    // lanes with equal (lane % ncv) share a channel vector: butterfly over the other lane bits, then across warps in order
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        for (int o = 16; o >= ncv; o >>= 1) {
+            s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], o);
+            s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], o);
+            if (KIND == SRC_OUTER) s3[k] += __shfl_xor_sync(0xffffffffu, s3[k], o);
+        }
+    }
+    if (lane < ncv) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s_w[(wid * 3 + 0) * nchl + lane * 8 + k] = s1[k];
+            s_w[(wid * 3 + 1) * nchl + lane * 8 + k] = s2[k];
+            s_w[(wid * 3 + 2) * nchl + lane * 8 + k] = s3[k];
+        }
+    }
+    if (KIND == SRC_OUTER) {
+        sdl = warp_sum(sdl);
+        if (lane == 0) s_wdl[wid] = sdl;
+    }
+    __syncthreads();
+    const int64_t row = (int64_t)(C + 8);
+    float* out = a.part + ((int64_t)n * fp.cs + rank) * 3 * row;
+    // with ncv < 32 a warp covers channel vector (lane % ncv) only when ncv divides 32; warps hold every local vector
+    for (int i = tid; i < 3 * nchl; i += FT) {
+        const int which = i / nchl, chl = i % nchl;
+        float t = 0.f;
+        if (ncv <= 32) {
+            for (int w2 = 0; w2 < NW; ++w2) t += s_w[(w2 * 3 + which) * nchl + chl];
+        } else {
+            // ncv = 64: lane l of warp w holds vector (w * 32 + l) % 64 -> warps of equal parity share vectors
+            const int v = chl >> 3, par = v >> 5;
+            for (int w2 = par; w2 < NW; w2 += 2) t += s_w[(w2 * 3 + which) * nchl + ((v & 31) * 8 + (chl & 7))];
+        }
+        s_ch[which][chl] = t;
+        out[which * row + cv0 * 8 + chl] = t;
+    }
+    if (KIND == SRC_OUTER && tid == 0) {
+        float t = 0.f;
+        for (int w2 = 0; w2 < NW; ++w2) t += s_wdl[w2];
+        if (cv0 == 0) out[C] = t;
+    }
+    // ---- exchange: per-channel totals of the unit in rank order, then the constants of the unit's groups
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    for (int i = tid; i < 2 * nchl; i += FT) {
+        const int which = i / nchl, chl = i % nchl;
+        const uint32_t local = (uint32_t)__cvta_generic_to_shared(&s_ch[which][chl]);
+        double t = 0.0;
+        for (int rk = 0; rk < fp.cs; ++rk) {
+            uint32_t remote;
+            float v;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rk));
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+            t += (double)v;
+        }
+        s_tot[which][chl] = t;
+    }
+    __syncthreads();
+    const int ngl = nchl >= gs ? nchl / gs : 0;        // whole groups inside the unit (host guarantees >= 1)
+    if (tid < ngl) {
+        const int g = (cv0 * 8) / gs + tid, ng = n * kGroups + g;
+        const double mean = (double)a.stats[ng * 2], rstd = (double)a.stats[ng * 2 + 1];
+        double m1 = 0.0, m2 = 0.0;
+        for (int j = 0; j < gs; ++j) {
+            const int chl = tid * gs + j, ch = cv0 * 8 + chl;
+            const double gm = (double)a.gamma[KIND == SRC_BLEND_PS ? ch / 4 : ch];
+            m1 += gm * s_tot[0][chl];
+            m2 += gm * (s_tot[1][chl] - mean * s_tot[0][chl]);
+        }
+        m1 *= fp.inv_count;
+        m2 *= rstd * fp.inv_count;
+        s_q[tid] = (float)(-rstd * m1 + mean * rstd * rstd * m2);
+        s_p[tid] = (float)(-rstd * rstd * m2);
+    }
+    // second cluster barrier: nobody's shared memory is read remotely after it (CTAs may exit), and s_q / s_p are visible
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+
+    // ---- phase 2: dr = sc*dz + p*r + q over the same rows (cached operands first)
+    float cq[8], cp[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int gl = (cvl * 8 + k) / gs;
+        cq[k] = s_q[gl];
+        cp[k] = s_p[gl];
+    }
+    for (int i0 = 0; p0 + i0 * pstep < npx; i0 += UB) {
+        Raw<P, POOL> w[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int pi = min(p0 + (i0 + u) * pstep, npx - 1);
+            if (i0 + u < fp.K) {
+                const uint4* slot = cache + (size_t)(i0 + u) * RAWV * FT + tid;
+#pragma unroll
+                for (int q = 0; q < P; ++q) { w[u].r[q] = slot[q * FT]; w[u].a[q] = slot[(P + q) * FT]; }
+                if (POOL) w[u].gp = slot[2 * P * FT];
+            } else {
+                load_raw<KIND, P>(a, n, r0 + pi / UW, pi % UW, cv, w[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int pi = p0 + (i0 + u) * pstep;
+            if (pi >= npx) continue;
+            const int uy = r0 + pi / UW, ux = pi % UW;
+            float rv[P][8], dz[P][8], act[8], dl = 0.f;
+            grads_from_raw<KIND, P>(c, w[u], al, wv, rv, dz, dl, act);
+#pragma unroll
+            for (int q = 0; q < P; ++q) {
+                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[q][k], fmaf(cp[k], rv[q][k], cq[k]));
+                store8(a.dr.at(n, y, x, cv * 8), o);
+            }
+        }
+    }
+}
+
+struct FusedPlan { bool ok; FusedParams fp; size_t smem; int units; int ft; };
+
+inline int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+inline int fused_threads() {
+    static const int ft = env_int("MRISR_GNBWD_FT", 512) == 256 ? 256 : 512;
+    return ft;
+}
+
+template <int KIND>
+FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
+    const int FT = fused_threads();
+    constexpr bool POOL = KindTraits<KIND>::pool;
+    constexpr int P = POOL ? 4 : 1, RAWV = 2 * P + (POOL ? 1 : 0);
+    FusedPlan pl;
+    pl.ok = false;
+    static const int enabled = env_int("MRISR_GNBWD_FUSED", 1);
+    // two CTAs per SM (64 registers) for the one-pixel kinds; the 2x2-window kinds need 128 registers -> one CTA with all the SM's
+    // shared memory
+    static const int smem_kb = env_int(POOL ? "MRISR_GNBWD_POOL_SMEM_KB" : "MRISR_GNBWD_SMEM_KB",
+                                       FT == 512 ? (POOL ? 190 : 96) : (POOL ? 95 : 40));
+    static const int cs_env = env_int("MRISR_GNBWD_CS", 0);
+    if (!enabled) return pl;
+    const int C = a.r.C, nv = C / 8, gs = C / kGroups;
+    const int ncv = a.r.planar() ? 1 : nv;
+    if (C % 8 || ncv * 8 > kMaxUnitCh || FT % ncv || (ncv * 8) % gs) return pl;          // groups must not straddle units
+    const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
+    if (UH < 1 || UW < 1) return pl;
+    const size_t red_bytes = (size_t)(FT / 32) * 3 * ncv * 8 * sizeof(float);
+    const size_t budget = (size_t)smem_kb * 1024 > red_bytes + 4096 ? (size_t)smem_kb * 1024 - red_bytes : 4096;
+    const int kmax = (int)(budget / ((size_t)FT * RAWV * 16));
+    const int64_t items = (int64_t)UH * UW * ncv;                     // (unit, channel vector) pairs of one unit
+    int cs = cs_env ? cs_env : 4;
+    while (cs > UH && cs > 1) cs >>= 1;
+    if (cs != 1 && cs != 2 && cs != 4 && cs != 8 && cs != 16) return pl;
+    pl.ft = FT;
+    pl.fp.cs = cs;
+    pl.fp.ncv = ncv;
+    pl.fp.ups = nv / ncv;
+    pl.fp.rows_pc = ceil_div(UH, cs);
+    const int iters = (int)ceil_div64((int64_t)pl.fp.rows_pc * UW * ncv, FT);
+    pl.fp.K = iters < kmax ? iters : kmax;
+    pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
+    pl.smem = (size_t)pl.fp.K * RAWV * FT * 16 + red_bytes;
+    pl.units = a.r.N * pl.fp.ups;
+    pl.ok = true;
+    return pl;
+}
+
+template <int KIND, int FT>
+int run_fused(const GnBwdArgs<__nv_bfloat16>& a, const FusedPlan& pl, cudaStream_t s) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr_done = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(pl.units * pl.fp.cs));
+    cfg.blockDim = dim3(FT);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = pl.fp.cs;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    MRISR_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gn_bwd_fused_kernel<KIND, FT>, a, pl.fp));
+    MRISR_LAUNCH_CHECK();
+    const int pcs = KIND == SRC_BLEND_PS ? a.r.C / 4 : a.r.C;
+    gn_bwd_finalize_kernel<__nv_bfloat16, KIND><<<pcs, FTHR, 0, s>>>(a, pl.fp.cs, pl.fp.inv_count, 0, a.r.N, 1);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
 template <typename T, int KIND>
 int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
     const int C = a.r.C, nv = C / 8;
     if (nv > NTHR) { set_error("gn_bwd: C = %d is too wide", C); return -1; }
+    if constexpr (sizeof(T) == 2) {
+        const FusedPlan fpl = fused_plan<KIND>(a);
+        if (fpl.ok) return fpl.ft == 256 ? run_fused<KIND, 256>(a, fpl, s) : run_fused<KIND, 512>(a, fpl, s);
+    }
     const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
     const int rows_pb = rows_per_block(UW, nv, NTHR, UNITS_PER_THREAD);
     const int slots = ceil_div(UH, rows_pb);
@@ -343,7 +772,8 @@ int gn_bwd_slots(int H, int W, int C) {
     // upper bound over both unit shapes (pool kinds use half the rows and half the columns)
     const int full = ceil_div(H, rows_per_block(W, C / 8, NTHR, UNITS_PER_THREAD));
     const int pool = ceil_div(H / 2, rows_per_block(W / 2, C / 8, NTHR, UNITS_PER_THREAD));
-    return full > pool ? full : pool;
+    const int m = full > pool ? full : pool;
+    return m > 16 ? m : 16;                  // the fused kernel uses one slot per cluster rank (<= 16)
 }
 
 template <typename T>

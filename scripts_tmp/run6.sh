@@ -1,6 +1,22 @@
 cd $GRAFT_REPO_ROOT
-timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/r13_tests.log 2>&1; echo rc=$? >> gpurun_out/r13_tests.log
-tail -5 gpurun_out/r13_tests.log
-timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --perceptual 0.1 --batch 16 --layer-report gpurun_out/r13_layers_vgg.txt > gpurun_out/r13_bench_vgg.log 2>&1
-cut -c1-400 gpurun_out/r13_bench_vgg.log
-grep -i "vgg\|conv_tc" gpurun_out/r13_layers_vgg.txt | head -40
+run() {
+  name=$1; shift
+  env "$@" timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --layer-report gpurun_out/r13_layers_$name.txt > gpurun_out/r13_bench_$name.log 2>&1
+  python - <<PY
+import json
+d=json.loads([l for l in open('gpurun_out/r13_bench_$name.log') if l.startswith('{')][-1])
+g=[k for k in d['kernels'] if k['kernel']=='gn_bwd'][0]
+print('$name', 'step', round(d['ms_per_step'],3), 'gn_bwd', g['ms_per_step'])
+PY
+  grep gn_bwd gpurun_out/r13_layers_$name.txt | awk '{printf "   %s %s\n", $1, $6}' | tr '\n' ' '; echo
+}
+timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > gpurun_out/r13_tests.log 2>&1; echo rc=$? >> gpurun_out/r13_tests.log
+tail -3 gpurun_out/r13_tests.log
+run cs8 MRISR_GNBWD_CS=8
+run cs4 MRISR_GNBWD_CS=4
+run cs2 MRISR_GNBWD_CS=2
+run cs8_ft256 MRISR_GNBWD_CS=8 MRISR_GNBWD_FT=256
+run cs4_ft256 MRISR_GNBWD_CS=4 MRISR_GNBWD_FT=256
+run cs16_ft256 MRISR_GNBWD_CS=16 MRISR_GNBWD_FT=256
+run cs8_190 MRISR_GNBWD_CS=8 MRISR_GNBWD_SMEM_KB=190
+run cs8_pool95 MRISR_GNBWD_CS=8 MRISR_GNBWD_POOL_SMEM_KB=95
