@@ -312,8 +312,12 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
 // so the unit of independence is a sample (NHWC) or one 8-channel plane of a sample (planar-8, C <= 64: groups never straddle
 // planes).  A thread-block CLUSTER owns a unit: every CTA reduces its share of the rows, the per-channel partial sums are
 // exchanged through distributed shared memory (fixed rank order: deterministic), every CTA derives (q, p) of its groups and
-// applies dr = sc*dz + p*r + q to the same rows.  The raw operands a thread loaded in the first phase are kept in shared
-// memory (thread-private slots, as many units as fit) so the second phase does not read HBM again: 5 -> 3 tensor passes.
+// applies dr = sc*dz + p*r + q to the same rows.
+// Measured on B200 (batch 64, profiles/r01_gn_bwd_fused.md): clusters of 2 are fastest (gn_bwd 6.8 -> 5.0 ms per step); larger
+// clusters lose more to gang scheduling than their bigger shared-memory share of a unit wins back, and with 2 CTAs the
+// operands kept in shared memory between the phases (K slots) are a few percent of a unit, so the second phase still
+// re-reads most operands (5 passes, now at ~70% of the HBM copy rate instead of 45%).  MRISR_GNBWD_CS / _FT / _SMEM_KB / _D / _K
+// reproduce the sweep.
 constexpr int kFtMax = 512;             // threads per CTA of the fused kernel: 512 (2 CTAs / SM) or 256 (4 CTAs / SM)
 constexpr int kMaxUnitCh = 512;         // channels of one unit
 
@@ -326,32 +330,6 @@ __device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
         v[2 * i] = __uint_as_float(w[i] << 16);
         v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
     }
-}
-
-template <int KIND, int P>
-__device__ __forceinline__ void load_raw(const GnBwdArgs<__nv_bfloat16>& a, int n, int uy, int ux, int cv, Raw<P, KindTraits<KIND>::pool>& w) {
-#pragma unroll
-    for (int q = 0; q < P; ++q) {
-        const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-        w.r[q] = *reinterpret_cast<const uint4*>(a.r.at(n, y, x, cv * 8));
-        if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
-            w.a[q] = *reinterpret_cast<const uint4*>(a.g.at(n, y, x, a.coff + cv * 8));
-        } else if (KIND == SRC_BLEND_BIL) {
-            w.a[q] = *reinterpret_cast<const uint4*>(a.g.at(n, y, x, cv * 8));
-        } else if (KIND == SRC_BLEND_PS) {
-            // channels 8cv..8cv+7 of the unshuffled tensor = channels (2cv, 2cv+1) of g at the four sub-pixels (i, j)
-            uint32_t t[4];
-#pragma unroll
-            for (int ij = 0; ij < 4; ++ij)
-                t[ij] = *reinterpret_cast<const uint32_t*>(a.g.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), 2 * cv));
-            w.a[q] = make_uint4(t[0], t[1], t[2], t[3]);
-        } else if (KIND == SRC_OUTER) {
-            const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
-            const float yy = a.y[pi];
-            w.a[q] = make_uint4(__float_as_uint(a.dy[pi] * yy * (1.f - yy)), 0u, 0u, 0u);
-        }
-    }
-    if (KindTraits<KIND>::pool) w.gp = *reinterpret_cast<const uint4*>(a.gpool.at(n, uy, ux, cv * 8));
 }
 
 // same arithmetic as unit_grads, operands taken from the raw words
@@ -380,7 +358,8 @@ __device__ __forceinline__ void grads_from_raw(const ChanCtx& c, const Raw<P, Ki
                 dA[4 + ij] = al * __uint_as_float(t[ij] & 0xffff0000u);
             }
         } else if (KIND == SRC_OUTER) {
-            const float dl = __uint_as_float(w.a[q].x);
+            const float yy = __uint_as_float(w.a[q].x);
+            const float dl = __uint_as_float(w.a[q].y) * yy * (1.f - yy);
             dl_out = dl;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -421,20 +400,28 @@ struct FusedParams {
     int ncv;           // channel vectors per unit (1: one plane of a planar tensor; C/8: a whole NHWC sample)
     int ups;           // units per sample
     int rows_pc;       // unit rows per CTA
-    int K;             // units per thread cached in shared memory
+    int slots;         // shared-memory slots per thread (K, or K + S)
+    int K;             // units per thread kept in shared memory between the phases (plus S streaming slots)
     double inv_count;
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <int KIND, int FT>
+// Every operand goes global -> shared memory with cp.async into thread-private slots (no registers held while in flight):
+// K "cached" slots keep the first K units of the thread for the second phase, S "streaming" slots form a depth-S software
+// pipeline for the rest.  The second phase walks the streamed units in reverse order (most recently read first: L2), and its
+// first S reloads are issued before the cluster barriers so the exchange latency is hidden behind them.
+template <int KIND, int FT, int S>
 __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / FT)) gn_bwd_fused_kernel(GnBwdArgs<__nv_bfloat16> a, FusedParams fp) {
     using T = __nv_bfloat16;
     constexpr bool POOL = KindTraits<KIND>::pool;
-    // kinds whose operands are plain 16-byte vectors stream the cached units with cp.async (no registers held while in flight)
-    constexpr bool ASYNC = KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL;
     constexpr int P = POOL ? 4 : 1;
     constexpr int RAWV = 2 * P + (POOL ? 1 : 0);
     constexpr int NW = FT / 32;
@@ -456,8 +443,10 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     const int npx = (r1 - r0) * UW;                    // units of this CTA per channel vector
     const int cvl = tid % ncv, cv = cv0 + cvl;
     const int p0 = tid / ncv, pstep = FT / ncv;
-    uint4* cache = dyn_smem;                           // [K][RAWV][FT]
-    float* s_w = reinterpret_cast<float*>(dyn_smem + (size_t)fp.K * RAWV * FT);      // [NW][3][nchl]
+    const int nu = p0 < npx ? (npx - p0 + pstep - 1) / pstep : 0;      // units of this thread
+    const int K = fp.K;
+    uint4* cache = dyn_smem;                           // [K + S][RAWV][FT]
+    float* s_w = reinterpret_cast<float*>(dyn_smem + (size_t)fp.slots * RAWV * FT);      // [NW][3][nchl]
 
     ChanCtx c;
     load_ctx<T, KIND>(a, n, cv, c);
@@ -467,12 +456,52 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
 #pragma unroll
     for (int k = 0; k < 8; ++k) wv[k] = KIND == SRC_OUTER ? a.wvec[cv * 8 + k] : 0.f;
 
+    auto issue = [&](int i, int sidx) {                // unit i of this thread -> slot sidx
+        const int pi = p0 + i * pstep, uy = r0 + pi / UW, ux = pi % UW;
+        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+            const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+            cp_async16(sl + q * FT, a.r.at(n, y, x, cv * 8));
+            uint4* sa = sl + (P + q) * FT;
+            if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) {
+                cp_async16(sa, a.g.at(n, y, x, a.coff + cv * 8));
+            } else if (KIND == SRC_BLEND_BIL) {
+                cp_async16(sa, a.g.at(n, y, x, cv * 8));
+            } else if (KIND == SRC_BLEND_PS) {
+                // channels 8cv..8cv+7 of the unshuffled tensor = channels (2cv, 2cv+1) of g at the four sub-pixels (i, j)
+#pragma unroll
+                for (int ij = 0; ij < 4; ++ij)
+                    cp_async4(reinterpret_cast<uint32_t*>(sa) + ij, a.g.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), 2 * cv));
+            } else if (KIND == SRC_OUTER) {
+                const int64_t pix = ((int64_t)n * a.r.H + y) * a.r.W + x;
+                cp_async4(reinterpret_cast<uint32_t*>(sa), a.y + pix);
+                cp_async4(reinterpret_cast<uint32_t*>(sa) + 1, a.dy + pix);
+            }
+        }
+        if (POOL) cp_async16(sl + 2 * P * FT, a.gpool.at(n, uy, ux, cv * 8));
+    };
+    auto fetch = [&](int sidx, Raw<P, POOL>& w) {
+        const uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
+#pragma unroll
+        for (int q = 0; q < P; ++q) { w.r[q] = sl[q * FT]; w.a[q] = sl[(P + q) * FT]; }
+        if (POOL) w.gp = sl[2 * P * FT];
+    };
+    auto slot_of = [&](int i) { return i < K ? i : K + (i - K) % S; };
+
     // ---- phase 1: partial sums of this CTA's rows
     float s1[8], s2[8], s3[8], sdl = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
-    constexpr int UB = P == 4 ? 1 : 2;
-    auto accumulate = [&](const Raw<P, POOL>& w) {
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        if (i < nu) issue(i, slot_of(i));
+        cp_async_commit();
+    }
+    for (int i = 0; i < nu; ++i) {
+        cp_async_wait<S - 1>();
+        Raw<P, POOL> w;
+        fetch(slot_of(i), w);
         float rv[P][8], dz[P][8], act[8], dl = 0.f;
         grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
 #pragma unroll
@@ -484,54 +513,15 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
             for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
             if (cvl == 0) sdl += dl;
         }
-    };
-    if (ASYNC) {
-        for (int i = 0; i < fp.K; ++i) {
-            const int pi = p0 + i * pstep;
-            if (pi >= npx) break;
-            const int uy = r0 + pi / UW, ux = pi % UW;
-            uint4* slot = cache + (size_t)i * RAWV * FT + tid;
-#pragma unroll
-            for (int q = 0; q < P; ++q) {
-                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-                cp_async16(slot + q * FT, a.r.at(n, y, x, cv * 8));
-                cp_async16(slot + (P + q) * FT, a.g.at(n, y, x, (KIND == SRC_BLEND_BIL ? 0 : a.coff) + cv * 8));
-            }
-            if (POOL) cp_async16(slot + 2 * P * FT, a.gpool.at(n, uy, ux, cv * 8));
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (i + S < nu) issue(i + S, slot_of(i + S));          // the streaming slot just consumed (or a fresh one)
+        cp_async_commit();
     }
-    // units that do not fit the cache (all units for the gather kinds, which also fill the cache from registers)
-    for (int i0 = ASYNC ? fp.K : 0; p0 + i0 * pstep < npx; i0 += UB) {
-        Raw<P, POOL> w[UB];
+    // reloads of the streamed units for the second phase, newest first: unit nu-1-t -> streaming slot t % S
+    const int nstream = nu > K ? nu - K : 0;
 #pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            const int pi = min(p0 + (i0 + u) * pstep, npx - 1);
-            load_raw<KIND, P>(a, n, r0 + pi / UW, pi % UW, cv, w[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            if (p0 + (i0 + u) * pstep >= npx) continue;
-            if (!ASYNC && i0 + u < fp.K) {
-                uint4* slot = cache + (size_t)(i0 + u) * RAWV * FT + tid;
-#pragma unroll
-                for (int q = 0; q < P; ++q) { slot[q * FT] = w[u].r[q]; slot[(P + q) * FT] = w[u].a[q]; }
-                if (POOL) slot[2 * P * FT] = w[u].gp;
-            }
-            accumulate(w[u]);
-        }
-    }
-    if (ASYNC) {
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        for (int i = 0; i < fp.K; ++i) {
-            if (p0 + i * pstep >= npx) break;
-            const uint4* slot = cache + (size_t)i * RAWV * FT + tid;
-            Raw<P, POOL> w;
-#pragma unroll
-            for (int q = 0; q < P; ++q) { w.r[q] = slot[q * FT]; w.a[q] = slot[(P + q) * FT]; }
-            if (POOL) w.gp = slot[2 * P * FT];
-            accumulate(w);
-        }
+    for (int t = 0; t < S; ++t) {
+        if (t < nstream) issue(nu - 1 - t, K + t);
+        cp_async_commit();
     }
     // lanes with equal (lane % ncv) share a channel vector: butterfly over the other lane bits, then across warps in order
 #pragma unroll
@@ -611,7 +601,7 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     // second cluster barrier: nobody's shared memory is read remotely after it (CTAs may exit), and s_q / s_p are visible
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 
-    // ---- phase 2: dr = sc*dz + p*r + q over the same rows (cached operands first)
+    // ---- phase 2: dr = sc*dz + p*r + q over the same rows (cached operands first, then the streamed ones)
     float cq[8], cp[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -619,40 +609,35 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         cq[k] = s_q[gl];
         cp[k] = s_p[gl];
     }
-    for (int i0 = 0; p0 + i0 * pstep < npx; i0 += UB) {
-        Raw<P, POOL> w[UB];
+    auto apply = [&](int i, const Raw<P, POOL>& w) {
+        const int pi = p0 + i * pstep, uy = r0 + pi / UW, ux = pi % UW;
+        float rv[P][8], dz[P][8], act[8], dl = 0.f;
+        grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
 #pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            const int pi = min(p0 + (i0 + u) * pstep, npx - 1);
-            if (i0 + u < fp.K) {
-                const uint4* slot = cache + (size_t)(i0 + u) * RAWV * FT + tid;
+        for (int q = 0; q < P; ++q) {
+            const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+            float o[8];
 #pragma unroll
-                for (int q = 0; q < P; ++q) { w[u].r[q] = slot[q * FT]; w[u].a[q] = slot[(P + q) * FT]; }
-                if (POOL) w[u].gp = slot[2 * P * FT];
-            } else {
-                load_raw<KIND, P>(a, n, r0 + pi / UW, pi % UW, cv, w[u]);
-            }
+            for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[q][k], fmaf(cp[k], rv[q][k], cq[k]));
+            store8(a.dr.at(n, y, x, cv * 8), o);
         }
-#pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            const int pi = p0 + (i0 + u) * pstep;
-            if (pi >= npx) continue;
-            const int uy = r0 + pi / UW, ux = pi % UW;
-            float rv[P][8], dz[P][8], act[8], dl = 0.f;
-            grads_from_raw<KIND, P>(c, w[u], al, wv, rv, dz, dl, act);
-#pragma unroll
-            for (int q = 0; q < P; ++q) {
-                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
-                float o[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[q][k], fmaf(cp[k], rv[q][k], cq[k]));
-                store8(a.dr.at(n, y, x, cv * 8), o);
-            }
-        }
+    };
+    for (int i = 0; i < K && i < nu; ++i) {
+        Raw<P, POOL> w;
+        fetch(i, w);
+        apply(i, w);
+    }
+    for (int t = 0; t < nstream; ++t) {
+        cp_async_wait<S - 1>();
+        Raw<P, POOL> w;
+        fetch(K + t % S, w);
+        apply(nu - 1 - t, w);
+        if (t + S < nstream) issue(nu - 1 - (t + S), K + t % S);
+        cp_async_commit();
     }
 }
 
-struct FusedPlan { bool ok; FusedParams fp; size_t smem; int units; int ft; };
+struct FusedPlan { bool ok; FusedParams fp; size_t smem; int units; int ft; int depth; };
 
 inline int env_int(const char* name, int dflt) {
     const char* e = getenv(name);
@@ -687,7 +672,7 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     const size_t budget = (size_t)smem_kb * 1024 > red_bytes + 4096 ? (size_t)smem_kb * 1024 - red_bytes : 4096;
     const int kmax = (int)(budget / ((size_t)FT * RAWV * 16));
     const int64_t items = (int64_t)UH * UW * ncv;                     // (unit, channel vector) pairs of one unit
-    int cs = cs_env ? cs_env : 4;
+    int cs = cs_env ? cs_env : 2;
     while (cs > UH && cs > 1) cs >>= 1;
     if (cs != 1 && cs != 2 && cs != 4 && cs != 8 && cs != 16) return pl;
     pl.ft = FT;
@@ -696,20 +681,33 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     pl.fp.ups = nv / ncv;
     pl.fp.rows_pc = ceil_div(UH, cs);
     const int iters = (int)ceil_div64((int64_t)pl.fp.rows_pc * UW * ncv, FT);
-    pl.fp.K = iters < kmax ? iters : kmax;
+    // pipeline depth S (= streaming slots): 2 for the 2x2-window kinds (9 vectors per unit), else 4, or 8 with MRISR_GNBWD_D=8
+    static const int d_env = env_int("MRISR_GNBWD_D", 4);
+    const int S = POOL ? 2 : (d_env == 8 ? 8 : 4);
+    static const int k_env = env_int("MRISR_GNBWD_K", -1);
+    int slots;                                                     // shared-memory slots per thread
+    if (iters <= kmax && k_env < 0) { pl.fp.K = iters; slots = iters; }      // everything stays resident: no streaming slots
+    else {
+        if (kmax < S) return pl;
+        pl.fp.K = iters < kmax - S ? iters : kmax - S;
+        if (k_env >= 0 && k_env < pl.fp.K) pl.fp.K = k_env;
+        slots = pl.fp.K + S;
+    }
+    pl.depth = S;
     pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
-    pl.smem = (size_t)pl.fp.K * RAWV * FT * 16 + red_bytes;
+    pl.smem = (size_t)slots * RAWV * FT * 16 + red_bytes;
+    pl.fp.slots = slots;
     pl.units = a.r.N * pl.fp.ups;
     pl.ok = true;
     return pl;
 }
 
-template <int KIND, int FT>
+template <int KIND, int FT, int S>
 int run_fused(const GnBwdArgs<__nv_bfloat16>& a, const FusedPlan& pl, cudaStream_t s) {
     static bool attr_done = false;
     if (!attr_done) {
-        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_fused_kernel<KIND, FT, S>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         attr_done = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -724,7 +722,7 @@ int run_fused(const GnBwdArgs<__nv_bfloat16>& a, const FusedPlan& pl, cudaStream
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    MRISR_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gn_bwd_fused_kernel<KIND, FT>, a, pl.fp));
+    MRISR_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gn_bwd_fused_kernel<KIND, FT, S>, a, pl.fp));
     MRISR_LAUNCH_CHECK();
     const int pcs = KIND == SRC_BLEND_PS ? a.r.C / 4 : a.r.C;
     gn_bwd_finalize_kernel<__nv_bfloat16, KIND><<<pcs, FTHR, 0, s>>>(a, pl.fp.cs, pl.fp.inv_count, 0, a.r.N, 1);
@@ -739,7 +737,11 @@ int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     if (nv > NTHR) { set_error("gn_bwd: C = %d is too wide", C); return -1; }
     if constexpr (sizeof(T) == 2) {
         const FusedPlan fpl = fused_plan<KIND>(a);
-        if (fpl.ok) return fpl.ft == 256 ? run_fused<KIND, 256>(a, fpl, s) : run_fused<KIND, 512>(a, fpl, s);
+        if (fpl.ok) {
+            constexpr int S0 = KindTraits<KIND>::pool ? 2 : 4;
+            if (fpl.depth == 8) return fpl.ft == 256 ? run_fused<KIND, 256, 8>(a, fpl, s) : run_fused<KIND, 512, 8>(a, fpl, s);
+            return fpl.ft == 256 ? run_fused<KIND, 256, S0>(a, fpl, s) : run_fused<KIND, 512, S0>(a, fpl, s);
+        }
     }
     const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
     const int rows_pb = rows_per_block(UW, nv, NTHR, UNITS_PER_THREAD);

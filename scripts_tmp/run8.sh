@@ -1,10 +1,22 @@
 cd $GRAFT_REPO_ROOT
-( time timeout 900 python bench.py ) > gpurun_out/r15_bench_default.log 2>&1
-cut -c1-1500 gpurun_out/r15_bench_default.log | tail -5
-( time timeout 900 python bench.py --impl reference --steps 2 --warmup 1 ) > gpurun_out/r15_bench_ref.log 2>&1
-tail -6 gpurun_out/r15_bench_ref.log | cut -c1-900
-( time timeout 600 python bench.py --mode infer --steps 5 --warmup 3 --no-cpu-baseline ) > gpurun_out/r15_bench_infer.log 2>&1
-tail -6 gpurun_out/r15_bench_infer.log | cut -c1-700
-( time timeout 600 python -c "import __graft_entry__ as g; g.smoke()" ) > gpurun_out/r15_smoke.log 2>&1
-tail -8 gpurun_out/r15_smoke.log
-nproc; lscpu | grep "Model name"
+run() {
+  name=$1; shift
+  env "$@" timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --layer-report gpurun_out/r15_layers_$name.txt > gpurun_out/r15_bench_$name.log 2>&1
+  python - <<PY
+import json
+try:
+    d=json.loads([l for l in open('gpurun_out/r15_bench_$name.log') if l.startswith('{')][-1])
+    g=[k for k in d['kernels'] if k['kernel']=='gn_bwd'][0]
+    print('$name', 'step', round(d['ms_per_step'],3), 'gn_bwd', g['ms_per_step'])
+except Exception as e:
+    print('$name', 'FAILED', e)
+PY
+}
+timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > gpurun_out/r15_tests.log 2>&1; echo rc=$? >> gpurun_out/r15_tests.log
+tail -3 gpurun_out/r15_tests.log
+run cs2 MRISR_GNBWD_CS=2
+run cs16_res MRISR_GNBWD_CS=16 MRISR_GNBWD_SMEM_KB=190 MRISR_GNBWD_D=8
+run cs16_96 MRISR_GNBWD_CS=16
+run cs16_96_ft256 MRISR_GNBWD_CS=16 MRISR_GNBWD_FT=256
+run cs8_190_d8 MRISR_GNBWD_CS=8 MRISR_GNBWD_SMEM_KB=190 MRISR_GNBWD_D=8
+run cs1 MRISR_GNBWD_CS=1
