@@ -11,7 +11,7 @@
 namespace mrisr {
 namespace {
 constexpr int T = 32;          // output tile edge
-constexpr int NTHR = 256;
+constexpr int NTHR = 320;      // 10 warps: 312 horizontal-pass tasks of the 11-tap training configuration fill them in one round
 
 struct Taps { float w[11]; };
 
@@ -23,12 +23,38 @@ struct Geo {
     static constexpr size_t smem_floats = 2 * IN * IN + 5 * IN * MID + (GRAD ? 3 * MID * MID : 0);
 };
 
+constexpr int run_len(int extent) { return extent % 8 == 0 ? 8 : (extent % 7 == 0 ? 7 : 8); }
+
+// Register-blocked 1-D filter: a thread produces L consecutive outputs of NM maps from L + WIN - 1 inputs it loads once
+// (the plain form reads one shared-memory word per FMA and is LDS-bound; this one reads (L + WIN - 1) / (L * WIN) words).
+// Taps are applied in ascending order per output, as in the unblocked form.
+template <int L, int NM, int WIN, typename F>
+__device__ __forceinline__ void run_filter(const Taps& taps, float (&acc)[L][NM], F&& load) {
+#pragma unroll
+    for (int o = 0; o < L; ++o)
+#pragma unroll
+        for (int m = 0; m < NM; ++m) acc[o][m] = 0.f;
+#pragma unroll
+    for (int j = 0; j < L + WIN - 1; ++j) {
+        float p[NM];
+        load(j, p);
+#pragma unroll
+        for (int o = 0; o < L; ++o) {
+            const int t = j - o;
+            if (t >= 0 && t < WIN) {
+#pragma unroll
+                for (int m = 0; m < NM; ++m) acc[o][m] = fmaf(taps.w[t], p[m], acc[o][m]);
+            }
+        }
+    }
+}
+
 // scratch layout: [nblocks][2] block partials (sum|p-t|, sum S), blocks ordered n-major
 template <int R, bool GRAD>
-__global__ void __launch_bounds__(NTHR) l1_ssim_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
-                                                       float* __restrict__ dpred, float* __restrict__ partial, int H,
-                                                       int W, Taps taps, float C1, float C2, float l1_coef,
-                                                       float ssim_coef) {
+__global__ void __launch_bounds__(NTHR, 2) l1_ssim_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                          float* __restrict__ dpred, float* __restrict__ partial, int H,
+                                                          int W, Taps taps, float C1, float C2, float l1_coef,
+                                                          float ssim_coef) {
     using G = Geo<R, GRAD>;
     constexpr int IN = G::IN, MID = G::MID, HALO = G::HALO, WIN = 2 * R + 1;
     extern __shared__ float smem[];
@@ -50,80 +76,103 @@ __global__ void __launch_bounds__(NTHR) l1_ssim_kernel(const float* __restrict__
         sy[i] = in ? py[(int64_t)gy * W + gx] : 0.f;
     }
     __syncthreads();
-    // horizontal pass of x, y, xx, yy, xy
-    for (int i = tid; i < IN * MID; i += NTHR) {
-        const int r = i / MID, c = i % MID;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+    // horizontal pass of x, y, xx, yy, xy: task = (row, run of LH columns)
+    {
+        constexpr int LH = run_len(MID), RUNS = (MID + LH - 1) / LH;
+        for (int task = tid; task < IN * RUNS; task += NTHR) {
+            const int r = task / RUNS, c0 = (task % RUNS) * LH;
+            float acc[LH][5];
+            run_filter<LH, 5, WIN>(taps, acc, [&](int j, float (&p)[5]) {
+                const int idx = r * IN + min(c0 + j, IN - 1);
+                const float x = sx[idx], y = sy[idx];
+                p[0] = x; p[1] = y; p[2] = x * x; p[3] = y * y; p[4] = x * y;
+            });
 #pragma unroll
-        for (int t = 0; t < WIN; ++t) {
-            const float w = taps.w[t], x = sx[r * IN + c + t], y = sy[r * IN + c + t];
-            a0 = fmaf(w, x, a0); a1 = fmaf(w, y, a1);
-            a2 = fmaf(w, x * x, a2); a3 = fmaf(w, y * y, a3); a4 = fmaf(w, x * y, a4);
+            for (int o = 0; o < LH; ++o)
+                if (c0 + o < MID) {
+#pragma unroll
+                    for (int m = 0; m < 5; ++m) hb[m * IN * MID + r * MID + c0 + o] = acc[o][m];
+                }
         }
-        hb[i] = a0; hb[IN * MID + i] = a1; hb[2 * IN * MID + i] = a2; hb[3 * IN * MID + i] = a3; hb[4 * IN * MID + i] = a4;
     }
     __syncthreads();
-    // vertical pass -> SSIM map (+ derivative maps)
+    // vertical pass -> SSIM map (+ derivative maps): task = (run of LV rows, column)
     float ssum = 0.f, lsum = 0.f;
-    for (int i = tid; i < MID * MID; i += NTHR) {
-        const int r = i / MID, c = i % MID;
-        float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    {
+        constexpr int LV = GRAD ? run_len(MID) : 4, RUNS = (MID + LV - 1) / LV;
+        for (int task = tid; task < RUNS * MID; task += NTHR) {
+            const int r0 = (task / MID) * LV, c = task % MID;
+            float acc[LV][5];
+            run_filter<LV, 5, WIN>(taps, acc, [&](int j, float (&p)[5]) {
+                const int idx = min(r0 + j, IN - 1) * MID + c;
 #pragma unroll
-        for (int t = 0; t < WIN; ++t) {
-            const float w = taps.w[t];
-            const int j = (r + t) * MID + c;
-            m1 = fmaf(w, hb[j], m1); m2 = fmaf(w, hb[IN * MID + j], m2);
-            e11 = fmaf(w, hb[2 * IN * MID + j], e11); e22 = fmaf(w, hb[3 * IN * MID + j], e22);
-            e12 = fmaf(w, hb[4 * IN * MID + j], e12);
-        }
-        const int off = GRAD ? R : 0;
-        const int gy = ty0 - off + r, gx = tx0 - off + c;
-        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
-        const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-        const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
-        const float inv = 1.f / (B1 * B2);
-        const float S = A1 * A2 * inv;
-        const bool center = r >= off && r < off + T && c >= off && c < off + T;
-        if (in && center) ssum += S;
-        if (GRAD) {
-            const float d11 = in ? -S / B2 : 0.f;
-            const float d12 = in ? 2.f * A1 * inv : 0.f;
-            const float d1 = in ? 2.f * m2 * (A2 - A1) * inv - 2.f * m1 * S / B1 + 2.f * m1 * S / B2 : 0.f;
-            mp[i] = d1; mp[MID * MID + i] = d11; mp[2 * MID * MID + i] = d12;
+                for (int m = 0; m < 5; ++m) p[m] = hb[m * IN * MID + idx];
+            });
+#pragma unroll
+            for (int o = 0; o < LV; ++o) {
+                const int r = r0 + o;
+                if (r >= MID) continue;
+                const float m1 = acc[o][0], m2 = acc[o][1], e11 = acc[o][2], e22 = acc[o][3], e12 = acc[o][4];
+                const int off = GRAD ? R : 0;
+                const int gy = ty0 - off + r, gx = tx0 - off + c;
+                const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+                const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+                const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
+                const float inv = 1.f / (B1 * B2);
+                const float S = A1 * A2 * inv;
+                const bool center = r >= off && r < off + T && c >= off && c < off + T;
+                if (in && center) ssum += S;
+                if (GRAD) {
+                    const float d11 = in ? -S / B2 : 0.f;
+                    const float d12 = in ? 2.f * A1 * inv : 0.f;
+                    const float d1 = in ? 2.f * m2 * (A2 - A1) * inv - 2.f * m1 * S / B1 + 2.f * m1 * S / B2 : 0.f;
+                    const int i = r * MID + c;
+                    mp[i] = d1; mp[MID * MID + i] = d11; mp[2 * MID * MID + i] = d12;
+                }
+            }
         }
     }
     if (GRAD) {
         __syncthreads();
-        // horizontal pass of the three derivative maps: rows MID, cols T  (into hb)
-        for (int i = tid; i < MID * T; i += NTHR) {
-            const int r = i / T, c = i % T;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+        // horizontal pass of the three derivative maps: rows MID, cols T  (into hb); task = (row, run of 8 columns)
+        {
+            constexpr int LB = 8, RUNS = T / LB;
+            for (int task = tid; task < MID * RUNS; task += NTHR) {
+                const int r = task / RUNS, c0 = (task % RUNS) * LB;
+                float acc[LB][3];
+                run_filter<LB, 3, WIN>(taps, acc, [&](int j, float (&p)[3]) {
+                    const int idx = r * MID + c0 + j;
+                    p[0] = mp[idx]; p[1] = mp[MID * MID + idx]; p[2] = mp[2 * MID * MID + idx];
+                });
 #pragma unroll
-            for (int t = 0; t < WIN; ++t) {
-                const float w = taps.w[t];
-                const int j = r * MID + c + t;
-                a0 = fmaf(w, mp[j], a0); a1 = fmaf(w, mp[MID * MID + j], a1); a2 = fmaf(w, mp[2 * MID * MID + j], a2);
+                for (int o = 0; o < LB; ++o)
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) hb[m * MID * T + r * T + c0 + o] = acc[o][m];
             }
-            hb[i] = a0; hb[MID * T + i] = a1; hb[2 * MID * T + i] = a2;
         }
         __syncthreads();
-        for (int i = tid; i < T * T; i += NTHR) {
-            const int r = i / T, c = i % T;
-            const int gy = ty0 + r, gx = tx0 + c;
-            if (gy < H && gx < W) {
-                float g1 = 0.f, g11 = 0.f, g12 = 0.f;
+        // vertical pass + output: task = (run of 4 rows, column)
+        {
+            constexpr int LB = 4, RUNS = T / LB;
+            for (int task = tid; task < RUNS * T; task += NTHR) {
+                const int r0 = (task / T) * LB, c = task % T;
+                float acc[LB][3];
+                run_filter<LB, 3, WIN>(taps, acc, [&](int j, float (&p)[3]) {
+                    const int idx = (r0 + j) * T + c;
+                    p[0] = hb[idx]; p[1] = hb[MID * T + idx]; p[2] = hb[2 * MID * T + idx];
+                });
 #pragma unroll
-                for (int t = 0; t < WIN; ++t) {
-                    const float w = taps.w[t];
-                    const int j = (r + t) * T + c;
-                    g1 = fmaf(w, hb[j], g1); g11 = fmaf(w, hb[MID * T + j], g11); g12 = fmaf(w, hb[2 * MID * T + j], g12);
+                for (int o = 0; o < LB; ++o) {
+                    const int r = r0 + o, gy = ty0 + r, gx = tx0 + c;
+                    if (gy < H && gx < W) {
+                        const float x = sx[(r + HALO) * IN + c + HALO], y = sy[(r + HALO) * IN + c + HALO];
+                        const float d = x - y;
+                        lsum += fabsf(d);
+                        const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+                        if (dpred) dpred[(int64_t)n * H * W + (int64_t)gy * W + gx] =
+                            l1_coef * sg + ssim_coef * (acc[o][0] + 2.f * x * acc[o][1] + y * acc[o][2]);
+                    }
                 }
-                const float x = sx[(r + HALO) * IN + c + HALO], y = sy[(r + HALO) * IN + c + HALO];
-                const float d = x - y;
-                lsum += fabsf(d);
-                const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
-                if (dpred) dpred[(int64_t)n * H * W + (int64_t)gy * W + gx] =
-                    l1_coef * sg + ssim_coef * (g1 + 2.f * x * g11 + y * g12);
             }
         }
     }

@@ -194,39 +194,58 @@ __device__ __forceinline__ AdjTaps adj_taps(int i, int in_size, float scale) {
 }
 
 // gather form of the adjoint: deterministic, no atomics.  One block = `rows_pb` source rows of one sample, mapped by the
-// layout of the (4x larger) gradient tensor being read.
+// layout of the (4x larger) gradient tensor being read.  The tap tables (first destination index, count, weights) of every
+// source column and of the block's rows are built once per block in shared memory: computing them per pixel cost more
+// instructions than the gather itself.
+constexpr int kAdjMaxW = 1024, kAdjMaxRows = 64;
+struct AdjTap5 { int lo, cnt; float w[5]; float pad; };           // 32 B
 template <typename T>
 __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T> addend, Act<T> dsrc, float sy,
                                                               float sx, int rows_pb) {
+    __shared__ AdjTap5 s_tx[kAdjMaxW];
+    __shared__ AdjTap5 s_ty[kAdjMaxRows];
     const int n = blockIdx.y;
+    const int y_begin = blockIdx.x * rows_pb, y_end = min(dsrc.H, y_begin + rows_pb);
+    for (int i = threadIdx.x; i < dsrc.W + (y_end - y_begin); i += NTHR) {
+        const bool is_x = i < dsrc.W;
+        const AdjTaps t = is_x ? adj_taps(i, dsrc.W, sx) : adj_taps(y_begin + i - dsrc.W, dsrc.H, sy);
+        AdjTap5& o = is_x ? s_tx[i] : s_ty[i - dsrc.W];
+        o.lo = t.lo;
+        o.cnt = t.cnt < 5 ? t.cnt : 5;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) o.w[j] = t.w[j];
+    }
+    __syncthreads();
     const RowMap m = row_map(ddst, NTHR, threadIdx.x);
     if (!m.active) return;
     const int cv = m.cv;
-    const int y_end = min(dsrc.H, (int)(blockIdx.x + 1) * rows_pb);
-    for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
-        const AdjTaps ty = adj_taps(y, dsrc.H, sy);
+    const int ps = ddst.ps ? ddst.ps : ddst.C;
+    for (int y = y_begin; y < y_end; ++y) {
+        const AdjTap5 ty = s_ty[y - y_begin];
         for (int x = m.x0; x < dsrc.W; x += m.xstep) {
-            const AdjTaps tx = adj_taps(x, dsrc.W, sx);
+            const AdjTap5 tx = s_tx[x];
             float acc[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] = 0.f;
             if (addend.p) load8(addend.at(n, y, x, cv * 8), acc);
 #pragma unroll
-            for (int jy = 0; jy < 6; ++jy) {
+            for (int jy = 0; jy < 5; ++jy) {
                 if (jy >= ty.cnt) continue;
-                const float wy = ty.w[jy];
                 const T* rowp = ddst.at(n, ty.lo + jy, tx.lo, cv * 8);
-                const int ps = ddst.ps ? ddst.ps : ddst.C;
+                float h[8];
 #pragma unroll
-                for (int jx = 0; jx < 6; ++jx) {
+                for (int k = 0; k < 8; ++k) h[k] = 0.f;
+#pragma unroll
+                for (int jx = 0; jx < 5; ++jx) {
                     if (jx < tx.cnt) {
                         float v[8];
                         load8(rowp + (int64_t)jx * ps, v);
-                        const float w = wy * tx.w[jx];
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, v[k], acc[k]);
+                        for (int k = 0; k < 8; ++k) h[k] = fmaf(tx.w[jx], v[k], h[k]);
                     }
                 }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fmaf(ty.w[jy], h[k], acc[k]);
             }
             store8(dsrc.at(n, y, x, cv * 8), acc);
         }
@@ -312,7 +331,9 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-    const int rpb = rows_per_block(dsrc.W, dsrc.C / 8, NTHR, 2);
+    int rpb = rows_per_block(dsrc.W, dsrc.C / 8, NTHR, 4);
+    if (rpb > kAdjMaxRows) rpb = kAdjMaxRows;
+    if (dsrc.W > kAdjMaxW) { set_error("upsample2x_bwd: W = %d exceeds the tap table (%d)", dsrc.W, kAdjMaxW); return -1; }
     dim3 grid(ceil_div(dsrc.H, rpb), dsrc.N);
     upsample2x_bwd_kernel<T><<<grid, NTHR, 0, s>>>(ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W), rpb);
     MRISR_LAUNCH_CHECK();

@@ -1,6 +1,6 @@
 cd $GRAFT_REPO_ROOT
-nvidia-smi -L
-( time timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 ) > gpurun_out/r16_bench_2gpu.log 2>&1
-tail -4 gpurun_out/r16_bench_2gpu.log | cut -c1-900
-( time timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 2 --warmup 1 --impl reference ) > gpurun_out/r16_bench_2gpu_ref.log 2>&1
-tail -4 gpurun_out/r16_bench_2gpu_ref.log | cut -c1-400
+timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/r16_tests.log 2>&1; echo rc=$? >> gpurun_out/r16_tests.log
+tail -5 gpurun_out/r16_tests.log
+timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --layer-report gpurun_out/r16_layers.txt > gpurun_out/r16_bench.log 2>&1
+cut -c1-200 gpurun_out/r16_bench.log
+grep -E "l1_ssim|upsample2x_bwd" gpurun_out/r16_layers.txt
