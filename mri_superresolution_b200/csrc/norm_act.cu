@@ -104,28 +104,38 @@ __global__ void __launch_bounds__(NTHR) gn_apply_kernel(Act<T> r, const float* _
         sh[k] = beta[c] - mean * sc[k];
     }
     const int wy_end = min(WH, (int)(blockIdx.x + 1) * rows_pb);
+    // all loads of a batch are issued before the first store (the compiler cannot move a load above a store through
+    // pointers that may alias): UB units (or one 2x2 window) in flight per thread
+    constexpr int UB = 4;
     for (int wy = blockIdx.x * rows_pb; wy < wy_end; ++wy) {
-        for (int wx = m.x0; wx < WW; wx += m.xstep) {
-            if (!POOL) {
-                float v[8];
-                load8(r.at(n, wy, wx, cv * 8), v);
+        if (!POOL) {
+            for (int wx0 = m.x0; wx0 < WW; wx0 += UB * m.xstep) {
+                float v[UB][8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-                store8(a.at(n, wy, wx, cv * 8), v);
-            } else {
-                float mx[8];
+                for (int u = 0; u < UB; ++u) load8(r.at(n, wy, min(wx0 + u * m.xstep, WW - 1), cv * 8), v[u]);
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    const int wx = wx0 + u * m.xstep;
+                    if (wx >= WW) continue;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[u][k] = lrelu(fmaf(v[u][k], sc[k], sh[k]));
+                    store8(a.at(n, wy, wx, cv * 8), v[u]);
+                }
+            }
+        } else {
+            for (int wx = m.x0; wx < WW; wx += m.xstep) {
+                float v[4][8], mx[8];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) load8(r.at(n, 2 * wy + (q >> 1), 2 * wx + (q & 1), cv * 8), v[q]);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const int y = 2 * wy + (q >> 1), x = 2 * wx + (q & 1);
-                    float v[8];
-                    load8(r.at(n, y, x, cv * 8), v);
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) v[k] = lrelu(fmaf(v[k], sc[k], sh[k]));
-                    store8(a.at(n, y, x, cv * 8), v);
+                    for (int k = 0; k < 8; ++k) v[q][k] = lrelu(fmaf(v[q][k], sc[k], sh[k]));
+                    store8(a.at(n, 2 * wy + (q >> 1), 2 * wx + (q & 1), cv * 8), v[q]);
                     // max over the values as stored (rounded to T) so backward's argmax recomputation agrees
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        const float vr = to_f(from_f<T>(v[k]));
+                        const float vr = to_f(from_f<T>(v[q][k]));
                         mx[k] = q == 0 ? vr : fmaxf(mx[k], vr);
                     }
                 }
@@ -147,17 +157,29 @@ __global__ void __launch_bounds__(NTHR) upsample2x_kernel(Act<T> src, Act<T> dst
     for (int Y = blockIdx.x * rows_pb; Y < y_end; ++Y) {
         const Lerp ly = up_coord(Y, src.H, sy);
         const float h1 = ly.w1, h0 = 1.f - h1;
-        for (int X = m.x0; X < dst.W; X += m.xstep) {
-            const Lerp lx = up_coord(X, src.W, sx);
-            float v00[8], v01[8], v10[8], v11[8], o[8];
-            load8(src.at(n, ly.i0, lx.i0, cv * 8), v00);
-            load8(src.at(n, ly.i0, lx.i1, cv * 8), v01);
-            load8(src.at(n, ly.i1, lx.i0, cv * 8), v10);
-            load8(src.at(n, ly.i1, lx.i1, cv * 8), v11);
-            const float w1 = lx.w1, w0 = 1.f - w1;
+        constexpr int UB = 2;                          // destination pixels in flight per thread (8 loads before the first store)
+        for (int X0 = m.x0; X0 < dst.W; X0 += UB * m.xstep) {
+            float v[UB][4][8], w1[UB];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = h0 * (w0 * v00[k] + w1 * v01[k]) + h1 * (w0 * v10[k] + w1 * v11[k]);
-            store8(dst.at(n, Y, X, cv * 8), o);
+            for (int u = 0; u < UB; ++u) {
+                const Lerp lx = up_coord(min(X0 + u * m.xstep, dst.W - 1), src.W, sx);
+                w1[u] = lx.w1;
+                load8(src.at(n, ly.i0, lx.i0, cv * 8), v[u][0]);
+                load8(src.at(n, ly.i0, lx.i1, cv * 8), v[u][1]);
+                load8(src.at(n, ly.i1, lx.i0, cv * 8), v[u][2]);
+                load8(src.at(n, ly.i1, lx.i1, cv * 8), v[u][3]);
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const int X = X0 + u * m.xstep;
+                if (X >= dst.W) continue;
+                const float a1 = w1[u], a0 = 1.f - a1;
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    o[k] = h0 * (a0 * v[u][0][k] + a1 * v[u][1][k]) + h1 * (a0 * v[u][2][k] + a1 * v[u][3][k]);
+                store8(dst.at(n, Y, X, cv * 8), o);
+            }
         }
     }
 }
@@ -300,11 +322,11 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
     ProfScope prof_(tag, s);
     const int nv = r.C / 8;
     if (pooled.p) {
-        const int rpb = rows_per_block(r.W / 2, nv, NTHR, 2);
+        const int rpb = rows_per_block(r.W / 2, nv, NTHR, 4);
         dim3 grid(ceil_div(r.H / 2, rpb), r.N);
         gn_apply_kernel<T, true><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     } else {
-        const int rpb = rows_per_block(r.W, nv, NTHR, 4);
+        const int rpb = rows_per_block(r.W, nv, NTHR, 16);
         dim3 grid(ceil_div(r.H, rpb), r.N);
         gn_apply_kernel<T, false><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     }
@@ -315,7 +337,7 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     ProfScope prof_("upsample2x", s);
-    const int rpb = rows_per_block(dst.W, dst.C / 8, NTHR, 4);
+    const int rpb = rows_per_block(dst.W, dst.C / 8, NTHR, 8);
     dim3 grid(ceil_div(dst.H, rpb), dst.N);
     upsample2x_kernel<T><<<grid, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rpb);
     MRISR_LAUNCH_CHECK();

@@ -225,17 +225,17 @@ __global__ void __launch_bounds__(192, 1) wgrad_rows_kernel(const __grid_constan
 }
 
 // dw[co][ci_off + ci][tap] = sum over CTAs of partial[cta][dx][m][co],  m = ((dy * KP + plane) * 8 + c8), ci = plane * 8 + c8
-__global__ void wgrad_rows_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int ctas, int M, int KP, int N,
-                                         int Cin_total, int ci_off) {
+__global__ void __launch_bounds__(256) wgrad_rows_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int ctas,
+                                                                 int M, int KP, int N, int Cin_total, int ci_off) {
     const int total = 9 * KP * 8 * N;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const int co = i % N, ci = (i / N) % (KP * 8), tap = i / (N * KP * 8);
+    const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+    const bool valid = i < total;
+    const int iv = valid ? i : 0;
+    const int co = iv % N, ci = (iv / N) % (KP * 8), tap = iv / (N * KP * 8);
     const int dy = tap / 3, dx = tap - dy * 3;
     const int m = (dy * KP + (ci >> 3)) * 8 + (ci & 7);
-    float t = 0.f;
-    for (int c = 0; c < ctas; ++c) t += partial[(((int64_t)c * 3 + dx) * M + m) * N + co];
-    dw[((int64_t)co * Cin_total + ci_off + ci) * 9 + tap] = t;
+    const float t = sliced_partial_sum(partial + ((int64_t)dx * M + m) * N + co, (int64_t)3 * M * N, ctas, valid);
+    if (valid && threadIdx.x < 32) dw[((int64_t)co * Cin_total + ci_off + ci) * 9 + tap] = t;
 }
 
 struct RowsPlan { int SW, strips, tiles, R, RC, chunks, units, grid; uint32_t PLB, seg_bytes, smem_bytes, tmem_cols; bool ok; };
@@ -318,7 +318,7 @@ static int wgrad_rows_launch_group(const bf16* x, int64_t csx, int KP, const Wgr
     MRISR_LAUNCH_CHECK();
     const int M = KP == 2 ? 64 : 128;
     const int total = 9 * KP * 8 * Cout;
-    tc::wgrad_rows_reduce_kernel<<<ceil_div(total, 256), 256, 0, s>>>(a.partial, a.dw, pl.grid, M, KP, Cout, Cin_total, ci_off);
+    tc::wgrad_rows_reduce_kernel<<<ceil_div(total, 32), 256, 0, s>>>(a.partial, a.dw, pl.grid, M, KP, Cout, Cin_total, ci_off);
     MRISR_LAUNCH_CHECK();
     return 0;
 }

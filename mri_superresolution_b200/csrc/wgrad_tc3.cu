@@ -167,20 +167,20 @@ wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant
 
 // dw[co][ci][tap] = sum over splits of partial[split][group][dx * npairs + pair][(j & 1) * 64 + ci % 64][co]
 // with slab s = dy * cpt + ci / 64, group = s / SG, j = s % SG, pair = j / 2
-__global__ void wgrad_tc3_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int Cin, int Cout, int cpt,
-                                        int SG, int npairs, int groups, int splits) {
+__global__ void __launch_bounds__(256) wgrad_tc3_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int Cin,
+                                                                int Cout, int cpt, int SG, int npairs, int groups, int splits) {
     const int total = 9 * Cin * Cout;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const int co = i % Cout, ci = (i / Cout) % Cin, tap = i / (Cout * Cin);
+    const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+    const bool valid = i < total;
+    const int iv = valid ? i : 0;
+    const int co = iv % Cout, ci = (iv / Cout) % Cin, tap = iv / (Cout * Cin);
     const int dy = tap / 3, dx = tap - dy * 3;
     const int s = dy * cpt + ci / 64, g = s / SG, j = s - g * SG;
     const int tile = dx * npairs + j / 2, row = (j & 1) * 64 + (ci & 63);
     const int ntiles = 3 * npairs;
-    float t = 0.f;
-    for (int sp = 0; sp < splits; ++sp)
-        t += partial[((((int64_t)sp * groups + g) * ntiles + tile) * 128 + row) * Cout + co];
-    dw[((int64_t)co * Cin + ci) * 9 + tap] = t;
+    const float t = sliced_partial_sum(partial + ((((int64_t)g * ntiles + tile) * 128 + row) * Cout + co),
+                                       (int64_t)groups * ntiles * 128 * Cout, splits, valid);
+    if (valid && threadIdx.x < 32) dw[((int64_t)co * Cin + ci) * 9 + tap] = t;
 }
 
 struct Wgrad3Plan { int SG, npairs, groups, splits, kb_per_split, num_kb, stages, nslabs, cpt; uint32_t stage_bytes, smem_bytes, tmem_cols; bool ok; };
@@ -270,7 +270,7 @@ int launch_wgrad_tc3(const WgradArgs<bf16>& a, cudaStream_t s) {
     tc::wgrad_tc3_kernel<<<grid, 192, pl.smem_bytes, s>>>(tX1, tX2, tDY, p);
     MRISR_LAUNCH_CHECK();
     const int total = 9 * Cin * Cout;
-    tc::wgrad_tc3_reduce_kernel<<<ceil_div(total, 256), 256, 0, s>>>(a.partial, a.dw, Cin, Cout, pl.cpt, pl.SG, pl.npairs, pl.groups, pl.splits);
+    tc::wgrad_tc3_reduce_kernel<<<ceil_div(total, 32), 256, 0, s>>>(a.partial, a.dw, Cin, Cout, pl.cpt, pl.SG, pl.npairs, pl.groups, pl.splits);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
