@@ -55,7 +55,7 @@ __device__ __forceinline__ void quad_values(const BlendArgs<T>& a, const BlendCt
 
 // one block = `rows_pb` LOW-resolution rows of one sample; a thread owns one channel vector and walks 2x2 output quads
 template <typename T>
-__global__ void __launch_bounds__(NTHR) head_blend_kernel(BlendArgs<T> a, int rows_pb) {
+__global__ void __launch_bounds__(NTHR, 2) head_blend_kernel(BlendArgs<T> a, int rows_pb) {
     const int n = blockIdx.y;
     const RowMap m = row_map(a.xm, NTHR, threadIdx.x);
     if (!m.active) return;
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(NTHR) head_blend_kernel(BlendArgs<T> a, int ro
 
 // scratch[n * gridDim.x + blockIdx.x] = sum over the block's quads of dxm * (xb - xp)
 template <typename T>
-__global__ void __launch_bounds__(NTHR) blend_dalpha_kernel(BlendArgs<T> a, Act<T> dxm, float* __restrict__ scratch, int rows_pb) {
+__global__ void __launch_bounds__(NTHR, 2) blend_dalpha_kernel(BlendArgs<T> a, Act<T> dxm, float* __restrict__ scratch, int rows_pb) {
     __shared__ float s_w[NTHR / 32];
     const int n = blockIdx.y;
     const RowMap m = row_map(a.xm, NTHR, threadIdx.x);

@@ -189,6 +189,19 @@ __global__ void __launch_bounds__(256) wgrad_tc_reduce_kernel(const float* __res
     dw[((int64_t)co * Cin + ci) * taps + tap] = t;
 }
 
+// few splits: one thread per output, serial over the splits
+__global__ void wgrad_tc_reduce_serial_kernel(const float* __restrict__ partial, float* __restrict__ dw, int Mtot, int Cout, int Cin,
+                                              int taps, int splits) {
+    const int64_t total = (int64_t)Mtot * Cout;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    float t = 0.f;
+    for (int s = 0; s < splits; ++s) t += partial[(int64_t)s * total + i];
+    const int co = (int)(i % Cout), m = (int)(i / Cout);
+    const int tap = m / Cin, ci = m - tap * Cin;
+    dw[((int64_t)co * Cin + ci) * taps + tap] = t;
+}
+
 struct WgradPlan {
     int CS, CSB, MT, stages, num_slabs, Mtiles, groups, splits, kb_per_split, num_kb;
     uint32_t stage_bytes, smem_bytes;
@@ -295,7 +308,10 @@ int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
     tc::wgrad_tc_kernel<<<grid, 192, pl.smem_bytes, s>>>(tX1, tX2, tDY, p);
     MRISR_LAUNCH_CHECK();
     const int64_t total = (int64_t)p.Mtot * Cout;
-    tc::wgrad_tc_reduce_kernel<<<(unsigned)ceil_div64(total, 32), 256, 0, s>>>(a.partial, a.dw, p.Mtot, Cout, Cin, p.taps, pl.splits);
+    if (pl.splits >= 16)
+        tc::wgrad_tc_reduce_kernel<<<(unsigned)ceil_div64(total, 32), 256, 0, s>>>(a.partial, a.dw, p.Mtot, Cout, Cin, p.taps, pl.splits);
+    else
+        tc::wgrad_tc_reduce_serial_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, s>>>(a.partial, a.dw, p.Mtot, Cout, Cin, p.taps, pl.splits);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
