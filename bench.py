@@ -87,8 +87,8 @@ def tag_bytes(tag: str, n: int) -> float:
         c, hw = rest.split("@")
         hh, ww = [int(v) for v in hw.split("x")]
         elems = float(n) * int(c) * hh * ww
-        if name == "gn_bwd":                 # reduce pass reads r, g; apply pass reads r, g and writes dr
-            return 5 * 2.0 * elems
+        if name == "gn_bwd":                 # algorithmic minimum: read r and g once, write dr once (the kernel's second
+            return 3 * 2.0 * elems           # phase re-reads both from HBM today: see roofline.traffic)
         if name == "gn_apply":               # read r, write a (+ pooled quarter)
             return (2 + (0.25 if variant.endswith("1") else 0.0)) * 2.0 * elems
         if name == "upsample2x_bwd":         # dims are the low-resolution result: read 4x gradient (+ addend), write 1x
@@ -96,6 +96,13 @@ def tag_bytes(tag: str, n: int) -> float:
     except Exception:
         pass
     return 0.0
+
+
+# DRAM bytes per step of a kernel family from the committed ncu capture (profiles/r01_launches_step_v2.md, batch 64 train
+# step): dram__bytes_read.sum + dram__bytes_write.sum summed over the family's launches.  Reported per launch as
+# roofline.traffic when the bench runs the same workload.
+NCU_TRAFFIC_PER_STEP = {"gn_bwd": (13758 + 3462) * 1e6, "gn_apply": (1969 + 1334 + 478 + 433) * 1e6,
+                        "upsample2x_bwd": (1825 + 326) * 1e6, "l1_ssim": (134 + 43) * 1e6}
 
 
 def peaks():
@@ -384,10 +391,14 @@ def run_ours(args):
         elif tf["bytes"] > 0:
             achieved = tf["bytes"] / (tf["ms"] * 1e-3) / 1e9
             roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
-                        "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": None,
-                        "peak_source": pk["source"], "bytes_per_step": tf["bytes"], "ms_per_step": round(tf["ms"], 4),
+                        "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4),
+                        "traffic": (NCU_TRAFFIC_PER_STEP[top["kernel"]] / max(tf["calls"], 1)
+                                    if top["kernel"] in NCU_TRAFFIC_PER_STEP and nb == PER_GPU_BATCH and mode == "train" else None),
+                        "traffic_source": "profiles/r01_launches_step_v2.md (ncu dram bytes of the family / launches)",
+                        "peak_source": pk["source"], "bytes_per_step": tf["bytes"],
+                        "bytes_per_launch": tf["bytes"] / max(tf["calls"], 1), "ms_per_step": round(tf["ms"], 4),
                         "launches_per_step": tf["calls"], "share_of_step": top["share"],
-                        "note": "elementwise glue kernel family; algorithmic bytes = passes x bf16 tensor size (DESIGN.md 4)"}
+                        "note": "elementwise kernel family; algorithmic bytes = minimum passes x bf16 tensor size (DESIGN.md 4)"}
         else:
             roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": None, "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": None, "traffic": None, "share_of_step": top["share"],

@@ -16,6 +16,7 @@
 //     HBM time, profiles/r01_conv_ring_issue_bound.md);
 //   * GroupNorm partial statistics are accumulated in registers across the CTA's whole run and flushed once per sample.
 // Warp roles: warp 0 producer (bulk copies), warp 1 TMEM allocator + MMA issuer, warps 2..5 epilogue.
+#include <stdlib.h>
 #include "kernels.cuh"
 #include "tc_common.cuh"
 
@@ -341,26 +342,40 @@ __global__ void pack_weights_ring_kernel(const float* __restrict__ w, __nv_bfloa
     }
 }
 
-struct RingPlan { int G, R, halo_lo, halo_hi; uint32_t w_bytes, smem_bytes; bool ok; };
+struct RingPlan { int G, R, halo_lo, halo_hi, per_sm; uint32_t w_bytes, smem_bytes; bool ok; };
 
 // largest block (G = 2, then 1) and deepest look-ahead that fit shared memory
+// MRISR_RING_CTAS=1 keeps one CTA per SM (A/B measurements); default 2 where shared memory and TMEM allow
+static int ring_ctas_wanted() {
+    static const int want = [] { const char* e = getenv("MRISR_RING_CTAS"); return e ? atoi(e) : 2; }();
+    return want;
+}
+constexpr uint32_t kRingSmemTwoCtas = 113u * 1024u;      // (228 KB - 2 x 1 KB reserved) / 2
+
 static RingPlan ring_plan(int W, int Cin, int Cout) {
     RingPlan pl;
     const int pw = W + 2;
     pl.w_bytes = 9u * Cin * Cout * 2u;
     const uint32_t w_pad = (pl.w_bytes + 1023u) & ~1023u;
-    pl.ok = false; pl.R = 0; pl.G = 0; pl.smem_bytes = 0; pl.halo_lo = pl.halo_hi = 0;
-    for (int G = 2; G >= 1 && !pl.ok; --G) {
-        const int BLK = 128 * G;
-        const int lo = (pw + 1 + BLK - 1) / BLK, hi = (BLK + pw) / BLK;
-        if ((int64_t)lo * BLK > planar_guard(W)) continue;
-        const int live = lo + hi + 1;
-        for (int ahead = 4; ahead >= 1; --ahead) {
-            const int R = live + ahead;
-            const uint32_t need = w_pad + (uint32_t)(Cin / 8) * ((uint32_t)R * 2048u * G + 2048u) + 1024u;
-            if (R <= kRingMaxSlots && need <= 225u * 1024u) {
-                pl.G = G; pl.R = R; pl.halo_lo = lo; pl.halo_hi = hi; pl.smem_bytes = need; pl.ok = true;
-                break;
+    pl.ok = false; pl.R = 0; pl.G = 0; pl.smem_bytes = 0; pl.halo_lo = pl.halo_hi = 0; pl.per_sm = 1;
+    // pass 0: a ring small enough for two CTAs per SM (measured 1.6x on the 16-channel 512^2 layers: one CTA's epilogue and
+    // producer stalls hide behind the other's MMAs); pass 1: the deepest ring that fits one CTA
+    for (int pass = ring_ctas_wanted() >= 2 ? 0 : 1; pass < 2 && !pl.ok; ++pass) {
+        const uint32_t limit = pass == 0 ? kRingSmemTwoCtas : 225u * 1024u;
+        for (int G = 2; G >= 1 && !pl.ok; --G) {
+            if (pass == 0 && 4 * G * Cout > 256) continue;              // TMEM columns of two CTAs
+            const int BLK = 128 * G;
+            const int lo = (pw + 1 + BLK - 1) / BLK, hi = (BLK + pw) / BLK;
+            if ((int64_t)lo * BLK > planar_guard(W)) continue;
+            const int live = lo + hi + 1;
+            for (int ahead = 4; ahead >= (pass == 0 ? 2 : 1); --ahead) {      // two CTAs with look-ahead 1 measured slower than one
+                const int R = live + ahead;
+                const uint32_t need = w_pad + (uint32_t)(Cin / 8) * ((uint32_t)R * 2048u * G + 2048u) + 1024u;
+                if (R <= kRingMaxSlots && need <= limit) {
+                    pl.G = G; pl.R = R; pl.halo_lo = lo; pl.halo_hi = hi; pl.smem_bytes = need; pl.ok = true;
+                    pl.per_sm = pass == 0 ? 2 : 1;
+                    break;
+                }
             }
         }
     }
@@ -412,7 +427,9 @@ static RingGeom ring_geom(int N, int H, int W, int Cin, int Cout) {
     const int64_t rows = (int64_t)N * (H + 2) * (W + 2);
     const int BLK = 128 * pl.G;
     g.num_steps = (int)((rows + BLK - 1) / BLK);
-    g.steps_per_cta = ceil_div(g.num_steps, tc::num_sms());
+    // two CTAs per SM when shared memory and TMEM (4 accumulator buffers x G x Cout columns each) allow: one CTA's epilogue and
+    // producer stalls overlap the other's MMAs (MRISR_RING_CTAS=1 disables)
+    g.steps_per_cta = ceil_div(g.num_steps, tc::num_sms() * pl.per_sm);
     g.grid = ceil_div(g.num_steps, g.steps_per_cta);
     g.rec_per_warp = (int)(((int64_t)g.steps_per_cta * BLK) / ((int64_t)(H + 2) * (W + 2))) + 2;
     return g;

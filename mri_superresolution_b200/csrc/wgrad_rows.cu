@@ -12,6 +12,7 @@
 // A CTA walks work units (sample, column strip <= 256 wide, chunk of rows), keeps accumulating into the same TMEM tile and
 // writes one partial at the end; wgrad_rows_reduce_kernel sums the partials in a fixed order (deterministic).
 // Warp roles: warp 0 producer (cp.async.bulk per plane row segment), warp 1 MMA issuer, warps 2..5 epilogue.
+#include <stdlib.h>
 #include "kernels.cuh"
 #include "tc_common.cuh"
 
@@ -238,27 +239,40 @@ __global__ void __launch_bounds__(256) wgrad_rows_reduce_kernel(const float* __r
     if (valid && threadIdx.x < 32) dw[((int64_t)co * Cin_total + ci_off + ci) * 9 + tap] = t;
 }
 
-struct RowsPlan { int SW, strips, tiles, R, RC, chunks, units, grid; uint32_t PLB, seg_bytes, smem_bytes, tmem_cols; bool ok; };
+struct RowsPlan { int SW, strips, tiles, R, RC, chunks, units, grid, per_sm; uint32_t PLB, seg_bytes, smem_bytes, tmem_cols; bool ok; };
 
+// One CTA per SM with 256-pixel strips and the deepest row ring, or (pass 0, when it fits) two CTAs per SM with 128-pixel strips:
+// the producer / epilogue stalls of one CTA hide behind the other's MMAs (the same effect measured on conv_ring).
+// MRISR_ROWS_CTAS=1 keeps the one-CTA plan.
 static RowsPlan rows_plan(int N, int H, int W, int KP, int Cout) {
+    static const int want = [] { const char* e = getenv("MRISR_ROWS_CTAS"); return e ? atoi(e) : 2; }();
     RowsPlan pl;
     pl.ok = false;
-    pl.strips = (W + 255) / 256;
-    if (W % pl.strips) return pl;
-    pl.SW = W / pl.strips;
-    pl.tiles = (pl.SW + 127) / 128;
-    pl.seg_bytes = (uint32_t)(pl.SW + 2) * 16u;
-    pl.PLB = (((uint32_t)(pl.tiles * 128 + 3) * 16u) + 127u) & ~127u;
-    if ((pl.PLB >> 4) >= (1u << 14)) return pl;
-    const uint32_t rowb = (uint32_t)KP * pl.PLB, drowb = (uint32_t)(Cout / 8) * pl.PLB;
-    pl.R = 0;
-    for (int R = kRowsMaxSlots; R >= 4; --R) {
-        const uint32_t need = (uint32_t)(R + 3) * rowb + (uint32_t)kRowsDySlots * drowb + 1024u;
-        if (need <= 225u * 1024u) { pl.R = R; pl.smem_bytes = need; break; }
+    const int cols = 3 * Cout;
+    pl.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+    pl.per_sm = 1;
+    for (int pass = (want >= 2 && pl.tmem_cols <= 256) ? 0 : 1; pass < 2; ++pass) {
+        const int sw_max = pass == 0 ? 128 : 256;
+        const uint32_t limit = pass == 0 ? 113u * 1024u : 225u * 1024u;
+        pl.strips = (W + sw_max - 1) / sw_max;
+        if (W % pl.strips) { if (pass == 0) continue; return pl; }
+        pl.SW = W / pl.strips;
+        pl.tiles = (pl.SW + 127) / 128;
+        pl.seg_bytes = (uint32_t)(pl.SW + 2) * 16u;
+        pl.PLB = (((uint32_t)(pl.tiles * 128 + 3) * 16u) + 127u) & ~127u;
+        if ((pl.PLB >> 4) >= (1u << 14)) return pl;
+        const uint32_t rowb = (uint32_t)KP * pl.PLB, drowb = (uint32_t)(Cout / 8) * pl.PLB;
+        pl.R = 0;
+        for (int R = kRowsMaxSlots; R >= (pass == 0 ? 6 : 4); --R) {
+            const uint32_t need = (uint32_t)(R + 3) * rowb + (uint32_t)kRowsDySlots * drowb + 1024u;
+            if (need <= limit) { pl.R = R; pl.smem_bytes = need; break; }
+        }
+        if (pl.R) { pl.per_sm = pass == 0 ? 2 : 1; break; }
+        if (pass == 1) return pl;
     }
-    if (!pl.R) return pl;
     // rows per chunk: enough units to balance the CTAs (>= 6 per CTA when possible), halo overhead 2 / RC
-    const int64_t want_units = (int64_t)num_sms() * 6;
+    const int ctas = num_sms() * pl.per_sm;
+    const int64_t want_units = (int64_t)ctas * 6;
     int rc = (int)(((int64_t)N * pl.strips * H) / want_units);
     if (rc < 8) rc = 8;
     if (rc > 64) rc = 64;
@@ -266,9 +280,7 @@ static RowsPlan rows_plan(int N, int H, int W, int KP, int Cout) {
     pl.RC = rc;
     pl.chunks = (H + rc - 1) / rc;
     pl.units = N * pl.strips * pl.chunks;
-    pl.grid = pl.units < num_sms() ? pl.units : num_sms();
-    const int cols = 3 * Cout;
-    pl.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+    pl.grid = pl.units < ctas ? pl.units : ctas;
     pl.ok = true;
     return pl;
 }
@@ -288,7 +300,7 @@ bool wgrad_rows_supported(int N, int H, int W, int C1, int C2, int Cout, int ks)
 }
 
 size_t wgrad_rows_scratch_elems(int N, int H, int W, int Cin, int Cout) {
-    return (size_t)tc::num_sms() * 3 * 128 * Cout;
+    return (size_t)tc::num_sms() * 2 * 3 * 128 * Cout;          // up to two CTAs per SM, one partial each
 }
 
 static int wgrad_rows_launch_group(const bf16* x, int64_t csx, int KP, const WgradArgs<bf16>& a, int Cin_total, int ci_off, cudaStream_t s) {
