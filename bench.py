@@ -319,13 +319,21 @@ def run_ours(args):
     value = nb * world * args.steps / (ms * 1e-3)
 
     # ---- end to end: pinned host inputs, H2D copies and loss read-back inside the timed region
-    xb, tb = torch.empty_like(x_dev), torch.empty_like(t_dev)
+    # Every step's batch is copied host -> device once, by the package's double-buffered DevicePrefetcher (the copy of batch
+    # i+1 runs on a side stream while step i computes; utils/prefetch.py), as a training loop built on this package would.
+    from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
     d2h = [0]
+    e2e_steps = max(2, min(args.steps, 10))
+
+    def host_batches():
+        while True:
+            yield (x_pin, t_pin) if mode == "train" else (x_pin,)         # inference needs no target
+
+    feeder = DevicePrefetcher(host_batches(), dev)
 
     def e2e_step():
-        xb.copy_(x_pin, non_blocking=True)
-        tb.copy_(t_pin, non_blocking=True)
-        r = step(xb, tb)
+        batch = next(feeder)
+        r = step(batch[0], batch[1] if mode == "train" else None)
         if mode == "train":
             r.item()                                 # scripts/train.py:321 reads the loss every step
             d2h[0] = 4
@@ -334,10 +342,10 @@ def run_ours(args):
             d2h[0] = r[:1].numel() * 4
 
     e2e_step()
-    e2e_steps = max(2, min(args.steps, 10))
+    bytes0 = feeder.bytes_copied
     ms_e2e = timed(e2e_step, e2e_steps)
     e2e_value = nb * world * e2e_steps / (ms_e2e * 1e-3)
-    h2d = x_pin.numel() * 4 + t_pin.numel() * 4
+    h2d = (feeder.bytes_copied - bytes0) // e2e_steps          # counted from the tensors copied inside the timed region
 
     # ---- per-kernel attribution (same workload, CUDA events on the launching stream) ---------
     roofline, families = None, []
@@ -433,7 +441,9 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
             "config": workload_config(mode, world, nb, args.perceptual),
             "e2e": {"value": e2e_value, "unit": "slices/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h[0],
-                    "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps},
+                    "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
+                    "pipeline": "pinned host batch -> DevicePrefetcher (one H2D copy per step, on a side stream, double-buffered) "
+                                "-> public modules -> result read back every step"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "kernels": families, "whole_step": whole,
         }

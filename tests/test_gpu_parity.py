@@ -390,3 +390,22 @@ def test_perceptual_target_branch_has_no_gradient_and_l2_alias(golden_dir):
     assert t.grad is None and p.grad is not None                  # utils/losses.py:146-147
     assert abs(a.item() - pmse(p.detach(), t.detach()).item()) < 1e-6 * abs(a.item())   # :130 'l2' == 'mse'
     assert pl2(p.detach(), p.detach()).item() == 0.0
+
+
+@pytest.mark.gpu
+def test_device_prefetcher_order_and_reuse():
+    """DevicePrefetcher hands out every host batch once, in order, while the next one is being staged."""
+    from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
+    dev = torch.device("cuda:0")
+    host = [(torch.full((4, 1, 8, 8), float(i)).pin_memory(), torch.full((4, 1, 16, 16), float(-i)).pin_memory()) for i in range(7)]
+    seen = []
+    acc = torch.zeros((), device=dev)
+    for x, t in DevicePrefetcher(host, dev):
+        assert x.is_cuda and t.is_cuda
+        # a long-running consumer on the current stream: the slot must not be overwritten under it
+        for _ in range(50):
+            acc = acc + (x.sum() + t.sum()) * 0.0
+        seen.append((float(x.mean()), float(t.mean())))
+    assert seen == [(float(i), float(-i)) for i in range(7)]
+    with pytest.raises(ValueError):
+        DevicePrefetcher(host, dev, slots=1)

@@ -191,3 +191,9 @@ def test_vgg_abi_size_queries():
     assert L.mrisr_vgg_workspace_bytes(2, 40, 64, arr, len(cfg), 1) == 0             # H % 16 != 0
     bad = (ctypes.c_int * 2)(64, -1)
     assert L.mrisr_vgg_packed_bytes(bad, 2) == 0                                      # must end on a conv
+
+
+def test_device_prefetcher_rejects_cpu_device():
+    from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
+    with pytest.raises(RuntimeError):
+        DevicePrefetcher([], "cpu")
