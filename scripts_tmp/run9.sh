@@ -1,7 +1,3 @@
 cd $GRAFT_REPO_ROOT
-timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/r25_tests.log 2>&1; echo rc=$? >> gpurun_out/r25_tests.log
-tail -4 gpurun_out/r25_tests.log
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --layer-report gpurun_out/r25_layers.txt > gpurun_out/r25_bench.log 2>&1
-cut -c1-1200 gpurun_out/r25_bench.log
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --mode infer > gpurun_out/r25_bench_infer.log 2>&1
-cut -c1-900 gpurun_out/r25_bench_infer.log
+timeout 900 python -m pytest tests/test_gpu_knobs.py -q -rP -m gpu > gpurun_out/r28_tests.log 2>&1; echo rc=$? >> gpurun_out/r28_tests.log
+grep -E "passed|failed|^[a-z_0-9]+ \{|Assertion"  gpurun_out/r28_tests.log
