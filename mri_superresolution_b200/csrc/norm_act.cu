@@ -1,6 +1,9 @@
 // GroupNorm statistics / apply (+LeakyReLU, +2x2 max-pool), bilinear x2 up-sampling and its adjoint.
 // Forward semantics follow models/unet_model.py:29-37 (conv -> GroupNorm(8) -> LeakyReLU(0.2)),
 // :52 (MaxPool2d(2)), :71/:151 (Upsample(2, bilinear, align_corners=True)).
+#include <stdlib.h>
+#include <algorithm>
+#include <vector>
 #include "kernels.cuh"
 
 namespace mrisr {
@@ -274,6 +277,145 @@ __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T
     }
 }
 
+// Tiled form for bf16: a CTA owns TR source rows x TW source columns of one (sample, channel-vector range).  The destination
+// gradient rows / columns that tile gathers from are contiguous 16-byte vectors in both layouts (one plane of a planar-8
+// tensor, or all channels of an NHWC tensor), so they are staged global -> shared memory once with cp.async (coalesced,
+// everything in flight at once) and the ~16-20 taps of every output then read shared memory instead of L1/L2.
+__device__ __forceinline__ void cp_async16_na(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+struct UpBwdTile { int TR, TW, ncv, rows_cap, cols_cap, tiles_x, tiles_y; };
+
+__global__ void __launch_bounds__(NTHR, 2) upsample2x_bwd_tiled_kernel(Act<__nv_bfloat16> ddst, Act<__nv_bfloat16> addend,
+                                                                       Act<__nv_bfloat16> dsrc, float sy, float sx, UpBwdTile tp) {
+    using T = __nv_bfloat16;
+    extern __shared__ uint4 up_smem[];
+    uint4* rows = up_smem;                                                          // [rows_cap][cols_cap] 16-byte vectors
+    AdjTap5* s_tx = reinterpret_cast<AdjTap5*>(up_smem + (size_t)tp.rows_cap * tp.cols_cap);    // [TW]
+    AdjTap5* s_ty = s_tx + tp.TW;                                                   // [TR]
+    const int tid = threadIdx.x, ncv = tp.ncv;
+    const int tile_x = blockIdx.x % tp.tiles_x, tile_y = blockIdx.x / tp.tiles_x;
+    const int units_per_sample = (dsrc.C / 8) / ncv;
+    const int n = blockIdx.y / units_per_sample, cv0 = (blockIdx.y % units_per_sample) * ncv;
+    const int y0 = tile_y * tp.TR, x0 = tile_x * tp.TW;
+    const int th = min(tp.TR, dsrc.H - y0), tw = min(tp.TW, dsrc.W - x0);
+    for (int i = tid; i < tw + th; i += NTHR) {
+        const bool is_x = i < tw;
+        const AdjTaps t = is_x ? adj_taps(x0 + i, dsrc.W, sx) : adj_taps(y0 + i - tw, dsrc.H, sy);
+        AdjTap5& o = is_x ? s_tx[i] : s_ty[i - tw];
+        o.lo = t.lo;
+        o.cnt = t.cnt < 5 ? t.cnt : 5;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) o.w[j] = t.w[j];
+    }
+    __syncthreads();
+    const int d_lo = s_ty[0].lo, d_hi = s_ty[th - 1].lo + s_ty[th - 1].cnt - 1;
+    const int X_lo = s_tx[0].lo, X_hi = s_tx[tw - 1].lo + s_tx[tw - 1].cnt - 1;
+    const int nrows = d_hi - d_lo + 1, ncols = (X_hi - X_lo + 1) * ncv;
+    if (nrows > tp.rows_cap || ncols > tp.cols_cap) __trap();                       // the host sized the caps from the same taps
+    for (int idx = tid; idx < nrows * ncols; idx += NTHR) {
+        const int r = idx / ncols, c = idx - r * ncols;
+        cp_async16_na(rows + (size_t)r * tp.cols_cap + c, ddst.at(n, d_lo + r, X_lo, cv0 * 8) + (int64_t)c * 8);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    const int per_row = tw * ncv;
+    for (int idx = tid; idx < th * per_row; idx += NTHR) {
+        const int yl = idx / per_row, rem = idx - yl * per_row, xl = rem / ncv, cvl = rem - xl * ncv;
+        float add[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) add[k] = 0.f;
+        if (addend.p) load8(addend.at(n, y0 + yl, x0 + xl, (cv0 + cvl) * 8), add);     // consumed last: latency hidden by the taps
+        const AdjTap5 ty = s_ty[yl], tx = s_tx[xl];
+        const uint4* base = rows + (size_t)(ty.lo - d_lo) * tp.cols_cap + (size_t)(tx.lo - X_lo) * ncv + cvl;
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll
+        for (int jy = 0; jy < 5; ++jy) {
+            if (jy >= ty.cnt) continue;
+            float h[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) h[k] = 0.f;
+#pragma unroll
+            for (int jx = 0; jx < 5; ++jx) {
+                if (jx < tx.cnt) {
+                    const uint4 raw = base[(size_t)jy * tp.cols_cap + jx * ncv];
+                    const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        h[2 * i] = fmaf(tx.w[jx], __uint_as_float(w4[i] << 16), h[2 * i]);
+                        h[2 * i + 1] = fmaf(tx.w[jx], __uint_as_float(w4[i] & 0xffff0000u), h[2 * i + 1]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = fmaf(ty.w[jy], h[k], acc[k]);
+        }
+        // same association as the untiled kernel: addend first, then the taps in (jy, jx) order
+        float o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = add[k] + acc[k];
+        store8(dsrc.at(n, y0 + yl, x0 + xl, (cv0 + cvl) * 8), o);
+    }
+}
+
+// host replica of the tap ranges (same float arithmetic as up_coord / adj_weight): first and last destination index with a
+// non-zero weight for every source index
+static void adj_ranges_host(int in_size, std::vector<int>& lo, std::vector<int>& hi) {
+    const float scale = up_scale(in_size);
+    lo.assign(in_size, 1 << 30);
+    hi.assign(in_size, -1);
+    for (int d = 0; d < 2 * in_size; ++d) {
+        const float sf = scale * (float)d;
+        const int i0 = (int)sf, i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+        const float w1 = sf - (float)i0;
+        const float wa = (1.f - w1) + (i1 == i0 ? w1 : 0.f);               // adj_weight(d, i0)
+        if (wa != 0.f) { lo[i0] = std::min(lo[i0], d); hi[i0] = std::max(hi[i0], d); }
+        if (i1 != i0 && w1 != 0.f) { lo[i1] = std::min(lo[i1], d); hi[i1] = std::max(hi[i1], d); }
+    }
+}
+static int max_span(const std::vector<int>& lo, const std::vector<int>& hi, int tile) {
+    int m = 0;
+    const int n = (int)lo.size();
+    for (int a = 0; a < n; a += tile) {
+        const int b = std::min(n, a + tile) - 1;
+        m = std::max(m, hi[b] - lo[a] + 1);
+    }
+    return m;
+}
+
+static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>& dsrc, UpBwdTile& tp, size_t& smem) {
+    static const bool on = [] { const char* e = getenv("MRISR_UPBWD_TILED"); return !(e && e[0] == '0'); }();
+    if (!on || dsrc.C % 8) return false;
+    const int nv = dsrc.C / 8;
+    // the staged tensor is the (4x larger) destination gradient: units follow ITS layout (a plane, or all channels of an NHWC
+    // tensor); the low-resolution result is addressed per vector and may have the other layout (level 1 -> level 0 boundary)
+    tp.ncv = ddst.planar() ? 1 : nv;
+    std::vector<int> ylo, yhi, xlo, xhi;
+    adj_ranges_host(dsrc.H, ylo, yhi);
+    adj_ranges_host(dsrc.W, xlo, xhi);
+    for (int i = 0; i < dsrc.H; ++i) if (yhi[i] < 0 || yhi[i] - ylo[i] + 1 > 5) return false;
+    for (int i = 0; i < dsrc.W; ++i) if (xhi[i] < 0 || xhi[i] - xlo[i] + 1 > 5) return false;
+    int tw = (528 / tp.ncv - 4) / 2;
+    if (tw < 4) return false;
+    if (tw > dsrc.W) tw = dsrc.W;
+    tp.TW = tw;
+    tp.cols_cap = max_span(xlo, xhi, tw) * tp.ncv;
+    const size_t budget = 100u * 1024u;                               // two CTAs per SM
+    tp.TR = 0;
+    for (int tr = std::min(dsrc.H, 16); tr >= 1; --tr) {
+        const int rc = max_span(ylo, yhi, tr);
+        const size_t need = (size_t)rc * tp.cols_cap * 16 + (size_t)(tw + tr) * sizeof(AdjTap5);
+        if (need <= budget) { tp.TR = tr; tp.rows_cap = rc; smem = need; break; }
+    }
+    if (!tp.TR) return false;
+    tp.tiles_x = ceil_div(dsrc.W, tp.TW);
+    tp.tiles_y = ceil_div(dsrc.H, tp.TR);
+    return true;
+}
+
 inline int grid_for(int64_t total) {
     int64_t b = ceil_div64(total, NTHR);
     if (b > 148 * 16) b = 148 * 16;
@@ -353,6 +495,21 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
+    if constexpr (sizeof(T) == 2) {
+        UpBwdTile tp;
+        size_t smem = 0;
+        if (up_bwd_plan(ddst, dsrc, tp, smem)) {
+            static bool attr_done = false;
+            if (!attr_done) {
+                MRISR_CUDA_CHECK(cudaFuncSetAttribute(upsample2x_bwd_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+                attr_done = true;
+            }
+            dim3 grid(tp.tiles_x * tp.tiles_y, dsrc.N * ((dsrc.C / 8) / tp.ncv));
+            upsample2x_bwd_tiled_kernel<<<grid, NTHR, smem, s>>>(ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W), tp);
+            MRISR_LAUNCH_CHECK();
+            return 0;
+        }
+    }
     int rpb = rows_per_block(dsrc.W, dsrc.C / 8, NTHR, 4);
     if (rpb > kAdjMaxRows) rpb = kAdjMaxRows;
     if (dsrc.W > kAdjMaxW) { set_error("upsample2x_bwd: W = %d exceeds the tap table (%d)", dsrc.W, kAdjMaxW); return -1; }
