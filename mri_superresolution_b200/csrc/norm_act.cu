@@ -3,6 +3,8 @@
 // :52 (MaxPool2d(2)), :71/:151 (Upsample(2, bilinear, align_corners=True)).
 #include <stdlib.h>
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <vector>
 #include "kernels.cuh"
 
@@ -286,79 +288,113 @@ __device__ __forceinline__ void cp_async16_na(void* smem_dst, const void* gsrc) 
 }
 struct UpBwdTile { int TR, TW, ncv, rows_cap, cols_cap, tiles_x, tiles_y; };
 
+// tap table of one axis (in_size entries), built once per size and kept for the life of the library
+__global__ void adj_table_kernel(AdjTap5* __restrict__ tab, int in_size, float scale) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in_size) return;
+    const AdjTaps t = adj_taps(i, in_size, scale);
+    AdjTap5 o;
+    o.lo = t.lo;
+    o.cnt = t.cnt < 5 ? t.cnt : 5;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) o.w[j] = t.w[j];
+    o.pad = 0.f;
+    tab[i] = o;
+}
+
 __global__ void __launch_bounds__(NTHR, 2) upsample2x_bwd_tiled_kernel(Act<__nv_bfloat16> ddst, Act<__nv_bfloat16> addend,
-                                                                       Act<__nv_bfloat16> dsrc, float sy, float sx, UpBwdTile tp) {
-    using T = __nv_bfloat16;
+                                                                       Act<__nv_bfloat16> dsrc, const AdjTap5* __restrict__ tab_y,
+                                                                       const AdjTap5* __restrict__ tab_x, UpBwdTile tp) {
     extern __shared__ uint4 up_smem[];
     uint4* rows = up_smem;                                                          // [rows_cap][cols_cap] 16-byte vectors
-    AdjTap5* s_tx = reinterpret_cast<AdjTap5*>(up_smem + (size_t)tp.rows_cap * tp.cols_cap);    // [TW]
-    AdjTap5* s_ty = s_tx + tp.TW;                                                   // [TR]
+    AdjTap5* s_ty = reinterpret_cast<AdjTap5*>(up_smem + (size_t)tp.rows_cap * tp.cols_cap);    // [TR]
     const int tid = threadIdx.x, ncv = tp.ncv;
     const int tile_x = blockIdx.x % tp.tiles_x, tile_y = blockIdx.x / tp.tiles_x;
     const int units_per_sample = (dsrc.C / 8) / ncv;
     const int n = blockIdx.y / units_per_sample, cv0 = (blockIdx.y % units_per_sample) * ncv;
     const int y0 = tile_y * tp.TR, x0 = tile_x * tp.TW;
     const int th = min(tp.TR, dsrc.H - y0), tw = min(tp.TW, dsrc.W - x0);
-    for (int i = tid; i < tw + th; i += NTHR) {
-        const bool is_x = i < tw;
-        const AdjTaps t = is_x ? adj_taps(x0 + i, dsrc.W, sx) : adj_taps(y0 + i - tw, dsrc.H, sy);
-        AdjTap5& o = is_x ? s_tx[i] : s_ty[i - tw];
-        o.lo = t.lo;
-        o.cnt = t.cnt < 5 ? t.cnt : 5;
-#pragma unroll
-        for (int j = 0; j < 5; ++j) o.w[j] = t.w[j];
-    }
-    __syncthreads();
-    const int d_lo = s_ty[0].lo, d_hi = s_ty[th - 1].lo + s_ty[th - 1].cnt - 1;
-    const int X_lo = s_tx[0].lo, X_hi = s_tx[tw - 1].lo + s_tx[tw - 1].cnt - 1;
-    const int nrows = d_hi - d_lo + 1, ncols = (X_hi - X_lo + 1) * ncv;
+    const AdjTap5 ya = tab_y[y0], yb = tab_y[y0 + th - 1], xa = tab_x[x0], xb = tab_x[x0 + tw - 1];
+    const int d_lo = ya.lo, nrows = yb.lo + yb.cnt - d_lo;
+    const int X_lo = xa.lo, ncols = (xb.lo + xb.cnt - X_lo) * ncv;
     if (nrows > tp.rows_cap || ncols > tp.cols_cap) __trap();                       // the host sized the caps from the same taps
-    for (int idx = tid; idx < nrows * ncols; idx += NTHR) {
-        const int r = idx / ncols, c = idx - r * ncols;
-        cp_async16_na(rows + (size_t)r * tp.cols_cap + c, ddst.at(n, d_lo + r, X_lo, cv0 * 8) + (int64_t)c * 8);
+    for (int r = 0; r < nrows; ++r) {
+        const __nv_bfloat16* src = ddst.at(n, d_lo + r, X_lo, cv0 * 8);
+        uint4* dst = rows + (size_t)r * tp.cols_cap;
+        for (int c = tid; c < ncols; c += NTHR) cp_async16_na(dst + c, src + (int64_t)c * 8);
     }
+    if (tid < th * 2) cp_async16_na(reinterpret_cast<uint4*>(s_ty) + tid, reinterpret_cast<const uint4*>(tab_y + y0) + tid);
     asm volatile("cp.async.commit_group;" ::: "memory");
+    // a thread owns at most two (column, channel vector) pairs of the tile and walks the tile's rows: its horizontal taps stay
+    // in registers
+    const int per_row = tw * ncv;
+    AdjTap5 tx[2];
+    int xl[2], cvl[2], off[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int j = min(tid + u * NTHR, per_row - 1);
+        xl[u] = j / ncv;
+        cvl[u] = j - xl[u] * ncv;
+        tx[u] = tab_x[x0 + xl[u]];
+        off[u] = (tx[u].lo - X_lo) * ncv + cvl[u];
+    }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    const int per_row = tw * ncv;
-    for (int idx = tid; idx < th * per_row; idx += NTHR) {
-        const int yl = idx / per_row, rem = idx - yl * per_row, xl = rem / ncv, cvl = rem - xl * ncv;
-        float add[8];
+    for (int yl = 0; yl < th; ++yl) {
+        const AdjTap5 ty = s_ty[yl];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) add[k] = 0.f;
-        if (addend.p) load8(addend.at(n, y0 + yl, x0 + xl, (cv0 + cvl) * 8), add);     // consumed last: latency hidden by the taps
-        const AdjTap5 ty = s_ty[yl], tx = s_tx[xl];
-        const uint4* base = rows + (size_t)(ty.lo - d_lo) * tp.cols_cap + (size_t)(tx.lo - X_lo) * ncv + cvl;
-        float acc[8];
+        for (int u = 0; u < 2; ++u) {
+            if (tid + u * NTHR >= per_row) continue;
+            float add[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+            for (int k = 0; k < 8; ++k) add[k] = 0.f;
+            if (addend.p) load8(addend.at(n, y0 + yl, x0 + xl[u], (cv0 + cvl[u]) * 8), add);   // consumed last
+            const uint4* base = rows + (size_t)(ty.lo - d_lo) * tp.cols_cap + off[u];
+            float acc[8];
 #pragma unroll
-        for (int jy = 0; jy < 5; ++jy) {
-            if (jy >= ty.cnt) continue;
-            float h[8];
+            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+            for (int jy = 0; jy < ty.cnt; ++jy) {                     // warp-uniform trip count (one row per iteration of yl)
+                const float wy = s_ty[yl].w[jy];
+                float h[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) h[k] = 0.f;
+                for (int k = 0; k < 8; ++k) h[k] = 0.f;
 #pragma unroll
-            for (int jx = 0; jx < 5; ++jx) {
-                if (jx < tx.cnt) {
-                    const uint4 raw = base[(size_t)jy * tp.cols_cap + jx * ncv];
-                    const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
+                for (int jx = 0; jx < 5; ++jx) {
+                    if (jx < tx[u].cnt) {
+                        const uint4 raw = base[(size_t)jy * tp.cols_cap + jx * ncv];
+                        const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        h[2 * i] = fmaf(tx.w[jx], __uint_as_float(w4[i] << 16), h[2 * i]);
-                        h[2 * i + 1] = fmaf(tx.w[jx], __uint_as_float(w4[i] & 0xffff0000u), h[2 * i + 1]);
+                        for (int i = 0; i < 4; ++i) {
+                            h[2 * i] = fmaf(tx[u].w[jx], __uint_as_float(w4[i] << 16), h[2 * i]);
+                            h[2 * i + 1] = fmaf(tx[u].w[jx], __uint_as_float(w4[i] & 0xffff0000u), h[2 * i + 1]);
+                        }
                     }
                 }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fmaf(wy, h[k], acc[k]);
             }
+            float o[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = fmaf(ty.w[jy], h[k], acc[k]);
+            for (int k = 0; k < 8; ++k) o[k] = add[k] + acc[k];
+            store8(dsrc.at(n, y0 + yl, x0 + xl[u], (cv0 + cvl[u]) * 8), o);
         }
-        // same association as the untiled kernel: addend first, then the taps in (jy, jx) order
-        float o[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = add[k] + acc[k];
-        store8(dsrc.at(n, y0 + yl, x0 + xl, (cv0 + cvl) * 8), o);
     }
+}
+
+// device tap tables, one per axis length, built on first use (a handful of sizes per network)
+static const AdjTap5* adj_table(int in_size, cudaStream_t s) {
+    static std::mutex mu;
+    static std::map<int, AdjTap5*> tabs;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = tabs.find(in_size);
+    if (it != tabs.end()) return it->second;
+    AdjTap5* p = nullptr;
+    if (cudaMalloc(&p, (size_t)in_size * sizeof(AdjTap5)) != cudaSuccess) return nullptr;
+    adj_table_kernel<<<ceil_div(in_size, 128), 128, 0, s>>>(p, in_size, up_scale(in_size));
+    count_launch();
+    if (cudaStreamSynchronize(s) != cudaSuccess) { cudaFree(p); return nullptr; }   // first use only: other streams may read it next
+    tabs[in_size] = p;
+    return p;
 }
 
 // host replica of the tap ranges (same float arithmetic as up_coord / adj_weight): first and last destination index with a
@@ -389,6 +425,7 @@ static int max_span(const std::vector<int>& lo, const std::vector<int>& hi, int 
 static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>& dsrc, UpBwdTile& tp, size_t& smem) {
     static const bool on = [] { const char* e = getenv("MRISR_UPBWD_TILED"); return !(e && e[0] == '0'); }();
     if (!on || dsrc.C % 8) return false;
+    if (ddst.planar() != dsrc.planar()) return false;      // level 1 -> level 0 boundary: per-vector strided stores, the gather form is faster
     const int nv = dsrc.C / 8;
     // the staged tensor is the (4x larger) destination gradient: units follow ITS layout (a plane, or all channels of an NHWC
     // tensor); the low-resolution result is addressed per vector and may have the other layout (level 1 -> level 0 boundary)
@@ -398,7 +435,8 @@ static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>
     adj_ranges_host(dsrc.W, xlo, xhi);
     for (int i = 0; i < dsrc.H; ++i) if (yhi[i] < 0 || yhi[i] - ylo[i] + 1 > 5) return false;
     for (int i = 0; i < dsrc.W; ++i) if (xhi[i] < 0 || xhi[i] - xlo[i] + 1 > 5) return false;
-    int tw = (528 / tp.ncv - 4) / 2;
+    int tw = (528 / tp.ncv - 4) / 2;                                  // tile columns x channel vectors <= 2 x 256 threads
+    if (tw * tp.ncv > 2 * NTHR) tw = 2 * NTHR / tp.ncv;
     if (tw < 4) return false;
     if (tw > dsrc.W) tw = dsrc.W;
     tp.TW = tw;
@@ -407,7 +445,7 @@ static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>
     tp.TR = 0;
     for (int tr = std::min(dsrc.H, 16); tr >= 1; --tr) {
         const int rc = max_span(ylo, yhi, tr);
-        const size_t need = (size_t)rc * tp.cols_cap * 16 + (size_t)(tw + tr) * sizeof(AdjTap5);
+        const size_t need = (size_t)rc * tp.cols_cap * 16 + (size_t)tr * sizeof(AdjTap5);
         if (need <= budget) { tp.TR = tr; tp.rows_cap = rc; smem = need; break; }
     }
     if (!tp.TR) return false;
@@ -504,8 +542,11 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
                 MRISR_CUDA_CHECK(cudaFuncSetAttribute(upsample2x_bwd_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
                 attr_done = true;
             }
+            const AdjTap5* ty = adj_table(dsrc.H, s);
+            const AdjTap5* tx = dsrc.W == dsrc.H ? ty : adj_table(dsrc.W, s);
+            if (!ty || !tx) { set_error("upsample2x_bwd: tap table allocation failed"); return -1; }
             dim3 grid(tp.tiles_x * tp.tiles_y, dsrc.N * ((dsrc.C / 8) / tp.ncv));
-            upsample2x_bwd_tiled_kernel<<<grid, NTHR, smem, s>>>(ddst, addend, dsrc, up_scale(dsrc.H), up_scale(dsrc.W), tp);
+            upsample2x_bwd_tiled_kernel<<<grid, NTHR, smem, s>>>(ddst, addend, dsrc, ty, tx, tp);
             MRISR_LAUNCH_CHECK();
             return 0;
         }
