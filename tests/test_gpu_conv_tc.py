@@ -125,6 +125,8 @@ SHAPES = [
     (2, 20, 28, 128, 0, 64, 3, False),      # merged-tap weight gradient: two slab groups
     (1, 32, 32, 128, 128, 128, 3, False),   # ... six groups of two slabs, concat
     (5, 16, 16, 64, 0, 128, 3, False),      # ... odd slab count in the last group
+    (2, 24, 24, 32, 32, 64, 3, False),      # ... 32-channel slabs (64-byte swizzle), six slabs = one full + one half M tile
+    (2, 20, 36, 32, 0, 128, 3, False),      # ... 32-channel slabs, Cout = 128: one tile of three slabs
 ]
 
 
