@@ -55,6 +55,7 @@ struct Wgrad3Params {
     uint32_t stage_bytes, b_bytes, idesc, tmem_cols;
 };
 
+template <int CS>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant__ CUtensorMap tmX2,
                  const __grid_constant__ CUtensorMap tmDY, const Wgrad3Params p) {
@@ -88,8 +89,8 @@ wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant
 
     if (warp == 0) {
         if (lane == 0) {
-            const uint32_t slab = slab_bytes3(p.CS);
-            const uint32_t tx_bytes = (uint32_t)sgv * (66u * (uint32_t)p.CS * 2u) + p.b_bytes;
+            constexpr uint32_t slab = slab_bytes3(CS);
+            const uint32_t tx_bytes = (uint32_t)sgv * (66u * (uint32_t)CS * 2u) + p.b_bytes;
             int stage = 0;
             uint32_t phase = 0;
             for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -101,8 +102,8 @@ wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant
                     const int s = slab0 + j, dy = s / p.cpt, chunk = s - dy * p.cpt;
                     const int r = row0 + (dy - 1) * p.pw - 1;      // first of the 66 rows: tap (dy, dx = -1)
                     uint8_t* dst = base + (size_t)j * slab;
-                    if (chunk < p.chunks1) tma_load_2d(dst, &tmX1, &full_bar[stage], chunk * p.CS, r);
-                    else tma_load_2d(dst, &tmX2, &full_bar[stage], (chunk - p.chunks1) * p.CS, r);
+                    if (chunk < p.chunks1) tma_load_2d(dst, &tmX1, &full_bar[stage], chunk * CS, r);
+                    else tma_load_2d(dst, &tmX2, &full_bar[stage], (chunk - p.chunks1) * CS, r);
                 }
                 uint8_t* bdst = base + (size_t)p.SG * slab;
                 for (int b = 0; b < p.BN / 64; ++b)
@@ -113,12 +114,13 @@ wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant
     } else if (warp == 1) {
         // MN-major operands.  A: CS-channel slabs, rows of CS * 2 bytes with the matching swizzle; LBO = next slab, SBO = next 8
         // pixels; a K step of 16 pixels = 2 SBO.  B (dY): 64-channel slabs with the 128-byte swizzle.
-        const uint32_t slab = slab_bytes3(p.CS), row16 = (uint32_t)p.CS * 2u >> 4, sbo_a = 8u * (uint32_t)p.CS * 2u;
-        const uint32_t a_hi = (sbo_a >> 4) | (1u << 14) | (layout_type_for(p.CS * 2) << 29);
+        constexpr uint32_t slab = slab_bytes3(CS);
+        const uint32_t row16 = (uint32_t)CS * 2u >> 4, sbo_a = 8u * (uint32_t)CS * 2u;
+        const uint32_t a_hi = (sbo_a >> 4) | (1u << 14) | (layout_type_for(CS * 2) << 29);
         const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (layout_type_for(128) << 29);
         const uint32_t a_lo0 = ((slab >> 4) << 16) | (smem_u32(smem) >> 4);
         const uint32_t b_lo0 = ((8192u >> 4) << 16) | ((smem_u32(smem) + (uint32_t)p.SG * slab) >> 4);
-        const uint32_t spt = 128u / (uint32_t)p.CS, kstep_a = 2u * sbo_a >> 4;
+        const uint32_t spt = 128u / (uint32_t)CS, kstep_a = 2u * sbo_a >> 4;
         const uint32_t stage16 = p.stage_bytes >> 4;
         const uint32_t bn = (uint32_t)p.BN, idesc = p.idesc;
         const int npv = (sgv + (int)spt - 1) / (int)spt;           // M tiles that hold at least one valid slab
@@ -152,7 +154,7 @@ wgrad_tc3_kernel(const __grid_constant__ CUtensorMap tmX1, const __grid_constant
         const int ntiles = 3 * p.npairs;
         const int row = q * 32 + lane;
         for (int t = 0; t < ntiles; ++t) {
-            if ((t % p.npairs) * (128 / p.CS) >= sgv) continue;    // M tile without valid slabs: never accumulated
+            if ((t % p.npairs) * (128 / CS) >= sgv) continue;    // M tile without valid slabs: never accumulated
             float* out = p.partial + ((((int64_t)blockIdx.y * gridDim.x + g) * ntiles + t) * 128 + row) * p.BN;
             for (int c0 = 0; c0 < p.BN; c0 += 16) {
                 float v[16];
@@ -275,11 +277,13 @@ int launch_wgrad_tc3(const WgradArgs<bf16>& a, cudaStream_t s) {
     p.tmem_cols = pl.tmem_cols;
     static bool attr_done = false;
     if (!attr_done) {
-        MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc3_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc3_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_done = true;
     }
     dim3 grid(pl.groups, pl.splits);
-    tc::wgrad_tc3_kernel<<<grid, 192, pl.smem_bytes, s>>>(tX1, tX2, tDY, p);
+    if (pl.CS == 64) tc::wgrad_tc3_kernel<64><<<grid, 192, pl.smem_bytes, s>>>(tX1, tX2, tDY, p);
+    else tc::wgrad_tc3_kernel<32><<<grid, 192, pl.smem_bytes, s>>>(tX1, tX2, tDY, p);
     MRISR_LAUNCH_CHECK();
     const int total = 9 * Cin * Cout;
     tc::wgrad_tc3_reduce_kernel<<<ceil_div(total, 32), 256, 0, s>>>(a.partial, a.dw, Cin, Cout, pl.cpt, pl.SG, pl.npairs, pl.groups, pl.splits, pl.CS);
