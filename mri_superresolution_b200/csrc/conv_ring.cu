@@ -304,12 +304,16 @@ __global__ void __launch_bounds__(192, 1) conv_ring_kernel(const __grid_constant
 
 // stats[n][g] = (mean, rstd) from the per-warp records of conv_ring_kernel, summed in a fixed order (deterministic)
 __global__ void __launch_bounds__(256) gn_finalize_ring_kernel(const float* __restrict__ rec, float* __restrict__ stats,
-                                                               int num_rec, double count) {
+                                                               int rec_per_cta, int num_ctas, int64_t px_per_cta, int64_t S, double count) {
     __shared__ double s_acc[16][16];
     const int n = blockIdx.x;
     const int idx = threadIdx.x & 15, tl = threadIdx.x >> 4;
+    // only the CTAs whose pixel range [c * px_per_cta, (c + 1) * px_per_cta) meets sample n can hold records of it (each record
+    // still carries its sample index; a CTA's range usually straddles two samples)
+    const int c_lo = (int)(((int64_t)n * S) / px_per_cta);
+    const int c_hi = min(num_ctas - 1, (int)((((int64_t)n + 1) * S - 1) / px_per_cta));
     double acc = 0.0;
-    for (int r = tl; r < num_rec; r += 16) {
+    for (int r = c_lo * rec_per_cta + tl; r < (c_hi + 1) * rec_per_cta; r += 16) {
         const float* e = rec + (int64_t)r * kRingRecFloats;
         if (__float_as_int(e[16]) == n) acc += (double)e[idx];
     }
@@ -444,7 +448,8 @@ int conv_ring_stat_elems(int N, int H, int W, int Cin, int Cout) {
 int launch_gn_finalize_ring(const float* rec, float* stats, int N, int H, int W, int Cin, int Cout, double count, cudaStream_t s) {
     ProfScope prof_("gn_finalize", s);
     const RingGeom g = ring_geom(N, H, W, Cin, Cout);
-    tc::gn_finalize_ring_kernel<<<N, 256, 0, s>>>(rec, stats, g.grid * 4 * g.rec_per_warp, count);
+    tc::gn_finalize_ring_kernel<<<N, 256, 0, s>>>(rec, stats, 4 * g.rec_per_warp, g.grid, (int64_t)g.steps_per_cta * 128 * g.G,
+                                                  (int64_t)(H + 2) * (W + 2), count);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
