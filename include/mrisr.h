@@ -76,6 +76,24 @@ int mrisr_unet_backward(const float* params, const float* dy, const float* y, fl
                         void* workspace, size_t workspace_bytes, int N, int H, int W, int base_filters,
                         int precision, void* stream);
 
+/* ---- data-parallel support: gradient-readiness marks ------------------------------------------------------------
+ * The reference is single-device (scripts/train.py:296-318 has no exchange step); BASELINE.json config 3 adds a bucketed
+ * gradient all-reduce that overlaps the backward pass.  The backward schedule finishes the conv blocks in the order
+ * 19, 17, 18, 16, 15, ..., 0 and parameter offsets grow with the block index, so after block l every arena element at
+ * offset >= mrisr_unet_grads_final_from(f, l) is final.  mrisr_unet_backward_marked is mrisr_unet_backward that also
+ * records host_mark_events[k] (cudaEvent_t, e.g. from mrisr_event_create) on `stream` as soon as every gradient at
+ * offset >= host_mark_offsets[k] is final: a side stream that waits on event k may all-reduce grads[offsets[k] : ) while
+ * the rest of the backward pass still runs.  Both arrays are HOST arrays of n_marks (<= 32) entries. */
+int64_t mrisr_unet_grads_final_from(int base_filters, int conv_index);
+int mrisr_unet_backward_marked(const float* params, const float* dy, const float* y, float* grads, float* dx,
+                               void* workspace, size_t workspace_bytes, int N, int H, int W, int base_filters,
+                               int precision, void* stream, int n_marks, const int64_t* host_mark_offsets,
+                               void* const* host_mark_events);
+/* timing-disabled CUDA events owned by the library (NULL on failure), and cudaStreamWaitEvent on a caller stream */
+void* mrisr_event_create(void);
+int   mrisr_event_destroy(void* event);
+int   mrisr_stream_wait_event(void* stream, void* event);
+
 /* ---- fused L1 + SSIM loss and gradient (replaces utils/losses.py:27-81,200-226) ------------ */
 /* out5 (device, 5 floats): [0] mean|p-t|  [1] unclamped SSIM  [2] total = l1_w*L1 + ssim_w*(1-clamp(ssim,0,1))
  *                          [3], [4] reserved (perceptual term, total incl. perceptual).

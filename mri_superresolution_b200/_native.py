@@ -32,6 +32,12 @@ SIGNATURES = {
                                    c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mrisr_unet_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                     c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_unet_grads_final_from": (c_int64, [c_int, c_int]),
+    "mrisr_unet_backward_marked": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                           c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "mrisr_event_create": (c_void_p, []),
+    "mrisr_event_destroy": (c_int, [c_void_p]),
+    "mrisr_stream_wait_event": (c_int, [c_void_p, c_void_p]),
     "mrisr_l1_ssim_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mrisr_l1_ssim_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                       c_float, c_float, c_int, c_float, c_float, c_void_p]),

@@ -8,6 +8,14 @@ namespace mrisr {
 
 static inline bool is_up1x1(int l) { return l == 8 || l == 11 || l == 14; }
 
+// Arena offset from which every gradient is final once the backward schedule has finished conv block `l`
+// (schedule order 19, 17, 18, 16, 15, ..., 0; alpha, offset 0, is produced with block 19).
+static int64_t grads_final_from(const ParamLayout& pl, const ConvDesc (&conv)[kNumConv], int l) {
+    if (l >= 19 || l == 17) return pl.off[conv[19].w];
+    if (l == 18) return pl.off[conv[17].w];
+    return l <= 0 ? 0 : pl.off[conv[l].w];
+}
+
 template <typename T>
 struct Runner {
     Workspace<T>& ws;
@@ -122,6 +130,21 @@ struct Runner {
 
     // ---- backward helpers ----
     float* grads;
+    // gradient-readiness marks (include/mrisr.h, mrisr_unet_backward_marked): event k is recorded on the stream as soon as
+    // every arena element at offset >= mark_off[k] has its final value
+    int n_marks = 0;
+    const int64_t* mark_off = nullptr;
+    void* const* mark_ev = nullptr;
+    unsigned marks_done = 0;
+    int block_done(int l) {
+        const int64_t from = grads_final_from(pl, ws.conv, l);
+        for (int k = 0; k < n_marks; ++k)
+            if (!(marks_done >> k & 1u) && mark_off[k] >= from) {
+                MRISR_CUDA_CHECK(cudaEventRecord((cudaEvent_t)mark_ev[k], s));
+                marks_done |= 1u << k;
+            }
+        return 0;
+    }
     float* GP(int idx) const { return grads + pl.off[idx]; }
 
     GnBwdArgs<T> gn_args(int l, int kind, Act<T> g, int coff) {
@@ -188,27 +211,46 @@ struct Runner {
             TRY(conv_bwd(19, ws.XM, none, ws.dR[19], true));          // G[19] = d(blend)
         }
         TRY(launch_blend_dalpha<T>(blend_args(), ws.G[19], GP(0), ws.misc, s));
+        TRY(block_done(19));
         TRY(block_bwd(17, SRC_BLEND_BIL, ws.G[19], 0, none, ws.UB, none));        // G[17] = d(UB)
         TRY(block_bwd(18, SRC_BLEND_PS, ws.G[19], 0, none, ws.A[16], none));      // G[18] = d(y3) via pixel-shuffle branch
         TRY(launch_colsum<T>(ws.dR[18], GP(ws.conv[18].bias), ws.misc, s));
+        TRY(block_done(18));
         TRY(launch_upsample2x_bwd<T>(ws.G[17], ws.G[18], ws.DY3, s));
         TRY(block_bwd(16, SRC_DIRECT, ws.DY3, 0, none, ws.A[15], none));
+        TRY(block_done(16));
         TRY(block_bwd(15, SRC_DIRECT, ws.G[16], 0, none, ws.A[1], ws.A[14]));     // G[15]: [skip x1 | up]
+        TRY(block_done(15));
         TRY(up_branch_bwd(14, ws.G[15], f, ws.A[13]));
+        TRY(block_done(14));
         TRY(block_bwd(13, SRC_DIRECT, ws.G[14], 0, none, ws.A[12], none));
+        TRY(block_done(13));
         TRY(block_bwd(12, SRC_DIRECT, ws.G[13], 0, none, ws.A[3], ws.A[11]));
+        TRY(block_done(12));
         TRY(up_branch_bwd(11, ws.G[12], 2 * f, ws.A[10]));
+        TRY(block_done(11));
         TRY(block_bwd(10, SRC_DIRECT, ws.G[11], 0, none, ws.A[9], none));
+        TRY(block_done(10));
         TRY(block_bwd(9, SRC_DIRECT, ws.G[10], 0, none, ws.A[5], ws.A[8]));
+        TRY(block_done(9));
         TRY(up_branch_bwd(8, ws.G[9], 4 * f, ws.A[7]));
+        TRY(block_done(8));
         TRY(block_bwd(7, SRC_DIRECT, ws.G[8], 0, none, ws.A[6], none));
+        TRY(block_done(7));
         TRY(block_bwd(6, SRC_DIRECT, ws.G[7], 0, none, ws.P[5], none));           // G[6] = d(pool(x3))
+        TRY(block_done(6));
         TRY(block_bwd(5, SRC_DIRECT_POOL, ws.G[9], 0, ws.G[6], ws.A[4], none));
+        TRY(block_done(5));
         TRY(block_bwd(4, SRC_DIRECT, ws.G[5], 0, none, ws.P[3], none));
+        TRY(block_done(4));
         TRY(block_bwd(3, SRC_DIRECT_POOL, ws.G[12], 0, ws.G[4], ws.A[2], none));
+        TRY(block_done(3));
         TRY(block_bwd(2, SRC_DIRECT, ws.G[3], 0, none, ws.P[1], none));
+        TRY(block_done(2));
         TRY(block_bwd(1, SRC_DIRECT_POOL, ws.G[15], 0, ws.G[2], ws.A[0], none));
+        TRY(block_done(1));
         TRY(block_bwd(0, SRC_DIRECT, ws.G[1], 0, none, ws.X0, none, false));
+        TRY(block_done(0));
         return 0;
     }
 };
@@ -226,11 +268,12 @@ static int forward_t(const float* params, const float* x, float* y, void* wsp, s
 
 template <typename T>
 static int backward_t(const float* params, const float* dy, const float* y, float* grads, void* wsp, size_t wsb, int N,
-                      int H, int W, int f, cudaStream_t s) {
+                      int H, int W, int f, cudaStream_t s, int n_marks, const int64_t* mark_off, void* const* mark_ev) {
     Workspace<T> ws(wsp, N, H, W, f, true);
     if (ws.bytes > wsb) { set_error("workspace too small: need %zu bytes, got %zu", ws.bytes, wsb); return MRISR_E_WORKSPACE; }
     ParamLayout pl(f);
     Runner<T> r{ws, pl, params, s};
+    r.n_marks = n_marks; r.mark_off = mark_off; r.mark_ev = mark_ev;
     return r.backward(dy, y, grads);
 }
 
@@ -303,15 +346,46 @@ int mrisr_unet_forward(const float* params, const float* x, float* y, void* work
     return forward_t<__nv_bfloat16>(params, x, y, workspace, workspace_bytes, N, H, W, f, train, s);
 }
 
-int mrisr_unet_backward(const float* params, const float* dy, const float* y, float* grads, float* dx, void* workspace,
-                        size_t workspace_bytes, int N, int H, int W, int f, int precision, void* stream) {
+int mrisr_unet_backward_marked(const float* params, const float* dy, const float* y, float* grads, float* dx,
+                               void* workspace, size_t workspace_bytes, int N, int H, int W, int f, int precision,
+                               void* stream, int n_marks, const int64_t* host_mark_offsets, void* const* host_mark_events) {
     if (!params || !dy || !y || !grads || !workspace) { set_error("null pointer argument"); return MRISR_E_BADARG; }
     if (dx) { set_error("gradient wrt the input image is not provided by this path (pass dx = NULL)"); return MRISR_E_BADARG; }
+    if (n_marks < 0 || n_marks > 32 || (n_marks > 0 && (!host_mark_offsets || !host_mark_events))) {
+        set_error("gradient marks: 0..32 marks with host arrays of offsets and events"); return MRISR_E_BADARG;
+    }
+    for (int k = 0; k < n_marks; ++k)
+        if (host_mark_offsets[k] < 0 || !host_mark_events[k]) { set_error("gradient mark %d: negative offset or null event", k); return MRISR_E_BADARG; }
     int rc = check_shape(N, H, W, f, precision);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    if (precision == MRISR_FP32) return backward_t<float>(params, dy, y, grads, workspace, workspace_bytes, N, H, W, f, s);
-    return backward_t<__nv_bfloat16>(params, dy, y, grads, workspace, workspace_bytes, N, H, W, f, s);
+    if (precision == MRISR_FP32)
+        return backward_t<float>(params, dy, y, grads, workspace, workspace_bytes, N, H, W, f, s, n_marks, host_mark_offsets, host_mark_events);
+    return backward_t<__nv_bfloat16>(params, dy, y, grads, workspace, workspace_bytes, N, H, W, f, s, n_marks, host_mark_offsets, host_mark_events);
+}
+
+int mrisr_unet_backward(const float* params, const float* dy, const float* y, float* grads, float* dx, void* workspace,
+                        size_t workspace_bytes, int N, int H, int W, int f, int precision, void* stream) {
+    return mrisr_unet_backward_marked(params, dy, y, grads, dx, workspace, workspace_bytes, N, H, W, f, precision, stream,
+                                      0, nullptr, nullptr);
+}
+
+int64_t mrisr_unet_grads_final_from(int f, int conv_index) {
+    if (f < 16 || f % 16 || conv_index < 0 || conv_index >= kNumConv) return -1;
+    ConvDesc conv[kNumConv];
+    conv_table(f, conv);
+    return grads_final_from(ParamLayout(f), conv, conv_index);
+}
+
+void* mrisr_event_create(void) {
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return nullptr; }
+    return (void*)e;
+}
+int mrisr_event_destroy(void* event) { return event ? (int)cudaEventDestroy((cudaEvent_t)event) : 0; }
+int mrisr_stream_wait_event(void* stream, void* event) {
+    if (!event) { set_error("null event"); return MRISR_E_BADARG; }
+    return (int)cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0);
 }
 
 int mrisr_unet_debug_tensor(void* workspace, int N, int H, int W, int f, int precision, int kind, int layer, float* out,

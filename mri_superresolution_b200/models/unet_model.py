@@ -116,6 +116,8 @@ class UNetSuperRes(nn.Module):
         self._workspaces: Dict[tuple, torch.Tensor] = {}
         self._ticket = 0
         self._last_train_key = None
+        self._marks = None                 # (int64 offsets array, void* events array, n) set by parallel.GradientBuckets
+        self._marks_arena_ptr = 0
         self._initialize_weights(initial_alpha)
         self._flatten()
 
@@ -244,12 +246,40 @@ class UNetSuperRes(nn.Module):
         ws = self._workspace(n, h, w, True)
         arena = self._pick_grad_arena()
         dy32 = dy.to(torch.float32).contiguous()
-        rc = _native.lib().mrisr_unet_backward(_native.ptr(self._flat), _native.ptr(dy32), _native.ptr(y),
-                                               _native.ptr(arena), None, _native.ptr(ws), ws.numel(), n, h, w,
-                                               self.base_filters, _precision_code(self.precision),
-                                               _native.stream_ptr())
-        _native.check(rc, "mrisr_unet_backward")
+        if self._marks is not None:
+            offs, evs, nm = self._marks
+            rc = _native.lib().mrisr_unet_backward_marked(_native.ptr(self._flat), _native.ptr(dy32), _native.ptr(y),
+                                                          _native.ptr(arena), None, _native.ptr(ws), ws.numel(), n, h, w,
+                                                          self.base_filters, _precision_code(self.precision),
+                                                          _native.stream_ptr(), nm, offs, evs)
+            _native.check(rc, "mrisr_unet_backward_marked")
+            self._marks_arena_ptr = arena.data_ptr()
+        else:
+            rc = _native.lib().mrisr_unet_backward(_native.ptr(self._flat), _native.ptr(dy32), _native.ptr(y),
+                                                   _native.ptr(arena), None, _native.ptr(ws), ws.numel(), n, h, w,
+                                                   self.base_filters, _precision_code(self.precision),
+                                                   _native.stream_ptr())
+            _native.check(rc, "mrisr_unet_backward")
         return [arena[o:o + p.numel()].view(p.shape) for p, o in zip(self._param_list(), self._offs)]
+
+    # ---- gradient-readiness marks (data parallel: parallel.GradientBuckets) -------------------------
+    def set_gradient_marks(self, offsets, events) -> None:
+        """Ask every following backward pass to record ``events[k]`` (library-owned CUDA events) on the compute stream as
+        soon as all gradients at arena offset >= ``offsets[k]`` are final (include/mrisr.h, mrisr_unet_backward_marked)."""
+        if not offsets:
+            self._marks = None
+            self._marks_arena_ptr = 0
+            return
+        if len(offsets) != len(events) or len(offsets) > 32:
+            raise ValueError("gradient marks: offsets and events must have the same length (<= 32)")
+        import ctypes
+        n = len(offsets)
+        self._marks = ((ctypes.c_int64 * n)(*[int(o) for o in offsets]), (ctypes.c_void_p * n)(*events), n)
+
+    def gradient_marks_recorded(self) -> bool:
+        """True when ``.grad`` is exactly the arena the last marked backward wrote (no accumulation on top of it)."""
+        flat = self.flat_grads()
+        return self._marks is not None and flat is not None and flat.data_ptr() == self._marks_arena_ptr
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self._param_list())

@@ -234,6 +234,44 @@ def test_gradient_accumulation_matches_sum():
         assert torch.allclose(p.grad, a + b, rtol=1e-5, atol=1e-7)
 
 
+def test_gradient_marks_fire_only_when_the_bucket_is_final():
+    """mrisr_unet_backward_marked: a side stream that waits on mark k and copies grads[offset_k:] must see exactly the final
+    values (the arena still holds another batch's gradients until the kernels of this backward overwrite them)."""
+    import ctypes
+    from mri_superresolution_b200 import _native
+    from mri_superresolution_b200.parallel import SCHEDULE_CUTS, schedule_bounds
+    L = _native.lib()
+    model = _model(32, "bf16", UO.randomize_affine(UO.init_params(32)))
+    xa, _ = make_pairs(4, 64, 64, seed=1)
+    xb, _ = make_pairs(4, 64, 64, seed=2)
+    model(xa.to(_dev())).square().sum().backward()                      # fills the arena with batch A's gradients
+    total = L.mrisr_unet_param_elems(32)
+    bounds = schedule_bounds(total, [L.mrisr_unet_grads_final_from(32, l) for l in SCHEDULE_CUTS])
+    events = [L.mrisr_event_create() for _ in bounds]
+    assert all(events)
+    model.set_gradient_marks([s for s, _ in bounds], events)
+    arena_a = model.flat_grads()
+    model.zero_grad(set_to_none=True)
+    side = torch.cuda.Stream()
+    model(xb.to(_dev())).square().sum().backward()
+    assert model.gradient_marks_recorded() and model.flat_grads().data_ptr() == arena_a.data_ptr()
+    flat = model.flat_grads()
+    snaps = []
+    with torch.cuda.stream(side):
+        for (s, e), ev in zip(bounds, events):
+            assert L.mrisr_stream_wait_event(ctypes.c_void_p(side.cuda_stream), ctypes.c_void_p(ev)) == 0
+            snaps.append(flat[s:e].clone())
+    torch.cuda.synchronize()
+    for (s, e), snap in zip(bounds, snaps):
+        assert torch.equal(snap, flat[s:e])
+    # accumulation on top of .grad: the marks no longer describe .grad, the exchange must fall back to a stream wait
+    model(xa.to(_dev())).square().sum().backward()
+    assert not model.gradient_marks_recorded()
+    model.set_gradient_marks(None, None)
+    for ev in events:
+        assert L.mrisr_event_destroy(ctypes.c_void_p(ev)) == 0
+
+
 def test_cpu_tensor_raises():
     model = _model(16, "fp32")
     with pytest.raises(RuntimeError):

@@ -118,6 +118,26 @@ def test_bucket_bounds_cover_arena():
         assert b[0][1] == total                      # last slice of the arena goes first
 
 
+def test_schedule_buckets_follow_the_backward_order():
+    """Gradient-readiness marks (include/mrisr.h): the offset from which gradients are final never grows along the backward
+    schedule 19, 17, 18, 16, ..., 0, ends at 0, and the schedule-aligned buckets tile the arena back to front."""
+    from mri_superresolution_b200 import _native
+    from mri_superresolution_b200.parallel import SCHEDULE_CUTS, schedule_bounds
+    L = _native.lib()
+    for f in (16, 32):
+        total = L.mrisr_unet_param_elems(f)
+        order = [19, 17, 18] + list(range(16, -1, -1))
+        ff = [L.mrisr_unet_grads_final_from(f, l) for l in order]
+        assert all(a >= b for a, b in zip(ff, ff[1:])) and ff[-1] == 0 and 0 < ff[0] < total
+        # a block's own weight tensor is final once the block is done
+        assert L.mrisr_unet_grads_final_from(f, 9) == L.mrisr_unet_param_offset(f, 28)
+        b = schedule_bounds(total, [L.mrisr_unet_grads_final_from(f, l) for l in SCHEDULE_CUTS])
+        assert b[0][1] == total and b[-1][0] == 0 and all(x[0] == y[1] for x, y in zip(b, b[1:]))
+        assert (b[-1][1] - b[-1][0]) * 4 < 300e3 * (f / 32) ** 2      # the bucket exchanged after backward ends is small
+    assert L.mrisr_unet_grads_final_from(32, 20) == -1
+    assert schedule_bounds(10, [7, 7, 3]) == [(7, 10), (3, 7), (0, 3)]
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
