@@ -134,6 +134,12 @@ int     mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, c
 int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
                     float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                     float grad_scale, void* stream);
+/* Same update with the step number kept on the device, for CUDA-graph capture of the whole training step
+ * (scripts/train.py:296-323 as one graph launch): `state16` = 16 device bytes, int64 step count (advanced by this call)
+ * followed by two floats of scratch.  Two launches (advance + update); nothing step-dependent is baked into the launch. */
+int mrisr_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                        float lr, float beta1, float beta2, float eps, float weight_decay, void* state16,
+                        float grad_scale, void* stream);
 
 /* ---- convolution building block over padded NHWC bf16 tensors ---------------------------------
  * The implicit-GEMM kernels behind every nn.Conv2d of models/unet_model.py:29,34,72,101,152,168 (and of the VGG19

@@ -64,6 +64,8 @@ SIGNATURES = {
     "mrisr_prof_report": (c_int, [c_char_p, c_size_t]),
     "mrisr_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                                 c_float, c_float, c_int, c_float, c_void_p]),
+    "mrisr_adam_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
+                                    c_float, c_float, c_void_p, c_float, c_void_p]),
 }
 
 

@@ -20,7 +20,47 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
         v[i] = vi;
     }
 }
+// CUDA-graph form: the step number lives on the device (state[0] as int64, then step_size and 1/sqrt(bc2) as floats), so a
+// captured launch advances it on every replay instead of freezing the bias correction of the capture-time step.
+__global__ void adam_advance_kernel(long long* __restrict__ step, float* __restrict__ sc, float lr, float b1, float b2) {
+    const long long t = *step + 1;
+    *step = t;
+    const double bc1 = 1.0 - pow((double)b1, (double)t);
+    const double bc2 = 1.0 - pow((double)b2, (double)t);
+    sc[0] = (float)((double)lr / bc1);
+    sc[1] = (float)(1.0 / sqrt(bc2));
+}
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ m, float* __restrict__ v, int64_t n, float b1,
+                                                       float b2, float eps, float wd, const float* __restrict__ sc,
+                                                       float grad_scale) {
+    const float step_size = sc[0], inv_sqrt_bc2 = sc[1];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float pi = p[i];
+        const float gi = fmaf(wd, pi, g[i] * grad_scale);
+        const float mi = m[i] + (gi - m[i]) * (1.f - b1);
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+        p[i] = pi - step_size * (mi / denom);
+        m[i] = mi;
+        v[i] = vi;
+    }
+}
 }  // namespace
+
+int launch_adam_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                    float wd, void* state16, float grad_scale, cudaStream_t s) {
+    ProfScope prof_("adam", s);
+    long long* step = (long long*)state16;
+    float* sc = (float*)((char*)state16 + 8);
+    adam_advance_kernel<<<1, 1, 0, s>>>(step, sc, lr, b1, b2);
+    MRISR_LAUNCH_CHECK();
+    int blocks = (int)ceil_div64(n, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    adam_dev_kernel<<<blocks, 256, 0, s>>>(p, g, m, v, n, b1, b2, eps, wd, sc, grad_scale);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
 
 int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 float wd, int step, float grad_scale, cudaStream_t s) {

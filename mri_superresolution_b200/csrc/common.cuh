@@ -81,6 +81,13 @@ template <typename T> __device__ __forceinline__ T from_f(float v);
 template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
 template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 
+// 256-bit global store (sm_100+): the 16 bf16 channels of one accumulator chunk, 32-byte aligned
+__device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e, uint32_t f,
+                                              uint32_t g, uint32_t h) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+
 // 8-channel vector load/store (16 B for bf16, 32 B for fp32); pointers must be 8-element aligned.
 __device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
     const float4 a = *reinterpret_cast<const float4*>(p);

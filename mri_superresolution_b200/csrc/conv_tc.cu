@@ -9,9 +9,12 @@
 // (out-of-range rows are zero-filled by TMA), so the skip-concatenation is just a second tensor map over the K loop.
 // Rows that are border pixels compute garbage and are simply not stored (the zero border is an invariant).
 //
-// Warp roles (192 threads, 1 CTA/SM, persistent over tiles): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
-// warps 2..5 = epilogue (TMEM -> registers -> +bias -> bf16 -> global, GroupNorm partial sums).  Two TMEM accumulator
-// buffers let the epilogue of tile i overlap the MMAs of tile i+1.
+// Warp roles (320 threads, 1 CTA/SM, persistent over tiles): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..9 = epilogue (TMEM -> registers -> +bias -> bf16 -> global, GroupNorm partial sums).  Two TMEM accumulator
+// buffers let the epilogue of tile i overlap the MMAs of tile i+1.  Each TMEM lane quadrant is served by TWO epilogue
+// warps that take alternate 16-column chunks: with one warp per scheduler the epilogue ran at the dependent-issue latency
+// (~2.2 us per 128 x 64 tile measured on the 64-channel 512^2 layers, whatever the K depth) and set the pace of every
+// layer with few output channels.
 #include <mutex>
 #include <stdlib.h>
 #include "kernels.cuh"
@@ -114,6 +117,7 @@ struct ConvTcParams {
     int ldc;                // channels per output row (= Cout)
     int relu;               // epilogue: out = max(out, 0)                         (VGG conv + ReLU, utils/losses.py:95)
     const __nv_bfloat16* mask;   // epilogue: out = mask > 0 ? out : 0, same layout as dst (ReLU backward fused into dgrad)
+    int stages;             // WRES kernels: pipeline depth that fits beside the resident weights (<= Cfg::STAGES)
 };
 
 // MERGE3: one A tile of 128 + 2 pixel rows per (vertical tap, K chunk) serves the three horizontal taps - the operand
@@ -137,12 +141,20 @@ struct ConvTcCfg {
     static constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
 };
 
-template <int BN, int BK, bool MERGE3>
-__global__ void __launch_bounds__(192, 1)
+// WRES (MERGE3 only): all 9 * K-chunks weight tiles of the layer are fetched ONCE per CTA and stay in shared memory; a pipeline
+// stage then carries only the activation tile.  For the 64-channel layers the per-tile weight reload was 60% of the
+// L2 -> shared-memory traffic (3 x 24.6 KB of 3 x 41 KB per 128-pixel tile) and that traffic, not the MMA, set the pace
+// (VGG conv1_2 64>64@512^2: 543 TFLOP/s).  Usable while 9 * Cin * Cout * 2 B leaves room for >= 3 stages.
+constexpr int kConvTcThreads = 320;
+
+template <int BN, int BK, bool MERGE3, bool WRES = false>
+__global__ void __launch_bounds__(kConvTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+    static_assert(!WRES || MERGE3, "resident weights are implemented for the MERGE3 tile loop");
     using Cfg = ConvTcCfg<BN, BK, MERGE3>;
-    constexpr int STAGES = Cfg::STAGES;
+    constexpr int STAGES = WRES ? 8 : Cfg::STAGES;      // WRES: up to 8, the launcher passes what fits (p.stages)
+    constexpr int STAGE_BYTES = WRES ? Cfg::A_BYTES : Cfg::STAGE_BYTES;
     constexpr uint32_t LT = layout_type_for(Cfg::SWZ);
     constexpr uint32_t SBO = 8 * Cfg::SWZ;
     constexpr uint32_t IDESC = make_idesc_bf16(128, BN, 0, 0);
@@ -153,16 +165,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t tfull_bar[2];
     __shared__ __align__(8) uint64_t tempty_bar[2];
+    __shared__ __align__(8) uint64_t wfull_bar;
     __shared__ uint32_t s_tmem;
-    __shared__ float s_part[2][4][2][16];
+    __shared__ float s_part[2][8][2][16];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nstages = WRES ? p.stages : STAGES;
+    const int cpt = p.chunks1 + p.chunks2;            // K chunks per tap
+    uint8_t* const wres = smem;                       // WRES: [tap][chunk] weight tiles, then the activation stages
+    if constexpr (WRES) smem += 9 * cpt * Cfg::B_BYTES;
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmA1);
         tma_prefetch_desc(&tmA2);
         tma_prefetch_desc(&tmB);
+        mbar_init(&wfull_bar, 1);
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 256); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(&s_tmem, Cfg::TMEM_COLS);
@@ -170,7 +188,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = s_tmem;
-    const int cpt = p.chunks1 + p.chunks2;            // K chunks per tap
     const int num_kb = (MERGE3 ? 3 : p.taps) * cpt;   // pipeline stages per tile
 
     if (warp == 0) {
@@ -178,6 +195,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            if constexpr (WRES) {
+                mbar_arrive_expect_tx(&wfull_bar, (uint32_t)(9 * cpt * Cfg::B_BYTES));
+                for (int tap = 0; tap < 9; ++tap)
+                    for (int c = 0; c < cpt; ++c)
+                        tma_load_2d(wres + (tap * cpt + c) * Cfg::B_BYTES, &tmB, &wfull_bar, c * BK, tap * p.ldc);
+            }
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
                 const int m0 = (tile / p.n_blocks) * 128;
                 const int nb = tile % p.n_blocks;
@@ -186,15 +209,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                         const int row0 = m0 + (dy - 1) * p.pw - 1;             // first of the 130 rows: tap (dy, dx = -1)
                         for (int c = 0; c < cpt; ++c) {
                             mbar_wait(&empty_bar[stage], phase ^ 1);
-                            mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_TX + 3 * Cfg::B_BYTES);
-                            uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
+                            mbar_arrive_expect_tx(&full_bar[stage], WRES ? Cfg::A_TX : Cfg::A_TX + 3 * Cfg::B_BYTES);
+                            uint8_t* a_dst = smem + stage * STAGE_BYTES;
                             if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, row0);
                             else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, row0);
+                            if constexpr (!WRES) {
 #pragma unroll
-                            for (int dx = 0; dx < 3; ++dx)
-                                tma_load_2d(a_dst + Cfg::A_BYTES + dx * Cfg::B_BYTES, &tmB, &full_bar[stage], c * BK,
-                                            (dy * 3 + dx) * p.ldc + nb * BN);
-                            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                                for (int dx = 0; dx < 3; ++dx)
+                                    tma_load_2d(a_dst + Cfg::A_BYTES + dx * Cfg::B_BYTES, &tmB, &full_bar[stage], c * BK,
+                                                (dy * 3 + dx) * p.ldc + nb * BN);
+                            }
+                            if (++stage == nstages) { stage = 0; phase ^= 1; }
                         }
                     }
                 } else {
@@ -207,7 +232,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                             if (c < p.chunks1) tma_load_2d(a_dst, &tmA1, &full_bar[stage], c * BK, m0 + shift);
                             else tma_load_2d(a_dst, &tmA2, &full_bar[stage], (c - p.chunks1) * BK, m0 + shift);
                             tma_load_2d(a_dst + Cfg::A_BYTES, &tmB, &full_bar[stage], c * BK, tap * p.ldc + nb * BN);
-                            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                            if (++stage == nstages) { stage = 0; phase ^= 1; }
                         }
                     }
                 }
@@ -217,10 +242,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
         // ===== MMA issuer: warp-uniform loop, one elected lane issues; descriptor = constant hi word + (base lo + one add) =====
         constexpr uint32_t DESC_HI = ((SBO >> 4) & 0x3FFFu) | (1u << 14) | ((LT & 7u) << 29);
         const uint32_t a_lo0 = (1u << 16) | (smem_u32(smem) >> 4);                       // LBO = 16 B (unused for swizzled K-major)
-        const uint32_t b_lo0 = a_lo0 + (Cfg::A_BYTES >> 4);
+        const uint32_t b_lo0 = WRES ? (1u << 16) | (smem_u32(wres) >> 4) : a_lo0 + (Cfg::A_BYTES >> 4);
         int stage = 0;
         uint32_t phase = 0;
         int it = 0;
+        if constexpr (WRES) mbar_wait(&wfull_bar, 0);
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
             mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
@@ -230,14 +256,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after_sync();
                 if (elect_one_c()) {
-                    const uint32_t so = (uint32_t)stage * (uint32_t)(Cfg::STAGE_BYTES >> 4);
+                    const uint32_t so = (uint32_t)stage * (uint32_t)(STAGE_BYTES >> 4);
                     if constexpr (MERGE3) {
+                        // weight tile of (dy, dx, chunk): in the stage (streamed) or at [tap][chunk] of the resident block
+                        uint32_t bo = so;
+                        if constexpr (WRES) {
+                            const int dy = kb / cpt, c = kb - dy * cpt;
+                            bo = (uint32_t)((dy * 3 * cpt + c) * (Cfg::B_BYTES >> 4));
+                        }
+                        const uint32_t bdx = WRES ? (uint32_t)(cpt * (Cfg::B_BYTES >> 4)) : (uint32_t)(Cfg::B_BYTES >> 4);
 #pragma unroll
                         for (int dx = 0; dx < 3; ++dx)
 #pragma unroll
                             for (int k = 0; k < BK / 16; ++k)       // A start moves one 128-byte row per dx (base-offset field stays 0)
                                 umma_lohi2_c(d, a_lo0 + so + (uint32_t)(dx * (BK * 2 / 16) + k * 2), DESC_HI,
-                                             b_lo0 + so + (uint32_t)(dx * (Cfg::B_BYTES >> 4) + k * 2), DESC_HI, IDESC,
+                                             b_lo0 + bo + (uint32_t)dx * bdx + (uint32_t)(k * 2), DESC_HI, IDESC,
                                              (kb | dx | k) != 0 ? 1u : 0u);
                     } else {
 #pragma unroll
@@ -246,24 +279,46 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
                     }
                     umma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs have read it
                 }
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == nstages) { stage = 0; phase ^= 1; }
             }
             if (elect_one_c()) umma_commit(&tfull_bar[buf]);    // accumulator complete -> epilogue
         }
     } else {
-        // ===== epilogue: 4 warps, warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32) =====
+        // ===== epilogue: 8 warps; warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); half = which 16-column chunks =====
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         constexpr int GS = BN / 8;                           // channels per GroupNorm group
+        constexpr int NCH = BN / 32 > 0 ? BN / 32 : 1;       // 16-column chunks per warp
+        const bool do_stats = p.stat_part != nullptr;
+        const int ph = p.H + 2;
+        // (n, y, x) of this thread's row, advanced incrementally from tile to tile (one division pair per CTA, not per tile)
+        int rn, ry, rx, dn, dy_, dx_;
+        {
+            const int row0 = (blockIdx.x / p.n_blocks) * 128 + q * 32 + lane;
+            rn = row0 / p.S;
+            const int rem = row0 - rn * p.S;
+            ry = rem / p.pw; rx = rem - ry * p.pw;
+            const int step = (int)gridDim.x * 128;           // rows between this CTA's consecutive tiles (n_blocks == 1)
+            dn = step / p.S;
+            const int srem = step - dn * p.S;
+            dy_ = srem / p.pw; dx_ = srem - dy_ * p.pw;
+        }
         int it = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
-            mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
-            tc_fence_after_sync();
             const int mtile = tile / p.n_blocks, nb = tile - mtile * p.n_blocks;
             const int row = mtile * 128 + q * 32 + lane;
-            const int n = row / p.S;
-            const int rem = row - n * p.S;
-            const int y = rem / p.pw, x = rem - y * p.pw;
+            int n, y, x;
+            if (p.n_blocks == 1) {
+                n = rn; y = ry; x = rx;
+                rx += dx_; if (rx >= p.pw) { rx -= p.pw; ++ry; }
+                ry += dy_; if (ry >= ph) { ry -= ph; ++rn; }
+                rn += dn;
+            } else {
+                n = row / p.S;
+                const int rem = row - n * p.S;
+                y = rem / p.pw; x = rem - y * p.pw;
+            }
             const bool valid = row < p.total_rows && y >= 1 && y <= p.H && x >= 1 && x <= p.W;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
             __nv_bfloat16* out = p.dst + (int64_t)row * p.ldc + nb * BN;
@@ -272,39 +327,68 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             float s1[8], s2[8];
 #pragma unroll
             for (int g = 0; g < 8; ++g) s1[g] = s2[g] = 0.f;
+            mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
+            tc_fence_after_sync();
 #pragma unroll
-            for (int c0 = 0; c0 < BN; c0 += 16) {
-                float v[16];
-                tmem_ld16(taddr + c0, v);
-                if (bias) {
+            for (int j0 = 0; j0 < NCH; j0 += 2) {
+                // this warp's chunks are c0 = (2 * j + half) * 16; two TMEM loads in flight per wait
+                uint32_t raw[2][16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += __ldg(bias + c0 + i);
+                for (int jj = 0; jj < 2; ++jj) {
+                    const int c0 = (2 * (j0 + jj) + half) * 16;
+                    if (j0 + jj < NCH && c0 < BN) tmem_ld16_nowait(taddr + c0, raw[jj]);
                 }
-                if (p.relu) {
+                tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
-                }
-                if (msk && valid) {
-                    float m0[8], m1[8];
-                    load8(msk + c0, m0);
-                    load8(msk + c0 + 8, m1);
+                for (int jj = 0; jj < 2; ++jj) {
+                    const int c0 = (2 * (j0 + jj) + half) * 16;
+                    if (!(j0 + jj < NCH && c0 < BN)) continue;
+                    float v[16];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) { v[i] = m0[i] > 0.f ? v[i] : 0.f; v[8 + i] = m1[i] > 0.f ? v[8 + i] : 0.f; }
-                }
-                if (valid) {
+                    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[jj][i]);
+                    if (bias) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int g = (c0 + i) / GS;
-                        s1[g] += v[i];
-                        s2[g] = fmaf(v[i], v[i], s2[g]);
+                        for (int i = 0; i < 16; i += 4) {
+                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + c0 + i));
+                            v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+                        }
                     }
-                    uint4 o0, o1;
-                    o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
-                    o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
-                    o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
-                    o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
-                    *reinterpret_cast<uint4*>(out + c0) = o0;
-                    *reinterpret_cast<uint4*>(out + c0 + 8) = o1;
+                    if (p.relu) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+                    }
+                    if (msk && valid) {
+                        float m0[8], m1[8];
+                        load8(msk + c0, m0);
+                        load8(msk + c0 + 8, m1);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { v[i] = m0[i] > 0.f ? v[i] : 0.f; v[8 + i] = m1[i] > 0.f ? v[8 + i] : 0.f; }
+                    }
+                    if (valid) {
+                        if (do_stats) {
+                            // group of column c0 + i: (c0 + i) / GS with c0 = 32 * j + 16 * half; GS >= 2
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const int GL = (32 * (j0 + jj) + i) / GS, GH0 = (32 * (j0 + jj) + 16 + i) / GS;   // half 0 / half 1
+                                const int gl = GL < 8 ? GL : 7, gh = GH0 < 8 ? GH0 : 7;
+                                if (gl == gh) {
+                                    s1[gl] += v[i];
+                                    s2[gl] = fmaf(v[i], v[i], s2[gl]);
+                                } else if (half == 0) {
+                                    s1[gl] += v[i];
+                                    s2[gl] = fmaf(v[i], v[i], s2[gl]);
+                                } else {
+                                    s1[gh] += v[i];
+                                    s2[gh] = fmaf(v[i], v[i], s2[gh]);
+                                }
+                            }
+                        }
+                        // one 32-byte store per thread: two 16-byte stores to the same sector reach L2 as two partial-sector
+                        // writes (rows are >= 32 B apart, so nothing else merges them), which bounded the Cout <= 64 layers
+                        st_global_256(out + c0, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                      pack_bf16x2(v[6], v[7]), pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
+                                      pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+                    }
                 }
             }
             tc_fence_before_sync();
@@ -312,6 +396,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
             if (p.stat_part) {
                 const int n0 = (tile * 128) / p.S;
                 const int slot = n - n0;                     // 0 or 1 (S >= 128)
+                const int wslot = half * 4 + q;
 #pragma unroll
                 for (int sl = 0; sl < 2; ++sl) {
                     const bool mine = valid && slot == sl;
@@ -320,16 +405,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
 #pragma unroll
                         for (int g = 0; g < 8; ++g) { w[2 * g] = mine ? s1[g] : 0.f; w[2 * g + 1] = mine ? s2[g] : 0.f; }
                         warp_reduce16(w, lane);
-                        if ((lane & 1) == 0) s_part[it & 1][q][sl][lane >> 1] = w[0];
+                        if ((lane & 1) == 0) s_part[it & 1][wslot][sl][lane >> 1] = w[0];
                     } else if (lane < 16) {
-                        s_part[it & 1][q][sl][lane] = 0.f;
+                        s_part[it & 1][wslot][sl][lane] = 0.f;
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                if (q == 0) {
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (warp == 2) {
                     const int sl = lane >> 4, idx = lane & 15;
-                    const float t = (s_part[it & 1][0][sl][idx] + s_part[it & 1][1][sl][idx]) +
-                                    (s_part[it & 1][2][sl][idx] + s_part[it & 1][3][sl][idx]);
+                    float t = 0.f;
+#pragma unroll
+                    for (int w8 = 0; w8 < 8; ++w8) t += s_part[it & 1][w8][sl][idx];
                     p.stat_part[((int64_t)tile * 2 + sl) * 16 + idx] = t;
                 }
             }
@@ -383,16 +469,53 @@ __global__ void pack_weights_tc_kernel(const float* __restrict__ w, __nv_bfloat1
     }
 }
 
+constexpr int kMaxSmem = 222 * 1024;        // dynamic part; the static barriers and partial-sum scratch take 3.2 KB of the 227 KB
+
+// resident-weight variant: shared memory = weights + p.stages activation tiles
+template <int BN, int BK>
+static int launch_wres(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
+                       cudaStream_t s) {
+    using Cfg = ConvTcCfg<BN, BK, true>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+        attr_done = true;
+    }
+    const int smem = 9 * (p.chunks1 + p.chunks2) * Cfg::B_BYTES + p.stages * Cfg::A_BYTES + 1024;
+    conv_tc_kernel<BN, BK, true, true><<<grid, kConvTcThreads, smem, s>>>(tA1, tA2, tB, p);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+// pipeline depth of the resident-weight variant for this layer, 0 = does not fit / not worth it
+template <int BN, int BK>
+static int wres_stages(const ConvTcParams& p, int grid) {
+    using Cfg = ConvTcCfg<BN, BK, true>;
+    static const bool enabled = [] { const char* e = getenv("MRISR_CONV_TC_WRES"); return !(e && e[0] == '0'); }();
+    if (!enabled || p.n_blocks != 1 || p.num_tiles < 4 * grid) return 0;      // the one-off weight fetch must amortise
+    const int left = kMaxSmem - 1024 - 9 * (p.chunks1 + p.chunks2) * Cfg::B_BYTES;
+    const int st = left / Cfg::A_BYTES;
+    return st < 3 ? 0 : (st > 8 ? 8 : st);
+}
+
 template <int BN, int BK, bool MERGE3>
 static int launch_cfg(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
                       cudaStream_t s) {
     using Cfg = ConvTcCfg<BN, BK, MERGE3>;
+    if constexpr (MERGE3) {
+        const int st = wres_stages<BN, BK>(p, grid);
+        if (st > 0) {
+            ConvTcParams q = p;
+            q.stages = st;
+            return launch_wres<BN, BK>(tA1, tA2, tB, q, grid, s);
+        }
+    }
     static bool attr_done = false;
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK, MERGE3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_done = true;
     }
-    conv_tc_kernel<BN, BK, MERGE3><<<grid, 192, Cfg::SMEM_BYTES, s>>>(tA1, tA2, tB, p);
+    conv_tc_kernel<BN, BK, MERGE3><<<grid, kConvTcThreads, Cfg::SMEM_BYTES, s>>>(tA1, tA2, tB, p);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -480,7 +603,7 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     }
     tc::ConvTcParams p;
     p.dst = a.dst.p; p.bias = a.bias; p.stat_part = a.stat_part;
-    p.n_blocks = Cout / BN; p.ldc = Cout; p.relu = a.relu ? 1 : 0; p.mask = a.mask;
+    p.n_blocks = Cout / BN; p.ldc = Cout; p.relu = a.relu ? 1 : 0; p.mask = a.mask; p.stages = 0;
     p.chunks1 = C1 / bk; p.chunks2 = C2 / bk; p.taps = taps;
     p.pw = W + 2; p.S = (H + 2) * (W + 2); p.H = H; p.W = W;
     p.total_rows = (int)rows; p.num_tiles = (int)((rows + 127) / 128) * p.n_blocks;

@@ -6,8 +6,11 @@
 // utils/losses.py:98-99, so there is no weight gradient).  The network is described by a config list (channels per conv,
 // -1 = MaxPool2d(2)), so VGG16 or a shorter prefix is a config; VGG19[:36] is the parity target.
 //
-// Layout: padded NHWC bf16 with a zero border (zero padding of the NORMALISED image, as the reference pads); the three
-// input channels are padded to 16 (zero weights) so the first layer runs on the same implicit-GEMM kernel.
+// Layout: padded NHWC bf16 with a zero border (zero padding of the NORMALISED image, as the reference pads).
+// First conv (3 -> 64, K = 27): the image is packed as its own 3x3 patches, [pixel][tap * 3 + channel] padded to 32 columns
+// (out-of-image taps are the zero padding of the normalised image), so the layer is ONE K = 32 GEMM step per 128-pixel
+// tile on the 1x1 path of the implicit-GEMM kernel instead of nine K = 16 steps with 13 zero channels each
+// (3.28 -> see profiles/ ms per call at 64 x 512^2).  Its data gradient keeps the 16-channel form (3 real channels).
 // Fusions: bias + ReLU in the conv epilogue; ReLU backward (mask by the saved activation) in the dgrad epilogue;
 // max-pool backward routes to the first maximum in scan order and applies the ReLU mask in one pass.
 #include "../../include/mrisr.h"
@@ -18,7 +21,8 @@ namespace {
 using bf16 = __nv_bfloat16;
 constexpr int NTHR = 256;
 constexpr int kMaxCfg = 64;
-constexpr int kCin0 = 16;                 // padded input channels of the first conv
+constexpr int kCin0 = 16;                 // padded input channels of the first conv's data gradient
+constexpr int kK0 = 32;                   // patch columns of the first conv's forward operand: 9 taps x 3 channels, padded
 
 __constant__ float c_vgg_mean[3] = {0.485f, 0.456f, 0.406f};     // utils/losses.py:7
 __constant__ float c_vgg_std[3] = {0.229f, 0.224f, 0.225f};      // utils/losses.py:8
@@ -30,18 +34,30 @@ inline int grid_for(int64_t total) {
     return (int)b;
 }
 
-// x: N x 1 x H x W fp32 -> [N][H+2][W+2][16] bf16, channel c < 3 = (x - mean_c) / std_c    (utils/losses.py:107-114)
+// x: N x 1 x H x W fp32 -> [N][H+2][W+2][32] bf16 patches: column tap * 3 + c = (x[y + ty - 1, x + tx - 1] - mean_c) / std_c
+// inside the image, 0 outside (repeat + normalise + the conv's zero padding, utils/losses.py:107-114); columns 27..31 zero
 __global__ void __launch_bounds__(NTHR) vgg_pack_input_kernel(const float* __restrict__ x, Act<bf16> dst) {
     const int64_t total = (int64_t)dst.N * dst.H * dst.W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int xx = (int)(i % dst.W), yy = (int)((i / dst.W) % dst.H), n = (int)(i / ((int64_t)dst.W * dst.H));
-        const float v = x[i];
-        float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const float* img = x + (int64_t)n * dst.H * dst.W;
+        float o[kK0];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) o[c] = (v - c_vgg_mean[c]) / c_vgg_std[c];
-        bf16* p = dst.at(n, yy, xx, 0);
-        store8(p, o);
-        store8(p + 8, z);
+        for (int k = 27; k < kK0; ++k) o[k] = 0.f;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int sy = yy + tap / 3 - 1, sx = xx + tap % 3 - 1;
+            const bool in = sy >= 0 && sy < dst.H && sx >= 0 && sx < dst.W;
+            const float v = in ? __ldg(img + (int64_t)sy * dst.W + sx) : 0.f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o[tap * 3 + c] = in ? (v - c_vgg_mean[c]) / c_vgg_std[c] : 0.f;
+        }
+        bf16* p = dst.at(n, yy, xx, 0);           // 64 B per pixel as two full-sector stores
+#pragma unroll
+        for (int k = 0; k < kK0; k += 16)
+            st_global_256(p + k, pack_bf16x2(o[k], o[k + 1]), pack_bf16x2(o[k + 2], o[k + 3]), pack_bf16x2(o[k + 4], o[k + 5]),
+                          pack_bf16x2(o[k + 6], o[k + 7]), pack_bf16x2(o[k + 8], o[k + 9]), pack_bf16x2(o[k + 10], o[k + 11]),
+                          pack_bf16x2(o[k + 12], o[k + 13]), pack_bf16x2(o[k + 14], o[k + 15]));
     }
 }
 
@@ -159,14 +175,16 @@ __global__ void vgg_unpack_kernel(Act<bf16> a, float* __restrict__ out) {
     }
 }
 
-// first conv: fp32 [Cout][3][3][3] -> wf[tap][Cout][16], wd[8 - tap][16][Cout], input channels 3..15 zero
+// first conv: fp32 [Cout][3][3][3] -> wf[Cout][32] (column tap * 3 + ci, 27..31 zero: the patch operand of
+// vgg_pack_input_kernel) and the data-gradient form wd[8 - tap][16][Cout] (input channels 3..15 zero)
 __global__ void vgg_pack_first_kernel(const float* __restrict__ w, bf16* __restrict__ wf, bf16* __restrict__ wd, int Cout) {
     const int total = 9 * Cout * kCin0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int ci = i % kCin0, co = (i / kCin0) % Cout, tap = i / (kCin0 * Cout);
         const bf16 v = __float2bfloat16_rn(ci < 3 ? w[((int64_t)co * 3 + ci) * 9 + tap] : 0.f);
-        wf[((int64_t)tap * Cout + co) * kCin0 + ci] = v;
         wd[((int64_t)(8 - tap) * kCin0 + ci) * Cout + co] = v;
+        if (ci < 3) wf[(int64_t)co * kK0 + tap * 3 + ci] = v;
+        if (tap == 0 && ci < kK0 - 27) wf[(int64_t)co * kK0 + 27 + ci] = __float2bfloat16_rn(0.f);
     }
 }
 
@@ -227,8 +245,8 @@ struct VggWs {
     size_t bytes;
     VggWs(void* base, const VggNet& net, int N, int H, int W, bool grad) {
         Carve ar(base);
-        X0g = make_nhwc(ar, N, H, W, kCin0);
-        X0t = make_nhwc(ar, N, H, W, kCin0);
+        X0g = make_nhwc(ar, N, H, W, kK0);
+        X0t = make_nhwc(ar, N, H, W, kK0);
         for (int i = 0; i < net.n_conv; ++i) {
             const int h = H >> net.lvl[i], w = W >> net.lvl[i];
             Ag[i] = make_nhwc(ar, N, h, w, net.cout[i]);
@@ -253,7 +271,7 @@ static int check_args(const VggNet& net, int N, int H, int W) {
     const int div = 1 << net.n_pool;
     if (H % div || W % div) { set_error("vgg: H and W must be multiples of %d (%d poolings), got %dx%d", div, net.n_pool, H, W); return MRISR_E_SHAPE; }
     for (int i = 0; i < net.n_conv; ++i)
-        if (!conv_tc_supported(H >> net.lvl[i], W >> net.lvl[i], net.cin_padded(i), 0, net.cout[i], 3) ||
+        if (!conv_tc_supported(H >> net.lvl[i], W >> net.lvl[i], i == 0 ? kK0 : net.cin[i], 0, net.cout[i], i == 0 ? 1 : 3) ||
             !conv_tc_supported(H >> net.lvl[i], W >> net.lvl[i], net.cout[i], 0, net.cin_padded(i), 3)) {
             set_error("vgg: conv %d (%d -> %d) is not supported by the tcgen05 kernel", i, net.cin[i], net.cout[i]);
             return MRISR_E_SHAPE;
@@ -274,7 +292,8 @@ static int vgg_features(const VggNet& net, const void* packed, const float* weig
     for (int i = 0; i < net.n_conv; ++i) {
         ConvArgs<bf16> a;
         a.src1 = cur; a.src2 = none; a.w = (const bf16*)((const char*)packed + net.wf_off[i]);
-        a.bias = weights + net.b_off[i]; a.dst = A[i]; a.stat_part = nullptr; a.ks = 3; a.relu = true;
+        a.bias = weights + net.b_off[i]; a.dst = A[i]; a.stat_part = nullptr; a.relu = true;
+        a.ks = i == 0 ? 1 : 3;                       // the first layer's 3x3 window is already unrolled into its operand
         TRY(launch_conv_tc(a, s));
         cur = A[i];
         if (net.pool_after[i]) {

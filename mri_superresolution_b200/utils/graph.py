@@ -1,0 +1,69 @@
+"""The whole training step (scripts/train.py:296-323: zero_grad, forward, loss, backward, optimizer step) as ONE CUDA-graph
+launch.
+
+A step of the B200 path is ~190 kernel launches of 5-700 us each.  Run eagerly with the loss read back every step (as the
+reference's loop does, scripts/train.py:321), the host has to enqueue all of them again after every synchronisation and the
+GPU idles behind it at the start of each step.  ``GraphedTrainStep`` records the step once (torch.cuda.graph over the
+drop-in modules - every C-ABI entry point launches on the stream it is given, allocates nothing and bakes no host state
+into a launch, see include/mrisr.h) and replays it: one launch per step, inputs copied into the graph's static buffers.
+
+Requirements: ``FusedAdam(..., capturable=True)`` (device-side step count), fixed batch shape, single process
+(the data-parallel gradient exchange is not recorded).
+"""
+from __future__ import annotations
+
+import torch
+
+
+class GraphedTrainStep:
+    def __init__(self, model, criterion, optimizer, x_example: torch.Tensor, t_example: torch.Tensor, warmup: int = 2):
+        if not getattr(optimizer, "capturable", False):
+            raise ValueError("GraphedTrainStep needs FusedAdam(..., capturable=True): the step count must live on the device")
+        if not x_example.is_cuda or not t_example.is_cuda:
+            raise RuntimeError("GraphedTrainStep records CUDA work: example tensors must be CUDA tensors (no CPU fallback)")
+        self.model, self.criterion, self.optimizer = model, criterion, optimizer
+        self.x = x_example.detach().clone()
+        self.t = t_example.detach().clone()
+        self.loss = None
+        dev = self.x.device
+        # The warm-up steps (lazy one-time setup inside the library and the allocator) must not count as training:
+        # snapshot parameters and optimizer state, restore them after the capture (which itself executes nothing).
+        flat = model.flat_parameters()
+        snap = (flat.clone(), optimizer.exp_avg.clone(), optimizer.exp_avg_sq.clone(), optimizer.step_count)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        optimizer.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager()
+        with torch.no_grad():
+            flat.copy_(snap[0])
+            optimizer.exp_avg.copy_(snap[1])
+            optimizer.exp_avg_sq.copy_(snap[2])
+            optimizer.step_count = snap[3]
+            optimizer._device_state(dev)[0] = snap[3]
+        torch.cuda.synchronize(dev)
+
+    def _eager(self):
+        self.optimizer.zero_grad(set_to_none=True)
+        out = self.model(self.x)
+        loss = self.criterion(out, self.t)
+        loss.backward()
+        self.optimizer.step()
+        return loss.detach()
+
+    def __call__(self, x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+        """One training step on (x, t); returns the loss as a 0-dim device tensor that the NEXT call overwrites."""
+        if x.shape != self.x.shape or t.shape != self.t.shape:
+            raise ValueError(f"GraphedTrainStep was recorded for {tuple(self.x.shape)} / {tuple(self.t.shape)}, "
+                             f"got {tuple(x.shape)} / {tuple(t.shape)}")
+        self.x.copy_(x, non_blocking=True)
+        self.t.copy_(t, non_blocking=True)
+        self.graph.replay()
+        self.optimizer.step_count += 1
+        return self.loss
