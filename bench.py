@@ -304,18 +304,22 @@ def run_ours(args):
         return float(ms.item())
 
     # ---- resident-input timing -------------------------------------------------------------
-    # single process: the training step is replayed as one CUDA graph (utils/graph.py: the public GraphedTrainStep), so the
-    # GPU never waits for the ~190 launches of a step to be enqueued; data-parallel runs keep the eager step (the gradient
-    # exchange is not recorded).  gpu_launches counts the kernels one step launches (host counter over an eager step).
+    # the training step is replayed as one CUDA graph (utils/graph.py: the public GraphedTrainStep), so the GPU never waits
+    # for the ~190 launches of a step to be enqueued; under data parallelism the bucketed NCCL all-reduces on the side stream
+    # are part of the graph.  gpu_launches counts the kernels one step launches (host counter over an eager step).
     for _ in range(max(args.warmup - 1, 1)):
         step(x_dev, t_dev)
     l0 = _native.launch_count()
     step(x_dev, t_dev)
     launches_per_step = _native.launch_count() - l0
     graphed = None
-    if mode == "train" and world == 1 and not args.no_graph:
+    if mode == "train" and not args.no_graph:
         from mri_superresolution_b200.utils.graph import GraphedTrainStep
-        graphed = GraphedTrainStep(model, crit, opt, x_dev, t_dev)
+        graphed = GraphedTrainStep(model, crit, opt, x_dev, t_dev, buckets=buckets)
+    elif mode == "infer" and not args.no_graph:
+        from mri_superresolution_b200.utils.graph import GraphedForward
+        gfwd = GraphedForward(model, x_dev)
+        graphed = lambda x, t: gfwd(x)                                   # noqa: E731
     run_step = (lambda x, t: graphed(x, t)) if graphed is not None else step
     run_step(x_dev, t_dev)
     sampler = ClockSampler(local)
@@ -344,7 +348,7 @@ def run_ours(args):
     def e2e_step():
         batch = next(feeder)
         if graphed is not None:
-            r = graphed(batch[0], batch[1])
+            r = graphed(batch[0], batch[1] if mode == "train" else None)
         else:
             r = step(batch[0], batch[1] if mode == "train" else None)
         if mode == "train":
@@ -456,7 +460,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "slices/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h[0],
                     "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
                     "pipeline": "pinned host batch -> DevicePrefetcher (one H2D copy per step, on a side stream, double-buffered) "
-                                "-> " + ("GraphedTrainStep (whole step replayed as one CUDA graph)" if graphed is not None else "public modules (eager launches)")
+                                "-> " + (("GraphedTrainStep" if mode == "train" else "GraphedForward") + " (whole step replayed as one CUDA graph)" if graphed is not None else "public modules (eager launches)")
                                 + " -> result read back every step"},
             "gpu_launches": launches, "launch_mode": ("cuda graph replay of the eagerly counted step" if graphed is not None else "eager"),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,

@@ -7,8 +7,9 @@ GPU idles behind it at the start of each step.  ``GraphedTrainStep`` records the
 drop-in modules - every C-ABI entry point launches on the stream it is given, allocates nothing and bakes no host state
 into a launch, see include/mrisr.h) and replays it: one launch per step, inputs copied into the graph's static buffers.
 
-Requirements: ``FusedAdam(..., capturable=True)`` (device-side step count), fixed batch shape, single process
-(the data-parallel gradient exchange is not recorded).
+Requirements: ``FusedAdam(..., capturable=True)`` (device-side step count) and a fixed batch shape.  Data parallel: pass the
+``parallel.GradientBuckets`` of the run; its side-stream NCCL all-reduces are forked from / joined to the recorded stream
+by the same gradient-readiness events as in the eager step, so the overlap with backward is part of the graph.
 """
 from __future__ import annotations
 
@@ -16,12 +17,13 @@ import torch
 
 
 class GraphedTrainStep:
-    def __init__(self, model, criterion, optimizer, x_example: torch.Tensor, t_example: torch.Tensor, warmup: int = 2):
+    def __init__(self, model, criterion, optimizer, x_example: torch.Tensor, t_example: torch.Tensor, warmup: int = 2,
+                 buckets=None):
         if not getattr(optimizer, "capturable", False):
             raise ValueError("GraphedTrainStep needs FusedAdam(..., capturable=True): the step count must live on the device")
         if not x_example.is_cuda or not t_example.is_cuda:
             raise RuntimeError("GraphedTrainStep records CUDA work: example tensors must be CUDA tensors (no CPU fallback)")
-        self.model, self.criterion, self.optimizer = model, criterion, optimizer
+        self.model, self.criterion, self.optimizer, self.buckets = model, criterion, optimizer, buckets
         self.x = x_example.detach().clone()
         self.t = t_example.detach().clone()
         self.loss = None
@@ -54,7 +56,8 @@ class GraphedTrainStep:
         out = self.model(self.x)
         loss = self.criterion(out, self.t)
         loss.backward()
-        self.optimizer.step()
+        scale = self.buckets.allreduce() if self.buckets is not None else 1.0
+        self.optimizer.step(grad_scale=scale)
         return loss.detach()
 
     def __call__(self, x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
@@ -67,3 +70,37 @@ class GraphedTrainStep:
         self.graph.replay()
         self.optimizer.step_count += 1
         return self.loss
+
+
+class GraphedForward:
+    """The inference forward (scripts/infer.py:268-276: eval, no_grad, model(x), clamp(0, 1)) as one CUDA-graph launch for a
+    fixed input shape.  Returns the graph's static output tensor (overwritten by the next call)."""
+
+    def __init__(self, model, x_example: torch.Tensor, warmup: int = 2):
+        if not x_example.is_cuda:
+            raise RuntimeError("GraphedForward records CUDA work: the example tensor must be a CUDA tensor (no CPU fallback)")
+        self.model = model
+        self.x = x_example.detach().clone()
+        dev = self.x.device
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.y = self._eager()
+        torch.cuda.synchronize(dev)
+
+    def _eager(self):
+        with torch.no_grad():
+            return torch.clamp(self.model(self.x), 0, 1)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if x.shape != self.x.shape:
+            raise ValueError(f"GraphedForward was recorded for {tuple(self.x.shape)}, got {tuple(x.shape)}")
+        self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.y

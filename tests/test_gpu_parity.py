@@ -381,6 +381,19 @@ def test_graphed_train_step_matches_eager():
         GraphedTrainStep(model, crit, FusedAdam(model), batches[0][0].to(_dev()), batches[0][1].to(_dev()))
 
 
+def test_graphed_forward_matches_eager(golden_dir):
+    from mri_superresolution_b200.utils.graph import GraphedForward
+    model = _model(16, "bf16", UO.randomize_affine(UO.init_params(16, seed=5))).eval()
+    xs = [make_pairs(2, 32, 48, seed=60 + i)[0].to(_dev()) for i in range(3)]
+    g = GraphedForward(model, xs[0])
+    for x in xs:
+        with torch.no_grad():
+            ref = torch.clamp(model(x), 0, 1)
+        assert torch.equal(g(x), ref)
+    with pytest.raises(ValueError):
+        g(xs[0][:1])
+
+
 def test_full_size_forward_properties():
     """Config-2 shape (256^2 input) at a small batch: output range/shape and batch-independence
     (GroupNorm is per-sample, so sample i of a batch equals the same sample run alone)."""
