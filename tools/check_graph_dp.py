@@ -23,6 +23,8 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
+    say = lambda m: print(f"[check_graph_dp rank {rank}] {m}", flush=True)      # noqa: E731
+    say("process group up")
     batches = [tuple(t.to(dev) for t in make_pairs(4, 64, 64, seed=100 + i, rank=rank)) for i in range(3)]
     results = []
     for use_graph in (False, True):
@@ -34,6 +36,7 @@ def main():
         losses = []
         if use_graph:
             stepper = GraphedTrainStep(model, crit, opt, batches[0][0], batches[0][1], buckets=buckets)
+            say("graph recorded")
         for x, t in batches:
             if use_graph:
                 losses.append(float(stepper(x, t).item()))
@@ -44,6 +47,7 @@ def main():
                 opt.step(grad_scale=buckets.allreduce())
                 losses.append(float(loss.item()))
         results.append((losses, model.flat_parameters().clone()))
+        say(f"{'graph' if use_graph else 'eager'} leg done: {losses}")
         buckets.close()
     (l0, p0), (l1, p1) = results
     err = float((p0 - p1).abs().max() / p0.abs().max())
