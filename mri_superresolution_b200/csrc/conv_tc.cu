@@ -493,6 +493,9 @@ static int wres_stages(const ConvTcParams& p, int grid) {
     using Cfg = ConvTcCfg<BN, BK, true>;
     static const bool enabled = [] { const char* e = getenv("MRISR_CONV_TC_WRES"); return !(e && e[0] == '0'); }();
     if (!enabled || p.n_blocks != 1 || p.num_tiles < 4 * grid) return 0;      // the one-off weight fetch must amortise
+    // measured (profiles/r01_conv_tc_epilogue.md): a gain where the weight tiles dominate a stage (Cout = 128: 3 x 16 KB beside
+    // a 17 KB activation tile; 32-channel chunks), a loss for Cout <= 64 with 64-channel chunks (64>64, 128>64, 64>32)
+    if (!(BN >= 128 || BK == 32)) return 0;
     const int left = kMaxSmem - 1024 - 9 * (p.chunks1 + p.chunks2) * Cfg::B_BYTES;
     const int st = left / Cfg::A_BYTES;
     return st < 3 ? 0 : (st > 8 ? 8 : st);

@@ -127,11 +127,12 @@ SHAPES = [
     (5, 16, 16, 64, 0, 128, 3, False),      # ... odd slab count in the last group
     (2, 24, 24, 32, 32, 64, 3, False),      # ... 32-channel slabs (64-byte swizzle), six slabs = one full + one half M tile
     (2, 20, 36, 32, 0, 128, 3, False),      # ... 32-channel slabs, Cout = 128: one tile of three slabs
-    # >= 4 tiles per SM: conv_tc keeps the layer's weights resident in shared memory (WRES)
-    (6, 128, 96, 64, 0, 64, 3, True),       # 72 KB of weights, 8 activation stages
-    (5, 126, 126, 64, 64, 64, 3, False),    # concat, two K chunks per tap: 144 KB of weights, 4 stages
-    (6, 128, 96, 64, 0, 128, 3, False),     # N = 128
-    (6, 128, 96, 32, 0, 64, 3, False),      # 32-channel chunks (64-byte swizzle)
+    # >= 4 tiles per SM: many tiles per CTA (incremental pixel coordinates across tiles), and conv_tc keeps the layer's
+    # weights resident in shared memory (WRES) where Cout = 128 or the K chunks are 32 channels wide
+    (6, 128, 96, 64, 0, 64, 3, True),       # streamed weights, 5 tiles per CTA, bias
+    (5, 126, 126, 32, 32, 64, 3, False),    # WRES, concat: two K chunks per tap from two tensor maps
+    (6, 128, 96, 64, 0, 128, 3, False),     # WRES, N = 128: 144 KB of weights, 4 activation stages
+    (6, 128, 96, 32, 0, 64, 3, False),      # WRES, 32-channel chunks (64-byte swizzle), 8 stages
 ]
 
 
