@@ -134,11 +134,13 @@ int     mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, c
 int mrisr_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
                     float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                     float grad_scale, void* stream);
-/* Same update with the step number kept on the device, for CUDA-graph capture of the whole training step
- * (scripts/train.py:296-323 as one graph launch): `state16` = 16 device bytes, int64 step count (advanced by this call)
- * followed by two floats of scratch.  Two launches (advance + update); nothing step-dependent is baked into the launch. */
+/* Same update with the step number AND the learning rate kept on the device, for CUDA-graph capture of the whole training
+ * step (scripts/train.py:296-323 as one graph launch, with ReduceLROnPlateau of :189,397 still taking effect):
+ * `state32` = 32 device bytes: int64 step count (advanced by this call), two floats of scratch, float lr (written by the
+ * host whenever the scheduler changes it), 12 bytes reserved.  Two launches (advance + update); nothing step- or
+ * lr-dependent is baked into the launch arguments. */
 int mrisr_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
-                        float lr, float beta1, float beta2, float eps, float weight_decay, void* state16,
+                        float beta1, float beta2, float eps, float weight_decay, void* state32,
                         float grad_scale, void* stream);
 
 /* ---- convolution building block over padded NHWC bf16 tensors ---------------------------------

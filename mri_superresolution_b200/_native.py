@@ -65,7 +65,7 @@ SIGNATURES = {
     "mrisr_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                                 c_float, c_float, c_int, c_float, c_void_p]),
     "mrisr_adam_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
-                                    c_float, c_float, c_void_p, c_float, c_void_p]),
+                                    c_float, c_void_p, c_float, c_void_p]),
 }
 
 

@@ -20,11 +20,13 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
         v[i] = vi;
     }
 }
-// CUDA-graph form: the step number lives on the device (state[0] as int64, then step_size and 1/sqrt(bc2) as floats), so a
-// captured launch advances it on every replay instead of freezing the bias correction of the capture-time step.
-__global__ void adam_advance_kernel(long long* __restrict__ step, float* __restrict__ sc, float lr, float b1, float b2) {
+// CUDA-graph form: the step number and the learning rate live on the device (state: int64 step, float step_size,
+// float 1/sqrt(bc2), float lr), so a captured launch advances the step on every replay and follows the scheduler's lr instead
+// of freezing the capture-time values.
+__global__ void adam_advance_kernel(long long* __restrict__ step, float* __restrict__ sc, float b1, float b2) {
     const long long t = *step + 1;
     *step = t;
+    const float lr = sc[2];
     const double bc1 = 1.0 - pow((double)b1, (double)t);
     const double bc2 = 1.0 - pow((double)b2, (double)t);
     sc[0] = (float)((double)lr / bc1);
@@ -48,12 +50,12 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
 }
 }  // namespace
 
-int launch_adam_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
-                    float wd, void* state16, float grad_scale, cudaStream_t s) {
+int launch_adam_dev(float* p, const float* g, float* m, float* v, int64_t n, float b1, float b2, float eps, float wd,
+                    void* state32, float grad_scale, cudaStream_t s) {
     ProfScope prof_("adam", s);
-    long long* step = (long long*)state16;
-    float* sc = (float*)((char*)state16 + 8);
-    adam_advance_kernel<<<1, 1, 0, s>>>(step, sc, lr, b1, b2);
+    long long* step = (long long*)state32;
+    float* sc = (float*)((char*)state32 + 8);
+    adam_advance_kernel<<<1, 1, 0, s>>>(step, sc, b1, b2);
     MRISR_LAUNCH_CHECK();
     int blocks = (int)ceil_div64(n, 256);
     if (blocks > 148 * 8) blocks = 148 * 8;

@@ -152,7 +152,7 @@ int launch_ssim_forward(const float* a, const float* b, float* per_sample, void*
                         int win, float sigma, float val_range, cudaStream_t s);
 int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 float wd, int step, float grad_scale, cudaStream_t s);
-int launch_adam_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
-                    float wd, void* state16, float grad_scale, cudaStream_t s);
+int launch_adam_dev(float* p, const float* g, float* m, float* v, int64_t n, float b1, float b2, float eps, float wd,
+                    void* state32, float grad_scale, cudaStream_t s);
 
 }  // namespace mrisr

@@ -419,10 +419,10 @@ int mrisr_adam_step(float* p, const float* g, float* m, float* v, int64_t n, flo
     return launch_adam(p, g, m, v, n, lr, b1, b2, eps, wd, step, grad_scale, (cudaStream_t)stream);
 }
 
-int mrisr_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
-                        float wd, void* state16, float grad_scale, void* stream) {
-    if (!p || !g || !m || !v || !state16 || n <= 0) { set_error("bad argument"); return MRISR_E_BADARG; }
-    return launch_adam_dev(p, g, m, v, n, lr, b1, b2, eps, wd, state16, grad_scale, (cudaStream_t)stream);
+int mrisr_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, float b1, float b2, float eps, float wd,
+                        void* state32, float grad_scale, void* stream) {
+    if (!p || !g || !m || !v || !state32 || n <= 0) { set_error("bad argument"); return MRISR_E_BADARG; }
+    return launch_adam_dev(p, g, m, v, n, b1, b2, eps, wd, state32, grad_scale, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -18,7 +18,10 @@ import torch
 
 class GraphedTrainStep:
     def __init__(self, model, criterion, optimizer, x_example: torch.Tensor, t_example: torch.Tensor, warmup: int = 2,
-                 buckets=None):
+                 buckets=None, record_metric: bool = False):
+        """``record_metric``: also keep ``loss_and_metric`` = device tensor [loss, mean SSIM of (output, target)] of the last
+        step, the SSIM being the (unclamped) value the loss kernel computed (``criterion.last_components[1]``) - the
+        reference runs a second SSIM forward for it every step (scripts/train.py:322-323)."""
         if not getattr(optimizer, "capturable", False):
             raise ValueError("GraphedTrainStep needs FusedAdam(..., capturable=True): the step count must live on the device")
         if not x_example.is_cuda or not t_example.is_cuda:
@@ -27,10 +30,13 @@ class GraphedTrainStep:
         self.x = x_example.detach().clone()
         self.t = t_example.detach().clone()
         self.loss = None
+        self.loss_and_metric = None
+        self._record_metric = bool(record_metric)
         dev = self.x.device
         # The warm-up steps (lazy one-time setup inside the library and the allocator) must not count as training:
         # snapshot parameters and optimizer state, restore them after the capture (which itself executes nothing).
         flat = model.flat_parameters()
+        optimizer.step_count = int(optimizer.step_count)
         snap = (flat.clone(), optimizer.exp_avg.clone(), optimizer.exp_avg_sq.clone(), optimizer.step_count)
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -58,6 +64,10 @@ class GraphedTrainStep:
         loss.backward()
         scale = self.buckets.allreduce() if self.buckets is not None else 1.0
         self.optimizer.step(grad_scale=scale)
+        if self._record_metric:
+            comp = getattr(self.criterion, "last_components", None)
+            ssim = comp[1] if comp is not None else torch.zeros((), device=loss.device)
+            self.loss_and_metric = torch.stack([loss.detach(), ssim])
         return loss.detach()
 
     def __call__(self, x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
@@ -67,6 +77,7 @@ class GraphedTrainStep:
                              f"got {tuple(x.shape)} / {tuple(t.shape)}")
         self.x.copy_(x, non_blocking=True)
         self.t.copy_(t, non_blocking=True)
+        self.optimizer.sync_lr()                     # a scheduler may have changed param_groups[0]['lr'] since the last step
         self.graph.replay()
         self.optimizer.step_count += 1
         return self.loss

@@ -509,3 +509,66 @@ def test_device_prefetcher_order_and_reuse():
     assert seen == [(float(i), float(-i)) for i in range(7)]
     with pytest.raises(ValueError):
         DevicePrefetcher(host, dev, slots=1)
+
+
+# ------------------------------------------------------------------ drivers
+def test_train_driver_two_epochs_match_the_oracle_loop(tmp_path, capsys):
+    """drivers.train (graph replay, device-side running sums, prefetched CPU batches) against the reference loop restated over
+    the oracle (oracle/train_oracle.py = scripts/train.py:296-323) on the same batches: per-epoch train loss / SSIM, the
+    validation numbers, the JSON-lines schema and the checkpoint files."""
+    import json
+    from mri_superresolution_b200.drivers import TrainConfig, find_best_checkpoint, load_model, train
+    f = 16
+    params = UO.randomize_affine(UO.init_params(f, seed=21))
+    tr = [make_pairs(2, 32, 32, seed=300 + i) for i in range(3)]
+    va = [make_pairs(2, 32, 32, seed=400 + i) for i in range(2)]
+    cfg = TrainConfig(epochs=2, learning_rate=2e-4, weight_decay=1e-5, ssim_weight=0.4, base_filters=f, patience=5,
+                      checkpoint_dir=str(tmp_path), precision="fp32", batch_size=2)
+    res = train(cfg, lambda: tr, lambda: va, device=_dev(), model=_model(f, "fp32", params))
+    oracle = OracleTrainer(params, lr=2e-4, weight_decay=1e-5, ssim_weight=0.4)
+    for ep in range(2):
+        ls, ss = zip(*[oracle.step(x, t) for x, t in tr])
+        with torch.no_grad():
+            vl = [float(LO.combined_loss(UO.unet_forward(oracle.params, x), t, ssim_weight=0.4)) for x, t in va]
+            vs = [float(LO.ssim(UO.unet_forward(oracle.params, x), t)) for x, t in va]
+        h = res["history"][ep]
+        # fp32 mode; Adam's m / sqrt(v) amplifies last-bit gradient differences where a gradient is near zero, hence 1e-3
+        assert abs(h["train_loss"] - sum(ls) / 3) < 1e-3 * (sum(ls) / 3), (ep, h, ls)
+        assert abs(h["train_ssim"] - sum(ss) / 3) < 1e-3, (ep, h, ss)
+        assert abs(h["val_loss"] - sum(vl) / 2) < 1e-3 * (sum(vl) / 2), (ep, h, vl)
+        assert abs(h["val_ssim"] - sum(vs) / 2) < 1e-3, (ep, h, vs)
+    lines = [json.loads(l) for l in capsys.readouterr().out.strip().splitlines() if l.startswith("{")]
+    kinds = [l["type"] for l in lines]
+    assert kinds[0] == "params" and kinds.count("epoch_summary") == 2 and "batch_update" in kinds
+    summ = [l for l in lines if l["type"] == "epoch_summary"][0]
+    assert set(summ) == {"type", "epoch", "total_epochs", "train_loss", "val_loss", "train_ssim", "val_ssim", "elapsed", "lr"}
+    best = torch.load(res["best_path"], map_location="cpu", weights_only=False)
+    final = torch.load(res["final_path"], map_location="cpu", weights_only=False)
+    assert set(best) == {"epoch", "model_state_dict", "optimizer_state_dict", "scheduler_state_dict", "val_loss", "val_ssim"}
+    assert set(final) == {"epoch", "model_state_dict", "optimizer_state_dict", "val_loss", "val_ssim"}
+    assert list(final["model_state_dict"].keys()) == list(params.keys())
+    torch.optim.Adam([torch.nn.Parameter(v.clone()) for v in final["model_state_dict"].values()]).load_state_dict(
+        final["optimizer_state_dict"])                                     # stock Adam layout
+    assert find_best_checkpoint(str(tmp_path), "unet") == res["best_path"]
+    m = load_model("unet", res["final_path"], _dev(), base_filters=f, precision="fp32")
+    assert not m.training
+    for k, v in oracle.params.items():
+        assert rel_inf(m.state_dict()[k], v) < 5e-3, k                     # six sign-like Adam updates of 2e-4 each
+
+
+def test_super_resolve_shards_a_slice_stack_without_exchange():
+    """BASELINE.json config 5 in miniature: ranks take contiguous slice blocks; the blocks concatenate to the single-process
+    result, which equals the per-slice reference loop (scripts/infer.py:268-276) restated over the oracle."""
+    from mri_superresolution_b200.drivers import super_resolve
+    params = UO.randomize_affine(UO.init_params(16, seed=9))
+    model = _model(16, "fp32", params).eval()
+    vol, _ = make_pairs(10, 40, 40, seed=77)                               # 10 slices of a 40 x 40 volume (40 = 8 * 5)
+    whole = super_resolve(model, vol, batch=3)
+    parts = [super_resolve(model, vol, batch=2, rank=r, world=4, use_graph=(r % 2 == 0)) for r in range(4)]
+    assert [p.shape[0] for p in parts] == [2, 3, 2, 3]
+    assert rel_inf(torch.cat(parts), whole) < 1e-5                         # batch position only moves summation order
+    from oracle.train_oracle import infer_step
+    ref = infer_step(params, vol)
+    assert rel_inf(whole, ref) < 1e-4
+    with pytest.raises(ValueError):
+        super_resolve(model, vol[:, 0])

@@ -217,3 +217,63 @@ def test_device_prefetcher_rejects_cpu_device():
     from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
     with pytest.raises(RuntimeError):
         DevicePrefetcher([], "cpu")
+
+
+# ------------------------------------------------------------------ drivers and optimizer state layout
+def test_log_message_schema_matches_reference(capsys):
+    """scripts/train.py:54-68: dict messages get floats rounded to 6 places and a 'type' key; anything else is a string message."""
+    import json
+    from mri_superresolution_b200.drivers import log_message
+    log_message({"epoch": 3, "train_loss": 0.123456789, "val_loss": "N/A"}, "epoch_summary")
+    log_message(RuntimeError("boom"))
+    lines = [json.loads(l) for l in capsys.readouterr().out.strip().splitlines()]
+    assert lines[0] == {"epoch": 3, "train_loss": 0.123457, "val_loss": "N/A", "type": "epoch_summary"}
+    assert lines[1] == {"type": "info", "message": "boom"}
+
+
+def test_find_best_checkpoint_order_and_errors(tmp_path):
+    """scripts/infer.py:74-95: best_ before final_ before any *.pth naming the model type; FileNotFoundError otherwise."""
+    from mri_superresolution_b200.drivers import TrainConfig, find_best_checkpoint
+    with pytest.raises(FileNotFoundError):
+        find_best_checkpoint(str(tmp_path), "unet")
+    (tmp_path / "epoch3_unet.pth").write_bytes(b"x")
+    assert find_best_checkpoint(str(tmp_path), "unet").endswith("epoch3_unet.pth")
+    (tmp_path / "final_model_unet.pth").write_bytes(b"x")
+    assert find_best_checkpoint(str(tmp_path), "unet").endswith("final_model_unet.pth")
+    (tmp_path / "best_model_unet.pth").write_bytes(b"x")
+    assert find_best_checkpoint(str(tmp_path), "unet").endswith("best_model_unet.pth")
+    with pytest.raises(ValueError):
+        TrainConfig(model_type="resnet")                                   # scripts/train.py:175
+
+
+def test_fused_adam_state_dict_is_stock_adam_layout():
+    """optimizer_state_dict of a checkpoint (scripts/train.py:411-418) is torch.optim.Adam's: it must load into FusedAdam and
+    FusedAdam's must load into torch.optim.Adam over the same parameters, values preserved."""
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    from mri_superresolution_b200.optim import FusedAdam
+    torch.manual_seed(0)
+    model = UNetSuperRes(base_filters=16)
+    ref_params = [torch.nn.Parameter(p.detach().clone()) for p in model.parameters()]
+    ref = torch.optim.Adam(ref_params, lr=3e-4, weight_decay=1e-5)
+    for p in ref_params:
+        p.grad = torch.randn_like(p)
+    ref.step()
+    ref.step()
+    sd = ref.state_dict()
+    opt = FusedAdam(model, lr=1e-4)
+    assert opt.state_dict()["state"] == {}                                 # torch: empty before the first step
+    opt.load_state_dict(sd)
+    assert opt.step_count == 2 and opt.lr == 3e-4 and opt.weight_decay == 1e-5
+    back = opt.state_dict()
+    assert sorted(back["state"].keys()) == sorted(sd["state"].keys())
+    for i, st in sd["state"].items():
+        assert torch.equal(back["state"][i]["exp_avg"], st["exp_avg"]) and torch.equal(back["state"][i]["exp_avg_sq"], st["exp_avg_sq"])
+        assert float(back["state"][i]["step"]) == float(st["step"])
+    assert back["param_groups"][0]["params"] == sd["param_groups"][0]["params"]
+    fresh = torch.optim.Adam([torch.nn.Parameter(p.detach().clone()) for p in model.parameters()], lr=1.0)
+    fresh.load_state_dict(back)                                            # stock Adam accepts ours
+    assert fresh.param_groups[0]["lr"] == 3e-4
+    sched = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode="min", factor=0.5, patience=0)      # scripts/train.py:189
+    sched.step(1.0)
+    sched.step(2.0)
+    assert opt.lr == 1.5e-4
