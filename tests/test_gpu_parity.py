@@ -572,3 +572,26 @@ def test_super_resolve_shards_a_slice_stack_without_exchange():
     assert rel_inf(whole, ref) < 1e-4
     with pytest.raises(ValueError):
         super_resolve(model, vol[:, 0])
+
+
+@pytest.mark.parametrize("hw", [(320, 320), (512, 512)])
+def test_config4_config5_input_sizes_forward_parity(hw):
+    """BASELINE.json configs 4 (512 x 512 slices) and 5 (320 x 320 volume slices; 320 = 8 * 40 is not a multiple of the
+    128-pixel MMA tile or the 256-pixel ring block) at base_filters = 32, one slice: the inference forward against the
+    oracle run on the host in fp32.  fp32 mode within 1e-4; bf16 mode within the north_star tolerances (loss 1e-2 relative,
+    SSIM 1e-3, PSNR 0.05 dB) and at the bf16 rounding floor in relative L2."""
+    h, w = hw
+    params = UO.init_params(32, seed=1234)
+    x, tgt = make_pairs(1, h, w, seed=5)
+    with torch.no_grad():
+        ref = UO.unet_forward(params, x)
+        y32 = _model(32, "fp32", params).eval()(x.to(_dev())).cpu()
+        y16 = _model(32, "bf16", params).eval()(x.to(_dev())).cpu()
+    assert y16.shape == (1, 1, 2 * h, 2 * w)
+    assert rel_inf(y32, ref) < 1e-4
+    lref = float(LO.combined_loss(ref, tgt, ssim_weight=0.4))
+    l16 = float(LO.combined_loss(y16, tgt, ssim_weight=0.4))
+    assert abs(l16 - lref) < 1e-2 * lref
+    assert abs(float(LO.ssim(y16, tgt)) - float(LO.ssim(ref, tgt))) < 1e-3
+    assert abs(LO.psnr(y16, tgt) - LO.psnr(ref, tgt)) < 0.05
+    assert float((y16 - ref).norm() / ref.norm()) < 5e-2
