@@ -225,7 +225,9 @@ def run_reference(args):
 
 def workload_config(mode: str, world: int, per_gpu_batch: int, perceptual: float = 0.0):
     loss = "L1+SSIM(0.4)" if perceptual <= 0 else f"L1+SSIM(0.4)+VGG19 perceptual({perceptual})"
-    return {"workload": (f"BASELINE.json configs[{1 if perceptual <= 0 else 2}]: U-Net(base_filters={BASE_FILTERS}) "
+    cfg_id = (1 if perceptual <= 0 else 2) if mode == "train" else {512: 3, 320: 4}.get(H, 1)
+    note = "" if mode == "train" or H == 256 else (" (one chunk of the batch-256 job)" if H == 512 else " (one rank's share of the 256-slice volume)")
+    return {"workload": (f"BASELINE.json configs[{cfg_id}]{note}: U-Net(base_filters={BASE_FILTERS}) "
                          f"{'training step, ' + loss + ' loss, Adam' if mode == 'train' else 'inference forward'}, "
                          f"batch {per_gpu_batch}/GPU, {H}x{W} input -> {2 * H}x{2 * W} output"),
             "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * world, "input": [H, W],
@@ -484,8 +486,13 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="end-to-end leg with eager launches instead of the CUDA graph")
     ap.add_argument("--perceptual", type=float, default=0.0,
                     help="weight of the VGG19[:36] perceptual term (BASELINE.json configs[2] uses 0.1); 0 = configs[1]")
+    ap.add_argument("--input", type=int, default=256,
+                    help="square network input size; 256 = the headline workload, 512 / 320 = the slice sizes of BASELINE.json "
+                         "configs 4 / 5 (use with --mode infer and a --batch that is one rank's chunk)")
     ap.add_argument("--layer-report", default=None, help="write the per-kernel-tag (per layer shape) timing table here")
     args = ap.parse_args()
+    global H, W
+    H = W = args.input
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)

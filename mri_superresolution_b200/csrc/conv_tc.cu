@@ -347,10 +347,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[jj][i]);
                     if (bias) {
+                        // the bias is a slice of the flat parameter arena: 16-byte aligned for the VGG stack, at an odd
+                        // element offset in the U-Net arena (alpha comes first) -> vector loads only when aligned
+                        if ((reinterpret_cast<uintptr_t>(bias) & 15) == 0) {
 #pragma unroll
-                        for (int i = 0; i < 16; i += 4) {
-                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + c0 + i));
-                            v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+                            for (int i = 0; i < 16; i += 4) {
+                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + c0 + i));
+                                v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] += __ldg(bias + c0 + i);
                         }
                     }
                     if (p.relu) {

@@ -54,7 +54,7 @@ template <typename T>
 Act<T> Workspace<T>::make_act(Arena& ar, int lvl, int C) {
     Act<T> a;
     a.N = N; a.H = lvl_dim(H, lvl); a.W = lvl_dim(W, lvl); a.C = C;
-    if (planar_level(lvl) && sizeof(T) == 2 && C >= 16 && C % 8 == 0) {
+    if (level_is_planar(f, lvl, H, W) && sizeof(T) == 2 && C >= 16 && C % 8 == 0) {
         // planar-8: C/8 planes of [guard | N*S pixels rounded to 128 | guard] x 8 channels.  The guards are only ever READ
         // (the ring kernels fetch whole 128-pixel blocks around a tile, conv_ring.cu); what they hold is irrelevant
         // because only border outputs depend on them and those are never stored.
@@ -103,11 +103,11 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         }
         gnp_max = std::max(gnp_max, (size_t)N * gn_bwd_slots(h, w, c.cout) * 3 * (c.cout + 8));
         wg_max = std::max(wg_max, wgrad_generic_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
-        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_TC) {
+        if (sizeof(T) == 2 && layer_engine(c, l, H, W, f) == ENG_TC) {
             const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin;
             wg_max = std::max(wg_max, wgrad_tc_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c1, c.cin - c1, c.cout, c.ks));
         }
-        if (sizeof(T) == 2 && layer_engine(c, l, H, W) == ENG_RING) {
+        if (sizeof(T) == 2 && layer_engine(c, l, H, W, f) == ENG_RING) {
             wg_max = std::max(wg_max, wgrad_ring_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout, c.ks));
             wg_max = std::max(wg_max, wgrad_rows_scratch_elems(N, lvl_dim(H, c.lvl), lvl_dim(W, c.lvl), c.cin, c.cout));
         }

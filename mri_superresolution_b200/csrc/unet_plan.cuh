@@ -23,19 +23,40 @@ struct ConvDesc {
 void conv_table(int f, ConvDesc (&t)[kNumConv]);
 
 inline int lvl_dim(int d, int lvl) { return lvl < 0 ? 2 * d : d >> lvl; }
-// resolution levels whose bf16 tensors use the planar-8 layout (full resolution and the 2x head)
-inline bool planar_level(int lvl) { return lvl <= 0; }
 inline bool is_concat_conv(int l) { return l == 9 || l == 12 || l == 15; }   // DoubleConv fed by cat([skip, up])
+// Resolution levels whose bf16 tensors use the planar-8 layout: full resolution and the 2x head, AS LONG AS the sliding-window
+// kernels can hold three padded pixel rows of every 3x3 layer of that level in shared memory (conv_ring.cu: ring_plan).  At
+// 512 x 512 input (BASELINE.json config 4) the 64-channel layer at 512^2 and the 32-channel layer at 1024^2 cannot; such a
+// level falls back to NHWC + the TMA / tcgen05 kernels of conv_tc.cu as a whole (a tensor has ONE layout, and every layer of
+// the level reads or writes it) instead of dropping single layers to the CUDA-core kernels (measured: 81 of 96 ms).
+// MRISR_FORCE_NHWC=1 forces that fallback at every size (parity tests of the fallback at small sizes).
+inline bool level_is_planar(int f, int lvl, int H, int W) {
+    if (lvl > 0) return false;
+    static const bool force_nhwc = getenv("MRISR_FORCE_NHWC") != nullptr;
+    if (force_nhwc) return false;
+    ConvDesc t[kNumConv];
+    conv_table(f, t);
+    const int h = lvl_dim(H, lvl), w = lvl_dim(W, lvl);
+    for (int l = 0; l < kNumConv; ++l) {
+        const ConvDesc& c = t[l];
+        if (c.lvl != lvl || c.ks != 3 || c.cin < 16) continue;
+        const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin, c2 = c.cin - c1;
+        if (!(conv_ring_supported(h, w, c1, c2, c.cout, 3) && conv_ring_supported(h, w, c.cout, 0, c.cin, 3) &&
+              wgrad_ring_supported(h, w, c1, c2, c.cout, 3)))
+            return false;
+    }
+    return true;
+}
 // bf16 mode: does conv l (forward, data gradient and weight gradient) run on the tcgen05 kernels at input size HxW?
-// ENG_TC: NHWC + TMA + swizzled tcgen05 (conv_tc.cu / wgrad_tc.cu), levels >= 1.
+// ENG_TC: NHWC + TMA + swizzled tcgen05 (conv_tc.cu / wgrad_tc.cu), levels >= 1 (and wide levels <= 0, above).
 // ENG_RING: planar-8 sliding-window tcgen05 (conv_ring.cu / wgrad_ring.cu), the narrow layers at levels <= 0.
 enum Engine : int { ENG_GENERIC = 0, ENG_TC = 1, ENG_RING = 2 };
-inline int layer_engine(const ConvDesc& c, int l, int H, int W) {
+inline int layer_engine(const ConvDesc& c, int l, int H, int W, int f) {
     static const bool disabled = getenv("MRISR_DEBUG_NO_TC") != nullptr;   // debugging aid: all layers on CUDA cores
     if (disabled) return ENG_GENERIC;
     const int h = lvl_dim(H, c.lvl), w = lvl_dim(W, c.lvl);
     const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin, c2 = c.cin - c1;
-    if (planar_level(c.lvl)) {
+    if (level_is_planar(f, c.lvl, H, W)) {
         const bool planar_ok = c1 >= 16 && (c2 == 0 || c2 >= 16) && c.cout >= 16;     // C = 8 tensors stay NHWC
         return planar_ok && conv_ring_supported(h, w, c1, c2, c.cout, c.ks) && conv_ring_supported(h, w, c.cout, 0, c.cin, c.ks) &&
                        wgrad_ring_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_RING : ENG_GENERIC;

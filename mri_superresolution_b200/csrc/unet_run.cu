@@ -23,7 +23,7 @@ struct Runner {
     const float* params;
     cudaStream_t s;
     const float* P(int idx) const { return params + pl.off[idx]; }
-    int eng(int l) const { return sizeof(T) == 2 ? layer_engine(ws.conv[l], l, ws.H, ws.W) : (int)ENG_GENERIC; }
+    int eng(int l) const { return sizeof(T) == 2 ? layer_engine(ws.conv[l], l, ws.H, ws.W, ws.f) : (int)ENG_GENERIC; }
 
     // conv l: (src1 [, src2]) -> dst, GroupNorm partial statistics when `stats`
     int conv(int l, Act<T> src1, Act<T> src2, Act<T> dst, bool want_stats) {

@@ -44,6 +44,8 @@ KNOBS = [
     ("rows_one_cta", {"MRISR_ROWS_CTAS": "1"}, False),
     ("conv_tc_per_tap", {"MRISR_CONV_TC_MERGE3": "0"}, True),
     ("ring_one_cta", {"MRISR_RING_CTAS": "1"}, True),
+    # the wide-image fallback (unet_plan.cuh: level_is_planar): levels <= 0 in NHWC on the TMA kernels, as at 512 x 512 input
+    ("levels_nhwc", {"MRISR_FORCE_NHWC": "1"}, True),
 ]
 
 
