@@ -4,7 +4,8 @@
 // weights in registers and walks pixels; GroupNorm partial statistics come out of the same pass.  The weight gradient
 //   dW[co][tap] = sum_p X[p + shift(tap)] * dY[p][co]
 // uses the same mapping with 72 accumulators per thread and a fixed-order block / grid reduction (deterministic).
-// bf16 + planar output only; the fp32 parity mode keeps conv_generic.cu.
+// bf16 only (the fp32 parity mode keeps conv_generic.cu); the output / gradient tensor may be planar-8 or NHWC (the layout of
+// level 0 at wide images, unet_plan.cuh: level_is_planar) - RowMap gives the thread mapping of either.
 #include "kernels.cuh"
 
 namespace mrisr {
@@ -55,11 +56,12 @@ __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf1
 #pragma unroll
     for (int k = 0; k < 8; ++k) { s_red[0][tid * 8 + k] = s1[k]; s_red[1][tid * 8 + k] = s2[k]; }
     __syncthreads();
-    const int cnt = NTHR / nv;                                       // planar mapping: threads [cv*cnt, (cv+1)*cnt) share cv
+    const int cnt = NTHR / nv;                 // planar mapping: threads [cv*cnt, (cv+1)*cnt) share cv; NHWC: threads cv + j*nv
+    const bool planar = dst.planar();
     for (int i = tid; i < 2 * C; i += NTHR) {
         const int which = i / C, c = i % C, cv = c >> 3, k = c & 7;
         float t = 0.f;
-        for (int j = 0; j < cnt; ++j) t += s_red[which][(cv * cnt + j) * 8 + k];
+        for (int j = 0; j < cnt; ++j) t += s_red[which][(planar ? cv * cnt + j : cv + j * nv) * 8 + k];
         s_ch[which][c] = t;
     }
     __syncthreads();
@@ -74,6 +76,7 @@ __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf1
 // partial[(n * slots + slot)][tap][C] = block sums of X[p + shift(tap)] * dY[p][c]
 __global__ void __launch_bounds__(NTHR) wgrad_first_kernel(Act<bf16> x, Act<bf16> dy, float* __restrict__ partial, int rows_pb) {
     __shared__ float s_w[NTHR / 32][72];
+    __shared__ float s_wn[NTHR / 32][8][72];
     const int C = dy.C, nv = C / 8, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n = blockIdx.y;
     const RowMap m = row_map(dy, NTHR, tid);
     float acc[9][8];
@@ -98,24 +101,43 @@ __global__ void __launch_bounds__(NTHR) wgrad_first_kernel(Act<bf16> x, Act<bf16
             }
         }
     }
-    // a warp's lanes share the channel vector (threads per plane is a multiple of 32): butterfly, then across warps
-#pragma unroll
-    for (int t = 0; t < 9; ++t)
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float v = acc[t][k];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0) s_w[wid][t * 8 + k] = v;
-        }
-    __syncthreads();
-    const int wpc = (NTHR / 32) / nv;                                // warps per channel vector
     float* out = partial + ((int64_t)n * gridDim.x + blockIdx.x) * 9 * C;
-    for (int i = tid; i < 9 * C; i += NTHR) {
-        const int t = i / C, c = i % C, cv = c >> 3, k = c & 7;
-        float v = 0.f;
-        for (int j = 0; j < wpc; ++j) v += s_w[cv * wpc + j][t * 8 + k];
-        out[t * C + c] = v;
+    if (dy.planar()) {
+        // a warp's lanes share the channel vector (threads per plane is a multiple of 32): butterfly, then across warps
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float v = acc[t][k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) s_w[wid][t * 8 + k] = v;
+            }
+        __syncthreads();
+        const int wpc = (NTHR / 32) / nv;                            // warps per channel vector
+        for (int i = tid; i < 9 * C; i += NTHR) {
+            const int t = i / C, c = i % C, cv = c >> 3, k = c & 7;
+            float v = 0.f;
+            for (int j = 0; j < wpc; ++j) v += s_w[cv * wpc + j][t * 8 + k];
+            out[t * C + c] = v;
+        }
+    } else {
+        // NHWC mapping: lanes l, l + nv, l + 2 nv, ... of every warp share channel vector l (nv divides 32)
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float v = acc[t][k];
+                for (int o = 16; o >= nv; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane < nv) s_wn[wid][lane][t * 8 + k] = v;
+            }
+        __syncthreads();
+        for (int i = tid; i < 9 * C; i += NTHR) {
+            const int t = i / C, c = i % C, cv = c >> 3, k = c & 7;
+            float v = 0.f;
+            for (int j = 0; j < NTHR / 32; ++j) v += s_wn[j][cv][t * 8 + k];
+            out[t * C + c] = v;
+        }
     }
 }
 
@@ -141,7 +163,7 @@ __global__ void __launch_bounds__(256) wgrad_first_reduce_kernel(const float* __
 
 bool conv_first_supported(const Act<__nv_bfloat16>& src, const Act<__nv_bfloat16>& dst, int ks) {
     const int nv = dst.C / 8;
-    return ks == 3 && src.C == 1 && dst.planar() && dst.C % 8 == 0 && dst.C <= 64 && (NTHR / nv) % 32 == 0 && NTHR % nv == 0;
+    return ks == 3 && src.C == 1 && dst.C % 8 == 0 && dst.C <= 64 && (NTHR / nv) % 32 == 0 && NTHR % nv == 0 && 32 % nv == 0;
 }
 int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsFwd)); }
 size_t wgrad_first_scratch_elems(int N, int H, int W, int Cout) {
