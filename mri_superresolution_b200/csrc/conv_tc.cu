@@ -534,7 +534,9 @@ template <int BN>
 static int launch_bn(int bk, bool merge3, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p,
                      int grid, cudaStream_t s) {
     if constexpr (BN <= 128) {
-        if (merge3) return bk == 64 ? launch_cfg<BN, 64, true>(tA1, tA2, tB, p, grid, s) : launch_cfg<BN, 32, true>(tA1, tA2, tB, p, grid, s);
+        if (merge3) return bk == 64 ? launch_cfg<BN, 64, true>(tA1, tA2, tB, p, grid, s)
+                         : bk == 32 ? launch_cfg<BN, 32, true>(tA1, tA2, tB, p, grid, s)
+                                    : launch_cfg<BN, 16, true>(tA1, tA2, tB, p, grid, s);
     }
     switch (bk) {
         case 64: return launch_cfg<BN, 64, false>(tA1, tA2, tB, p, grid, s);
@@ -597,7 +599,9 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     const int BNsel = Cout > 256 ? 256 : Cout;
     // 32-channel chunks use the 64-byte swizzle: the same row-shifted descriptor start works (MRISR_CONV_TC_MERGE3_BK32=0 disables)
     static const bool bk32_ok = [] { const char* e = getenv("MRISR_CONV_TC_MERGE3_BK32"); return !(e && e[0] == '0'); }();
-    const bool merge3 = conv_tc_merge3_enabled() && taps == 9 && (bk == 64 || (bk == 32 && bk32_ok)) && BNsel <= 128;
+    // 16-channel chunks (32-byte swizzle, the NHWC fallback of the 2x head at wide images): same trick, MRISR_CONV_TC_MERGE3_BK16=0 disables
+    static const bool bk16_ok = [] { const char* e = getenv("MRISR_CONV_TC_MERGE3_BK16"); return !(e && e[0] == '0'); }();
+    const bool merge3 = conv_tc_merge3_enabled() && taps == 9 && (bk == 64 || (bk == 32 && bk32_ok) || (bk == 16 && bk16_ok)) && BNsel <= 128;
     const uint32_t a_rows = merge3 ? 130u : 128u;
     CUtensorMap tA1, tA2, tB;
     int rc = tc::make_tmap_2d_bf16(&tA1, a.src1.p, (uint64_t)rows, (uint64_t)C1, a_rows, (uint32_t)bk);
