@@ -403,7 +403,22 @@ struct FusedParams {
     int slots;         // shared-memory slots per thread (K, or K + S)
     int K;             // units per thread kept in shared memory between the phases (plus S streaming slots)
     double inv_count;
+    // ceil(2^40 / UW), used only by builds with -DMRISR_GNBWD_FASTDIV: unit index -> (row, column) by multiply-shift instead of
+    // an integer division (exact for indices < 2^24 and UW >= 8, tests/test_host_logic.py).  ncu of the kind-0 kernel:
+    // stall_not_selected 31 %, math 15 %, long scoreboard 3 %, ~417 thread instructions per 16-byte unit, i.e. issue-bound,
+    // and the two divisions per unit per pass are ~18 % of that stream (profiles/r01_gn_bwd_issue_bound.md).  Staged, not
+    // measured yet: build with `make EXTRA=-DMRISR_GNBWD_FASTDIV` to A/B it.
+    unsigned long long uw_magic;
 };
+
+__device__ __forceinline__ void unit_row_col(int pi, int UW, unsigned long long magic, int& row, int& col) {
+#ifdef MRISR_GNBWD_FASTDIV
+    row = (int)(((unsigned long long)(unsigned)pi * magic) >> 40);
+#else
+    row = pi / UW;
+#endif
+    col = pi - row * UW;
+}
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
@@ -457,7 +472,10 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     for (int k = 0; k < 8; ++k) wv[k] = KIND == SRC_OUTER ? a.wvec[cv * 8 + k] : 0.f;
 
     auto issue = [&](int i, int sidx) {                // unit i of this thread -> slot sidx
-        const int pi = p0 + i * pstep, uy = r0 + pi / UW, ux = pi % UW;
+        const int pi = p0 + i * pstep;
+        int uy, ux;
+        unit_row_col(pi, UW, fp.uw_magic, uy, ux);
+        uy += r0;
         uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
 #pragma unroll
         for (int q = 0; q < P; ++q) {
@@ -610,7 +628,10 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         cp[k] = s_p[gl];
     }
     auto apply = [&](int i, const Raw<P, POOL>& w) {
-        const int pi = p0 + i * pstep, uy = r0 + pi / UW, ux = pi % UW;
+        const int pi = p0 + i * pstep;
+        int uy, ux;
+        unit_row_col(pi, UW, fp.uw_magic, uy, ux);
+        uy += r0;
         float rv[P][8], dz[P][8], act[8], dl = 0.f;
         grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
 #pragma unroll
@@ -695,6 +716,10 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     }
     pl.depth = S;
     pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
+    pl.fp.uw_magic = ((1ull << 40) + (unsigned)UW - 1) / (unsigned)UW;
+#ifdef MRISR_GNBWD_FASTDIV
+    if (UW < 8 || (int64_t)pl.fp.rows_pc * UW >= (1 << 24)) return pl;            // outside the exact range: unfused path
+#endif
     pl.smem = (size_t)slots * RAWV * FT * 16 + red_bytes;
     pl.fp.slots = slots;
     pl.units = a.r.N * pl.fp.ups;

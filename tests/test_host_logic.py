@@ -5,6 +5,8 @@ import os
 import re
 import socket
 
+import numpy as np
+
 import pytest
 import torch
 import torch.multiprocessing as mp
@@ -277,3 +279,16 @@ def test_fused_adam_state_dict_is_stock_adam_layout():
     sched.step(1.0)
     sched.step(2.0)
     assert opt.lr == 1.5e-4
+
+
+def test_multiply_shift_row_index_is_exact():
+    """csrc/gn_bwd.cu: unit_row_col (staged -DMRISR_GNBWD_FASTDIV variant): row = (pi * ceil(2^40 / UW)) >> 40 must equal
+    pi // UW for every unit index below 2^24 and every row width the kernels see (UW >= 8)."""
+    rng = np.random.default_rng(0)
+    for uw in list(range(8, 1100)) + [2048, 4096]:
+        magic = ((1 << 40) + uw - 1) // uw
+        n = np.concatenate([np.arange(0, 4 * uw + 8, dtype=np.uint64), rng.integers(0, 1 << 24, size=2048, dtype=np.uint64),
+                            np.array([(1 << 24) - 1, uw * 4095 + uw - 1], dtype=np.uint64)])
+        assert int(n.max()) * magic < (1 << 64)
+        q = (n * np.uint64(magic)) >> np.uint64(40)
+        assert np.array_equal(q, n // np.uint64(uw)), uw
