@@ -7,6 +7,7 @@
 //   d mean(S)/d x = ( w*dmu1 + 2x (w*dE11) + y (w*dE12) ) / numel     (w* = same zero-padded filter)
 #include "kernels.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 namespace mrisr {
 namespace {
@@ -188,6 +189,196 @@ __global__ void __launch_bounds__(NTHR, 2) l1_ssim_kernel(const float* __restric
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// STAGED (MRISR_SSIM_SPLIT=1, default off, not yet measured on a B200): the same loss and gradient as l1_ssim_kernel<R, true>
+// in two kernels with halo R each instead of one kernel with halo 2R.  The fused tile recomputes the five forward maps on a
+// (T + 2R)^2 region to have the three derivative maps where the backward filters need them: ~430 FMA per output pixel
+// against 176 for the separable filters themselves.  Here the forward kernel writes the derivative maps of its OWN pixels
+// (d1, d11, d12: 12 B per pixel to scratch) and the gradient kernel filters them with halo R: ~203 FMA per pixel and
+// +24 B per pixel of HBM traffic (0.07 ms at batch 64), ~40 KB of shared memory per block instead of 149 KB.
+// Every map value is produced by the same run_filter calls in the same tap order as in the fused kernel, so the gradient is
+// expected to be bit-identical to the fused kernel's.
+constexpr int NTHR2 = 256;
+
+template <int R>
+__global__ void __launch_bounds__(NTHR2, 4) ssim_fwd_maps_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                                 float* __restrict__ dmaps, float* __restrict__ partial,
+                                                                 int H, int W, Taps taps, float C1, float C2) {
+    constexpr int IN = T + 2 * R, WIN = 2 * R + 1;
+    extern __shared__ float smem[];
+    float* sx = smem;                      // [IN][IN]
+    float* sy = sx + IN * IN;              // [IN][IN]
+    float* hb = sy + IN * IN;              // [5][IN][T]
+    __shared__ float s_red[2][NTHR2 / 32];
+    const int tid = threadIdx.x;
+    const int n = blockIdx.z, ty0 = blockIdx.y * T, tx0 = blockIdx.x * T;
+    const float* px = pred + (int64_t)n * H * W;
+    const float* py = tgt + (int64_t)n * H * W;
+    for (int i = tid; i < IN * IN; i += NTHR2) {
+        const int gy = ty0 - R + i / IN, gx = tx0 - R + i % IN;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        sx[i] = in ? px[(int64_t)gy * W + gx] : 0.f;
+        sy[i] = in ? py[(int64_t)gy * W + gx] : 0.f;
+    }
+    __syncthreads();
+    {   // horizontal pass of x, y, xx, yy, xy: task = (row, run of 8 columns)
+        constexpr int LH = 8, RUNS = T / LH;
+        for (int task = tid; task < IN * RUNS; task += NTHR2) {
+            const int r = task / RUNS, c0 = (task % RUNS) * LH;
+            float acc[LH][5];
+            run_filter<LH, 5, WIN>(taps, acc, [&](int j, float (&p)[5]) {
+                const int idx = r * IN + c0 + j;
+                const float x = sx[idx], y = sy[idx];
+                p[0] = x; p[1] = y; p[2] = x * x; p[3] = y * y; p[4] = x * y;
+            });
+#pragma unroll
+            for (int o = 0; o < LH; ++o)
+#pragma unroll
+                for (int m = 0; m < 5; ++m) hb[m * IN * T + r * T + c0 + o] = acc[o][m];
+        }
+    }
+    __syncthreads();
+    float ssum = 0.f, lsum = 0.f;
+    {   // vertical pass -> SSIM map and the three derivative maps of the tile's own pixels: task = (run of 4 rows, column)
+        constexpr int LV = 4, RUNS = T / LV;
+        const int64_t plane = (int64_t)gridDim.z * H * W;
+        for (int task = tid; task < RUNS * T; task += NTHR2) {
+            const int r0 = (task / T) * LV, c = task % T;
+            float acc[LV][5];
+            run_filter<LV, 5, WIN>(taps, acc, [&](int j, float (&p)[5]) {
+                const int idx = (r0 + j) * T + c;
+#pragma unroll
+                for (int m = 0; m < 5; ++m) p[m] = hb[m * IN * T + idx];
+            });
+#pragma unroll
+            for (int o = 0; o < LV; ++o) {
+                const int r = r0 + o, gy = ty0 + r, gx = tx0 + c;
+                if (gy >= H || gx >= W) continue;
+                const float m1 = acc[o][0], m2 = acc[o][1], e11 = acc[o][2], e22 = acc[o][3], e12 = acc[o][4];
+                const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+                const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
+                const float inv = 1.f / (B1 * B2);
+                const float S = A1 * A2 * inv;
+                ssum += S;
+                lsum += fabsf(sx[(r + R) * IN + c + R] - sy[(r + R) * IN + c + R]);
+                if (dmaps) {
+                    const int64_t i = (int64_t)n * H * W + (int64_t)gy * W + gx;
+                    dmaps[i] = 2.f * m2 * (A2 - A1) * inv - 2.f * m1 * S / B1 + 2.f * m1 * S / B2;
+                    dmaps[plane + i] = -S / B2;
+                    dmaps[2 * plane + i] = 2.f * A1 * inv;
+                }
+            }
+        }
+    }
+    ssum = warp_sum(ssum);
+    lsum = warp_sum(lsum);
+    if ((tid & 31) == 0) { s_red[0][tid >> 5] = lsum; s_red[1][tid >> 5] = ssum; }
+    __syncthreads();
+    if (tid < 2) {
+        float t = 0.f;
+        for (int w = 0; w < NTHR2 / 32; ++w) t += s_red[tid][w];
+        const int64_t b = ((int64_t)n * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        partial[b * 2 + tid] = t;
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(NTHR2, 4) ssim_grad_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                             const float* __restrict__ dmaps, float* __restrict__ dpred,
+                                                             int H, int W, Taps taps, float l1_coef, float ssim_coef) {
+    constexpr int IN = T + 2 * R, WIN = 2 * R + 1;
+    extern __shared__ float smem[];
+    float* mp = smem;                      // [3][IN][IN] derivative maps, zero outside the image
+    float* hb = mp + 3 * IN * IN;          // [3][IN][T]
+    const int tid = threadIdx.x;
+    const int n = blockIdx.z, ty0 = blockIdx.y * T, tx0 = blockIdx.x * T;
+    const int64_t plane = (int64_t)gridDim.z * H * W, base = (int64_t)n * H * W;
+    for (int i = tid; i < IN * IN; i += NTHR2) {
+        const int gy = ty0 - R + i / IN, gx = tx0 - R + i % IN;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        const int64_t g = base + (int64_t)gy * W + gx;
+        mp[i] = in ? dmaps[g] : 0.f;
+        mp[IN * IN + i] = in ? dmaps[plane + g] : 0.f;
+        mp[2 * IN * IN + i] = in ? dmaps[2 * plane + g] : 0.f;
+    }
+    __syncthreads();
+    {   // horizontal pass: task = (row, run of 8 columns)
+        constexpr int LB = 8, RUNS = T / LB;
+        for (int task = tid; task < IN * RUNS; task += NTHR2) {
+            const int r = task / RUNS, c0 = (task % RUNS) * LB;
+            float acc[LB][3];
+            run_filter<LB, 3, WIN>(taps, acc, [&](int j, float (&p)[3]) {
+                const int idx = r * IN + c0 + j;
+                p[0] = mp[idx]; p[1] = mp[IN * IN + idx]; p[2] = mp[2 * IN * IN + idx];
+            });
+#pragma unroll
+            for (int o = 0; o < LB; ++o)
+#pragma unroll
+                for (int m = 0; m < 3; ++m) hb[m * IN * T + r * T + c0 + o] = acc[o][m];
+        }
+    }
+    __syncthreads();
+    {   // vertical pass + output: task = (run of 4 rows, column)
+        constexpr int LB = 4, RUNS = T / LB;
+        for (int task = tid; task < RUNS * T; task += NTHR2) {
+            const int r0 = (task / T) * LB, c = task % T;
+            float acc[LB][3];
+            run_filter<LB, 3, WIN>(taps, acc, [&](int j, float (&p)[3]) {
+                const int idx = (r0 + j) * T + c;
+                p[0] = hb[idx]; p[1] = hb[IN * T + idx]; p[2] = hb[2 * IN * T + idx];
+            });
+#pragma unroll
+            for (int o = 0; o < LB; ++o) {
+                const int gy = ty0 + r0 + o, gx = tx0 + c;
+                if (gy < H && gx < W) {
+                    const int64_t g = base + (int64_t)gy * W + gx;
+                    const float x = pred[g], y = tgt[g];
+                    const float d = x - y;
+                    const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+                    dpred[g] = l1_coef * sg + ssim_coef * (acc[o][0] + 2.f * x * acc[o][1] + y * acc[o][2]);
+                }
+            }
+        }
+    }
+}
+
+template <int R>
+int run_split(const float* pred, const float* tgt, float* dpred, float* partial, float* dmaps, int N, int H, int W,
+              const Taps& taps, float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
+    constexpr int IN = T + 2 * R;
+    const size_t smem_f = (size_t)(2 * IN * IN + 5 * IN * T) * sizeof(float), smem_g = (size_t)(3 * IN * IN + 3 * IN * T) * sizeof(float);
+    static bool configured = false;
+    if (!configured) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(ssim_fwd_maps_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(ssim_grad_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
+        configured = true;
+    }
+    dim3 grid(ceil_div(W, T), ceil_div(H, T), N);
+    ssim_fwd_maps_kernel<R><<<grid, NTHR2, smem_f, s>>>(pred, tgt, dpred ? dmaps : nullptr, partial, H, W, taps, C1, C2);
+    MRISR_LAUNCH_CHECK();
+    if (dpred) {
+        ssim_grad_kernel<R><<<grid, NTHR2, smem_g, s>>>(pred, tgt, dmaps, dpred, H, W, taps, l1_coef, ssim_coef);
+        MRISR_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+int dispatch_split(int win, const float* pred, const float* tgt, float* dpred, float* partial, float* dmaps, int N, int H, int W,
+                   const Taps& taps, float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
+    switch (win / 2) {
+        case 1: return run_split<1>(pred, tgt, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 2: return run_split<2>(pred, tgt, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 3: return run_split<3>(pred, tgt, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        case 4: return run_split<4>(pred, tgt, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+        default: return run_split<5>(pred, tgt, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    }
+}
+
+bool ssim_split_enabled() {
+    static const bool on = [] { const char* e = getenv("MRISR_SSIM_SPLIT"); return e && e[0] == '1'; }();
+    return on;
+}
+
 // out5 = [l1, ssim, total, 0, total]; also a flag in out5-adjacent scratch is not needed: fix-up reads out5[1]
 __global__ void loss_finalize_kernel(const float* __restrict__ partial, int nblocks, double inv_numel, float l1_w,
                                      float ssim_w, float* __restrict__ out5) {
@@ -268,8 +459,12 @@ int dispatch(int win, const float* pred, const float* tgt, float* dpred, float* 
 }
 }  // namespace
 
+static size_t partial_bytes(int N, int H, int W) {
+    return (((size_t)N * ceil_div(H, T) * ceil_div(W, T) * 2 * sizeof(float)) + 255) & ~(size_t)255;
+}
 size_t l1_ssim_scratch_bytes(int N, int H, int W) {
-    return (size_t)N * ceil_div(H, T) * ceil_div(W, T) * 2 * sizeof(float);
+    // block partials, and (staged two-kernel variant only) the three derivative maps
+    return partial_bytes(N, H, W) + (ssim_split_enabled() ? (size_t)3 * N * H * W * sizeof(float) : 0);
 }
 
 int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* out5, void* scratch, int N, int H,
@@ -282,7 +477,13 @@ int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* 
     const float l1_coef = l1_w > 0.f ? (float)(l1_w / numel) : 0.f;
     const float ssim_coef = ssim_w > 0.f ? (float)(-ssim_w / numel) : 0.f;
     float* partial = (float*)scratch;
-    int rc = dispatch<true>(win, pred, target, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    int rc;
+    if (ssim_split_enabled()) {
+        float* dmaps = (float*)((char*)scratch + partial_bytes(N, H, W));
+        rc = dispatch_split(win, pred, target, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    } else {
+        rc = dispatch<true>(win, pred, target, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
+    }
     if (rc) return rc;
     const int nblocks = N * ceil_div(H, T) * ceil_div(W, T);
     loss_finalize_kernel<<<1, 32, 0, s>>>(partial, nblocks, 1.0 / numel, l1_w, ssim_w, out5);

@@ -68,3 +68,19 @@ def test_knob_variant_matches_default(tmp_path, baseline, name, env, fwd):
         tol = (0.2 if kind == "vector" else 6e-2) if fwd else 5e-3
         assert rel < tol, (name, k, rel)
     print(name, {k: (round(r, 6), n) for k, (r, n) in worst.items()})
+
+
+# Staged kernel variants: written and compiled, NOT yet measured or parity-checked on a B200 (the round's GPU budget ended first).
+# They are off in the shipped build; `MRISR_TEST_STAGED=1 python -m pytest tests/test_gpu_knobs.py -m gpu -k staged` is the first
+# thing to run on them.  MRISR_SSIM_SPLIT=1: forward-maps + gradient kernels instead of the fused halo-2R loss kernel
+# (csrc/loss.cu); every value comes from the same filter calls in the same order, so the gradients should match to the bit.
+@pytest.mark.skipif(os.environ.get("MRISR_TEST_STAGED") != "1", reason="staged variants are opt-in until measured")
+def test_staged_ssim_split_matches_default(tmp_path, baseline):
+    v = _probe(tmp_path, "ssim_split", {"MRISR_SSIM_SPLIT": "1"})
+    assert abs(float(v["loss"]) - float(baseline["loss"])) <= 1e-6 * abs(float(baseline["loss"]))
+    for k, b in baseline.items():
+        if k == "loss":
+            continue
+        a = v[k].astype(np.float64).ravel()
+        b = b.astype(np.float64).ravel()
+        assert np.linalg.norm(a - b) <= 1e-5 * max(np.linalg.norm(b), 1e-12), k
