@@ -21,9 +21,10 @@ from __future__ import annotations
 import json
 import os
 import time
-from typing import Callable, Dict, Iterable, Optional, Sequence
+from typing import Callable, Dict, Iterable, Optional
 
 import torch
+import torch.distributed as dist
 
 from .models.unet_model import UNetSuperRes
 from .optim import FusedAdam
@@ -80,7 +81,12 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
           model: Optional[UNetSuperRes] = None, log_stream=None) -> Dict:
     """Epoch loop of scripts/train.py:278-477.  ``train_batches()`` / ``val_batches()`` return a fresh iterable of
     ``(low_res N x 1 x H x W, high_res N x 1 x 2H x 2W)`` pairs per epoch (a DataLoader, a list, a generator).
-    Returns ``{'final_path', 'best_path', 'history'}``; ``history`` holds the printed epoch summaries."""
+    Returns ``{'final_path', 'best_path', 'history'}``; ``history`` holds the printed epoch summaries.
+
+    Data parallel (new; the reference is single-device): call under ``torchrun`` after ``dist.init_process_group("nccl")``;
+    every rank passes its own shard of the batches (equal counts and shapes).  Gradients are exchanged by
+    ``parallel.GradientBuckets`` inside the step, epoch sums are averaged over ranks, so all ranks take the same scheduler and
+    early-stopping decisions; rank 0 alone logs and writes checkpoints."""
     device = torch.device(device if device is not None else "cuda")
     if device.type != "cuda":
         raise RuntimeError("the B200 training path needs a CUDA device (there is no CPU fallback)")
@@ -89,6 +95,14 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
     if model is None:
         model = UNetSuperRes(1, 1, cfg.base_filters, cfg.initial_alpha, precision=cfg.precision)
     model = model.to(device)
+    world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank() if world > 1 else 0
+    buckets = None
+    if world > 1:
+        from .parallel import GradientBuckets
+        buckets = GradientBuckets(model)
+    if rank != 0:
+        log_stream = open(os.devnull, "w")                                     # one JSON-lines stream per job
     optimizer = FusedAdam(model, lr=cfg.learning_rate, weight_decay=cfg.weight_decay, capturable=cfg.use_graph)     # :186
     scheduler = torch.optim.lr_scheduler.ReduceLROnPlateau(optimizer, mode="min", factor=0.5,
                                                            patience=max(cfg.patience // 2, 0))               # :189
@@ -131,7 +145,7 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
             shape = (tuple(low_res.shape), tuple(high_res.shape))
             if cfg.use_graph and graphed is None:
                 from .utils.graph import GraphedTrainStep
-                graphed = GraphedTrainStep(model, criterion, optimizer, low_res, high_res, record_metric=True)
+                graphed = GraphedTrainStep(model, criterion, optimizer, low_res, high_res, record_metric=True, buckets=buckets)
                 graphed_shape = shape
             if cfg.use_graph and shape == graphed_shape:
                 loss = graphed(low_res, high_res)
@@ -141,7 +155,7 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
                 output = model(low_res)
                 loss = criterion(output, high_res)
                 loss.backward()
-                optimizer.step()
+                optimizer.step(grad_scale=buckets.allreduce() if buckets is not None else 1.0)
                 sums[0] += loss.detach()
                 with torch.no_grad():
                     sums[1] += metric_of(output.detach(), high_res)
@@ -149,7 +163,9 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
             if batch_idx % every == 0:                                         # :326
                 log_message({"epoch": epoch, "batch": batch_idx, "total_batches": total, "loss": float(loss.item())},
                             "batch_update", log_stream)
-        train_loss, train_ssim = (sums / max(nb, 1)).tolist()                  # one read-back per epoch
+        if world > 1:
+            dist.all_reduce(sums)                                              # equal batch counts per rank: mean of rank means
+        train_loss, train_ssim = (sums / (max(nb, 1) * world)).tolist()        # one read-back per epoch
 
         model.eval()                                                           # :351
         sums.zero_()
@@ -162,7 +178,9 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
                 nv += 1
         if nv == 0:
             raise ValueError("validation set is empty (scripts/train.py:390 divides by its length)")
-        val_loss, val_ssim = (sums / nv).tolist()
+        if world > 1:
+            dist.all_reduce(sums)
+        val_loss, val_ssim = (sums / (nv * world)).tolist()
 
         prev_lr = optimizer.param_groups[0]["lr"]
         scheduler.step(val_loss)                                               # :397
@@ -171,8 +189,9 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
             log_message(f"Learning rate adjusted from {prev_lr:.2e} to {cur_lr:.2e}", stream=log_stream)
         if val_loss < best_val_loss:                                           # :405-420
             best_val_loss, patience_counter = val_loss, 0
-            torch.save({"epoch": epoch, "model_state_dict": model.state_dict(), "optimizer_state_dict": optimizer.state_dict(),
-                        "scheduler_state_dict": scheduler.state_dict(), "val_loss": val_loss, "val_ssim": val_ssim}, best_path)
+            if rank == 0:
+                torch.save({"epoch": epoch, "model_state_dict": model.state_dict(), "optimizer_state_dict": optimizer.state_dict(),
+                            "scheduler_state_dict": scheduler.state_dict(), "val_loss": val_loss, "val_ssim": val_ssim}, best_path)
             log_message(f"Saved best model with validation loss: {val_loss:.6f}", stream=log_stream)
         else:
             patience_counter += 1
@@ -183,8 +202,11 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
             log_message(f"Early stopping triggered after {epoch + 1} epochs", stream=log_stream)
             break
 
-    torch.save({"epoch": epoch, "model_state_dict": model.state_dict(), "optimizer_state_dict": optimizer.state_dict(),
-                "val_loss": val_loss, "val_ssim": val_ssim}, final_path)           # :467-477
+    if rank == 0:
+        torch.save({"epoch": epoch, "model_state_dict": model.state_dict(), "optimizer_state_dict": optimizer.state_dict(),
+                    "val_loss": val_loss, "val_ssim": val_ssim}, final_path)       # :467-477
+    if buckets is not None:
+        buckets.close()
     log_message(f"Training completed. Final model saved to {final_path}", stream=log_stream)
     return {"final_path": final_path, "best_path": best_path if os.path.exists(best_path) else None, "history": history,
             "model": model, "optimizer": optimizer}
