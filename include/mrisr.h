@@ -76,6 +76,13 @@ int mrisr_unet_backward(const float* params, const float* dy, const float* y, fl
                         void* workspace, size_t workspace_bytes, int N, int H, int W, int base_filters,
                         int precision, void* stream);
 
+/* Diagnostic (host-only arithmetic, no device needed): which kernel family runs convolution `conv_index` (0..19, the order of
+ * models/unet_model.py:137-173 with the three up-path 1x1 convs at 8, 11, 14) in bf16 mode at input size H x W:
+ * 0 = CUDA cores, 1 = NHWC TMA / tcgen05 (conv_tc, wgrad_tc), 2 = planar-8 sliding-window tcgen05 (conv_ring, wgrad_rows).
+ * Levels <= 0 use 2 while three padded pixel rows of every 3x3 layer of the level fit in shared memory, else the whole
+ * level falls back to 1 (512 x 512 input, BASELINE.json config 4).  -1 = bad argument. */
+int mrisr_unet_layer_engine(int base_filters, int conv_index, int H, int W);
+
 /* ---- data-parallel support: gradient-readiness marks ------------------------------------------------------------
  * The reference is single-device (scripts/train.py:296-318 has no exchange step); BASELINE.json config 3 adds a bucketed
  * gradient all-reduce that overlaps the backward pass.  The backward schedule finishes the conv blocks in the order

@@ -59,6 +59,7 @@ SIGNATURES = {
                                    c_void_p, c_int, c_void_p]),
     "mrisr_vgg_perceptual_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                              c_int, c_int, c_int, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "mrisr_unet_layer_engine": (c_int, [c_int, c_int, c_int, c_int]),
     "mrisr_launch_count": (ctypes.c_longlong, []),
     "mrisr_prof_enable": (c_int, [c_int]),
     "mrisr_prof_report": (c_int, [c_char_p, c_size_t]),

@@ -377,6 +377,13 @@ int64_t mrisr_unet_grads_final_from(int f, int conv_index) {
     return grads_final_from(ParamLayout(f), conv, conv_index);
 }
 
+int mrisr_unet_layer_engine(int f, int conv_index, int H, int W) {
+    if (f < 16 || f % 16 || conv_index < 0 || conv_index >= kNumConv || H <= 0 || W <= 0 || H % 8 || W % 8) return -1;
+    ConvDesc conv[kNumConv];
+    conv_table(f, conv);
+    return layer_engine(conv[conv_index], conv_index, H, W, f);
+}
+
 void* mrisr_event_create(void) {
     cudaEvent_t e = nullptr;
     if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return nullptr; }

@@ -292,3 +292,22 @@ def test_multiply_shift_row_index_is_exact():
         assert int(n.max()) * magic < (1 << 64)
         q = (n * np.uint64(magic)) >> np.uint64(40)
         assert np.array_equal(q, n // np.uint64(uw)), uw
+
+
+def test_layer_engine_selection_by_input_size():
+    """include/mrisr.h: mrisr_unet_layer_engine (host arithmetic only).  At the headline 256^2 and at 320^2 the narrow
+    full-resolution / head layers run on the planar-8 sliding-window kernels (2) and every level >= 1 layer on the NHWC TMA
+    kernels (1); at 512^2 the 64-channel 512^2 layer and the 32-channel 1024^2 layer no longer fit the ring, and levels 0 and
+    -1 fall back to the NHWC kernels AS A WHOLE (never to the CUDA-core kernels, 0, except the 1-channel first layer, which has
+    its own kernel)."""
+    from mri_superresolution_b200 import _native
+    L = _native.lib()
+    eng = lambda hw: [L.mrisr_unet_layer_engine(32, l, hw, hw) for l in range(20)]      # noqa: E731
+    level0_and_head = [1, 15, 16, 17, 18, 19]          # inc.3, up3.conv x2, final_up_bilinear, final_up_pixelshuffle, final_conv.0
+    for hw in (256, 320):
+        e = eng(hw)
+        assert all(e[l] == 2 for l in level0_and_head), (hw, e)
+        assert all(e[l] == 1 for l in range(2, 15)), (hw, e)
+    e = eng(512)
+    assert all(v == 1 for v in e[1:]), e
+    assert L.mrisr_unet_layer_engine(32, 20, 256, 256) == -1 and L.mrisr_unet_layer_engine(32, 0, 250, 256) == -1
