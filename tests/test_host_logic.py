@@ -311,3 +311,28 @@ def test_layer_engine_selection_by_input_size():
     e = eng(512)
     assert all(v == 1 for v in e[1:]), e
     assert L.mrisr_unet_layer_engine(32, 20, 256, 256) == -1 and L.mrisr_unet_layer_engine(32, 0, 250, 256) == -1
+
+
+def test_graph_and_driver_entry_points_fail_loudly_without_cuda(tmp_path):
+    """No CPU fallback anywhere above the C ABI either: the graph helpers and the drivers refuse CPU tensors / devices, and
+    the argument checks that do not need a device fire first."""
+    from mri_superresolution_b200.drivers import TrainConfig, super_resolve, train
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    from mri_superresolution_b200.optim import FusedAdam
+    from mri_superresolution_b200.utils.graph import GraphedForward, GraphedTrainStep
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    model = UNetSuperRes(base_filters=16)
+    crit = CombinedLoss(ssim_weight=0.4)
+    x, t = torch.zeros(1, 1, 16, 16), torch.zeros(1, 1, 32, 32)
+    with pytest.raises(ValueError):
+        GraphedTrainStep(model, crit, FusedAdam(model), x, t)                       # step count must live on the device
+    with pytest.raises(RuntimeError):
+        GraphedTrainStep(model, crit, FusedAdam(model, capturable=True), x, t)      # CPU tensors
+    with pytest.raises(RuntimeError):
+        GraphedForward(model, x)
+    with pytest.raises(RuntimeError):
+        train(TrainConfig(epochs=1, checkpoint_dir=str(tmp_path)), lambda: [(x, t)], lambda: [(x, t)], device="cpu")
+    with pytest.raises(ValueError):
+        super_resolve(model, torch.zeros(4, 16, 16))
+    with pytest.raises(ValueError):
+        FusedAdam(model).step(closure=lambda: None)
