@@ -10,6 +10,7 @@
 //   dr = sc*dz + p*r + q.
 #include <stdlib.h>
 #include "kernels.cuh"
+#include "gn_bwd_trk.h"
 
 namespace mrisr {
 namespace {
@@ -409,7 +410,16 @@ struct FusedParams {
     // and the two divisions per unit per pass are ~18 % of that stream (profiles/r01_gn_bwd_issue_bound.md).  Staged, not
     // measured yet: build with `make EXTRA=-DMRISR_GNBWD_FASTDIV` to A/B it.
     unsigned long long uw_magic;
+    // Builds with -DMRISR_GNBWD_INCR: operand addresses by constant steps (gn_bwd_trk.h) instead of a division and 64-bit
+    // index arithmetic per unit (~100 of the 203 SASS instructions of the kind-0 phase-1 loop).  Staged, not measured yet.
+    TrkStep ts;
 };
+
+#ifdef MRISR_GNBWD_INCR
+constexpr bool kIncr = true;
+#else
+constexpr bool kIncr = false;
+#endif
 
 __device__ __forceinline__ void unit_row_col(int pi, int UW, unsigned long long magic, int& row, int& col) {
 #ifdef MRISR_GNBWD_FASTDIV
@@ -471,12 +481,47 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
 #pragma unroll
     for (int k = 0; k < 8; ++k) wv[k] = KIND == SRC_OUTER ? a.wvec[cv * 8 + k] : 0.f;
 
-    auto issue = [&](int i, int sidx) {                // unit i of this thread -> slot sidx
+    // incremental form (kIncr): per-thread base pointers at (first row of this CTA, column 0) and the pixel strides in elements
+    [[maybe_unused]] constexpr int PM = P == 4 ? 2 : 1;                 // pixels per unit along each axis
+    [[maybe_unused]] const int pitch = a.r.W + 2, hpitch = UW + 2, gpitch = a.g.W + 2;
+    [[maybe_unused]] const int psr = a.r.ps ? a.r.ps : a.r.C, psg = a.g.ps ? a.g.ps : a.g.C, psd = a.dr.ps ? a.dr.ps : a.dr.C;
+    [[maybe_unused]] const int psh = POOL ? (a.gpool.ps ? a.gpool.ps : a.gpool.C) : 0;
+    [[maybe_unused]] const T* rb = nullptr; [[maybe_unused]] const T* gb = nullptr; [[maybe_unused]] const T* hb = nullptr; [[maybe_unused]] T* db = nullptr;
+    if constexpr (kIncr) {
+        rb = a.r.at(n, PM * r0, 0, cv * 8);
+        db = a.dr.at(n, PM * r0, 0, cv * 8);
+        if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL) gb = a.g.at(n, PM * r0, 0, a.coff + cv * 8);
+        if (KIND == SRC_BLEND_BIL) gb = a.g.at(n, r0, 0, cv * 8);
+        if (KIND == SRC_BLEND_PS) gb = a.g.at(n, 2 * r0, 0, 2 * cv);
+        if (POOL) hb = a.gpool.at(n, r0, 0, cv * 8);
+    }
+    auto issue = [&](int i, int sidx, const UnitTrk& t) {                // unit i of this thread (at position t) -> slot sidx
+        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
+        if constexpr (kIncr) {
+#pragma unroll
+            for (int q = 0; q < P; ++q) {
+                const int po = PM * t.px + (q >> 1) * pitch + (q & 1);         // pixels from the base, r / g / dr geometry
+                cp_async16(sl + q * FT, rb + po * psr);
+                uint4* sa = sl + (P + q) * FT;
+                if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL) {
+                    cp_async16(sa, gb + po * psg);
+                } else if (KIND == SRC_BLEND_PS) {
+#pragma unroll
+                    for (int ij = 0; ij < 4; ++ij)
+                        cp_async4(reinterpret_cast<uint32_t*>(sa) + ij, gb + (2 * t.gpx + (ij >> 1) * gpitch + (ij & 1)) * psg);
+                } else if (KIND == SRC_OUTER) {
+                    const int64_t pix = ((int64_t)n * a.r.H + r0) * a.r.W + (p0 + i * pstep);
+                    cp_async4(reinterpret_cast<uint32_t*>(sa), a.y + pix);
+                    cp_async4(reinterpret_cast<uint32_t*>(sa) + 1, a.dy + pix);
+                }
+            }
+            if (POOL) cp_async16(sl + 2 * P * FT, hb + t.hpx * psh);
+            return;
+        }
         const int pi = p0 + i * pstep;
         int uy, ux;
         unit_row_col(pi, UW, fp.uw_magic, uy, ux);
         uy += r0;
-        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
 #pragma unroll
         for (int q = 0; q < P; ++q) {
             const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
@@ -511,9 +556,14 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     float s1[8], s2[8], s3[8], sdl = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
+    UnitTrk ti{0, 0, 0, 0};                            // position of the next unit to issue (kIncr)
+    if constexpr (kIncr) ti = trk_at(p0, UW, pitch, hpitch, gpitch);
 #pragma unroll
     for (int i = 0; i < S; ++i) {
-        if (i < nu) issue(i, slot_of(i));
+        if (i < nu) {
+            issue(i, slot_of(i), ti);
+            if constexpr (kIncr) trk_fwd(ti, fp.ts, UW);
+        }
         cp_async_commit();
     }
     for (int i = 0; i < nu; ++i) {
@@ -531,14 +581,21 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
             for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
             if (cvl == 0) sdl += dl;
         }
-        if (i + S < nu) issue(i + S, slot_of(i + S));          // the streaming slot just consumed (or a fresh one)
+        if (i + S < nu) {                                      // the streaming slot just consumed (or a fresh one)
+            issue(i + S, slot_of(i + S), ti);
+            if constexpr (kIncr) trk_fwd(ti, fp.ts, UW);
+        }
         cp_async_commit();
     }
     // reloads of the streamed units for the second phase, newest first: unit nu-1-t -> streaming slot t % S
     const int nstream = nu > K ? nu - K : 0;
+    UnitTrk ta = ti;                                   // every unit was issued once: ti (and ta) stand at unit nu
 #pragma unroll
     for (int t = 0; t < S; ++t) {
-        if (t < nstream) issue(nu - 1 - t, K + t);
+        if (t < nstream) {
+            if constexpr (kIncr) trk_bwd(ti, fp.ts, UW);
+            issue(nu - 1 - t, K + t, ti);
+        }
         cp_async_commit();
     }
     // lanes with equal (lane % ncv) share a channel vector: butterfly over the other lane bits, then across warps in order
@@ -627,33 +684,46 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         cq[k] = s_q[gl];
         cp[k] = s_p[gl];
     }
-    auto apply = [&](int i, const Raw<P, POOL>& w) {
-        const int pi = p0 + i * pstep;
-        int uy, ux;
-        unit_row_col(pi, UW, fp.uw_magic, uy, ux);
-        uy += r0;
+    auto apply = [&](int i, const Raw<P, POOL>& w, const UnitTrk& t) {
+        [[maybe_unused]] int uy = 0, ux = 0;
+        if constexpr (!kIncr) {
+            const int pi = p0 + i * pstep;
+            unit_row_col(pi, UW, fp.uw_magic, uy, ux);
+            uy += r0;
+        }
         float rv[P][8], dz[P][8], act[8], dl = 0.f;
         grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
 #pragma unroll
         for (int q = 0; q < P; ++q) {
-            const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
             float o[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[q][k], fmaf(cp[k], rv[q][k], cq[k]));
-            store8(a.dr.at(n, y, x, cv * 8), o);
+            if constexpr (kIncr) {
+                store8(db + (PM * t.px + (q >> 1) * pitch + (q & 1)) * psd, o);
+            } else {
+                const int y = P == 4 ? 2 * uy + (q >> 1) : uy, x = P == 4 ? 2 * ux + (q & 1) : ux;
+                store8(a.dr.at(n, y, x, cv * 8), o);
+            }
         }
     };
+    UnitTrk tc{0, 0, 0, 0};                            // cached units: ascending from the thread's first unit
+    if constexpr (kIncr) tc = trk_at(p0, UW, pitch, hpitch, gpitch);
     for (int i = 0; i < K && i < nu; ++i) {
         Raw<P, POOL> w;
         fetch(i, w);
-        apply(i, w);
+        apply(i, w, tc);
+        if constexpr (kIncr) trk_fwd(tc, fp.ts, UW);
     }
-    for (int t = 0; t < nstream; ++t) {
+    for (int t = 0; t < nstream; ++t) {                // streamed units: descending from unit nu - 1
         cp_async_wait<S - 1>();
         Raw<P, POOL> w;
         fetch(K + t % S, w);
-        apply(nu - 1 - t, w);
-        if (t + S < nstream) issue(nu - 1 - (t + S), K + t % S);
+        if constexpr (kIncr) trk_bwd(ta, fp.ts, UW);
+        apply(nu - 1 - t, w, ta);
+        if (t + S < nstream) {
+            if constexpr (kIncr) trk_bwd(ti, fp.ts, UW);
+            issue(nu - 1 - (t + S), K + t % S, ti);
+        }
         cp_async_commit();
     }
 }
@@ -692,7 +762,6 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     const size_t red_bytes = (size_t)(FT / 32) * 3 * ncv * 8 * sizeof(float);
     const size_t budget = (size_t)smem_kb * 1024 > red_bytes + 4096 ? (size_t)smem_kb * 1024 - red_bytes : 4096;
     const int kmax = (int)(budget / ((size_t)FT * RAWV * 16));
-    const int64_t items = (int64_t)UH * UW * ncv;                     // (unit, channel vector) pairs of one unit
     int cs = cs_env ? cs_env : 2;
     while (cs > UH && cs > 1) cs >>= 1;
     if (cs != 1 && cs != 2 && cs != 4 && cs != 8 && cs != 16) return pl;
@@ -717,6 +786,20 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     pl.depth = S;
     pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
     pl.fp.uw_magic = ((1ull << 40) + (unsigned)UW - 1) / (unsigned)UW;
+    pl.fp.ts = trk_steps(FT / ncv, UW, a.r.W + 2, a.g.W + 2);
+#ifdef MRISR_GNBWD_INCR
+    {
+        // 32-bit element offsets inside a sample, and the operand geometries the incremental form assumes
+        auto elems = [](const Act<__nv_bfloat16>& t) { return (double)t.sample_pixels() * (t.ps ? t.ps : t.C); };
+        const bool same_res = KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL;
+        if (elems(a.r) >= 2147483648.0 || elems(a.dr) >= 2147483648.0) return pl;
+        if (a.dr.W != a.r.W || a.dr.H != a.r.H) return pl;
+        if (KIND != SRC_OUTER && elems(a.g) >= 2147483648.0) return pl;
+        if (same_res && (a.g.W != a.r.W || a.g.H != a.r.H)) return pl;
+        if (KIND == SRC_BLEND_PS && (a.g.W != 2 * a.r.W || a.g.H != 2 * a.r.H)) return pl;
+        if (POOL && (a.gpool.W != UW || a.gpool.H != UH || elems(a.gpool) >= 2147483648.0)) return pl;
+    }
+#endif
 #ifdef MRISR_GNBWD_FASTDIV
     if (UW < 8 || (int64_t)pl.fp.rows_pc * UW >= (1 << 24)) return pl;            // outside the exact range: unfused path
 #endif

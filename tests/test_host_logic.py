@@ -294,6 +294,34 @@ def test_multiply_shift_row_index_is_exact():
         assert np.array_equal(q, n // np.uint64(uw)), uw
 
 
+def test_gn_bwd_incremental_addressing_replay(tmp_path):
+    """csrc/gn_bwd_trk.h (staged -DMRISR_GNBWD_INCR variant of gn_bwd_fused_kernel): tests/native/gn_bwd_trk_replay.cpp walks every
+    (cluster rank, thread) through the kernel's issue / reload / apply order with the constant-step tracker and compares every
+    operand index with the direct padded-pixel form of the default build; each unit must be issued and applied exactly once."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "trk_replay")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-I", os.path.join(root, "mri_superresolution_b200", "csrc"),
+                    os.path.join(root, "tests", "native", "gn_bwd_trk_replay.cpp"), "-o", exe], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert res.stdout.startswith("ok ")
+
+
+def test_library_variant_selection_fails_loudly():
+    """_native.py: MRISR_B200_VARIANT=<name> selects lib/libmrisr_b200_<name>.so; a variant that was not built raises (no
+    silent fall-back to the default build or to a CPU path)."""
+    import subprocess
+    import sys
+    code = ("import os; os.environ['MRISR_B200_VARIANT']='does_not_exist'\n"
+            "from mri_superresolution_b200 import _native\n"
+            "assert _native.LIB_PATH.endswith('libmrisr_b200_does_not_exist.so'), _native.LIB_PATH\n"
+            "try:\n    _native.lib()\nexcept RuntimeError as e:\n    print('raised', 'no CPU' in str(e))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root)
+    assert res.returncode == 0 and "raised True" in res.stdout, res.stdout + res.stderr
+
+
 def test_layer_engine_selection_by_input_size():
     """include/mrisr.h: mrisr_unet_layer_engine (host arithmetic only).  At the headline 256^2 and at 320^2 the narrow
     full-resolution / head layers run on the planar-8 sliding-window kernels (2) and every level >= 1 layer on the NHWC TMA

@@ -1,0 +1,20 @@
+#!/bin/bash
+# A/B of a staged build against the measured default: `gpurun -- 'bash tools/ab_variant.sh incr'` after
+#   make -C mri_superresolution_b200/csrc VARIANT=incr EXTRA=-DMRISR_GNBWD_INCR        (here; the .so travels with the snapshot)
+# Runs the GPU parity tests under the variant first (a variant that fails them is not timed), then the default bench twice
+# around the variant's (same box, back to back), with per-layer reports.
+cd "${GRAFT_REPO_ROOT:-.}"
+v=${1:?variant name}
+lib=mri_superresolution_b200/lib/libmrisr_b200_${v}.so
+[ -f "$lib" ] || { echo "missing $lib"; exit 2; }
+MRISR_B200_VARIANT=$v timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/ab_${v}_tests.log 2>&1; rc=$?
+tail -3 gpurun_out/ab_${v}_tests.log
+[ $rc -eq 0 ] || { echo "variant $v fails the GPU tests (rc=$rc): not timed"; exit 1; }
+for arm in default $v default2; do
+  var=$v; [ "$arm" = "$v" ] || var=""
+  MRISR_B200_VARIANT=$var timeout 600 python bench.py --no-cpu-baseline --layer-report gpurun_out/ab_${v}_${arm}_layers.txt \
+      > gpurun_out/ab_${v}_${arm}_bench.log 2>&1
+  echo "$arm: $(cut -c1-160 gpurun_out/ab_${v}_${arm}_bench.log | tail -1)"
+done
+grep -h "gn_bwd" gpurun_out/ab_${v}_default_layers.txt | head -12
+grep -h "gn_bwd" gpurun_out/ab_${v}_${v}_layers.txt | head -12
