@@ -413,6 +413,7 @@ struct FusedParams {
     // Builds with -DMRISR_GNBWD_INCR: operand addresses by constant steps (gn_bwd_trk.h) instead of a division and 64-bit
     // index arithmetic per unit (~100 of the 203 SASS instructions of the kind-0 phase-1 loop).  Staged, not measured yet.
     TrkStep ts;
+    int psr, psg, psd, psh;      // pixel strides (elements) of r, g, dr, gpool
 };
 
 #ifdef MRISR_GNBWD_INCR
@@ -435,6 +436,18 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+// shared-state-space forms (32-bit shared address) for the incremental build: no generic -> shared conversion per access
+[[maybe_unused]] __device__ __forceinline__ void cp_async16_s(uint32_t sdst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(gsrc) : "memory");
+}
+[[maybe_unused]] __device__ __forceinline__ void cp_async4_s(uint32_t sdst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(gsrc) : "memory");
+}
+[[maybe_unused]] __device__ __forceinline__ uint4 ld_shared_v4(uint32_t saddr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr) : "memory");
+    return v;
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -484,8 +497,13 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     // incremental form (kIncr): per-thread base pointers at (first row of this CTA, column 0) and the pixel strides in elements
     [[maybe_unused]] constexpr int PM = P == 4 ? 2 : 1;                 // pixels per unit along each axis
     [[maybe_unused]] const int pitch = a.r.W + 2, hpitch = UW + 2, gpitch = a.g.W + 2;
-    [[maybe_unused]] const int psr = a.r.ps ? a.r.ps : a.r.C, psg = a.g.ps ? a.g.ps : a.g.C, psd = a.dr.ps ? a.dr.ps : a.dr.C;
-    [[maybe_unused]] const int psh = POOL ? (a.gpool.ps ? a.gpool.ps : a.gpool.C) : 0;
+    [[maybe_unused]] const int psr = fp.psr, psg = fp.psg, psd = fp.psd, psh = fp.psh;      // pixel strides in elements
+    // slot handles: the slot index (default build) or the shared-memory byte address of this thread's first vector in the slot
+    // (kIncr: advanced by a constant with one wrap over the S streaming slots instead of slot_of(i) and a pointer product)
+    [[maybe_unused]] constexpr uint32_t kVec = FT * 16, kSlot = RAWV * FT * 16;
+    [[maybe_unused]] const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(cache) + tid * 16;
+    [[maybe_unused]] const uint32_t swrap0 = sbase + (uint32_t)K * kSlot, swrap1 = swrap0 + S * kSlot;
+    auto hnext = [&](uint32_t h) { h += kSlot; return h == swrap1 ? swrap0 : h; };
     [[maybe_unused]] const T* rb = nullptr; [[maybe_unused]] const T* gb = nullptr; [[maybe_unused]] const T* hb = nullptr; [[maybe_unused]] T* db = nullptr;
     if constexpr (kIncr) {
         rb = a.r.at(n, PM * r0, 0, cv * 8);
@@ -495,29 +513,30 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         if (KIND == SRC_BLEND_PS) gb = a.g.at(n, 2 * r0, 0, 2 * cv);
         if (POOL) hb = a.gpool.at(n, r0, 0, cv * 8);
     }
-    auto issue = [&](int i, int sidx, const UnitTrk& t) {                // unit i of this thread (at position t) -> slot sidx
-        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
+    auto issue = [&](int i, uint32_t h, const UnitTrk& t) {              // unit i of this thread (at position t) -> slot handle h
         if constexpr (kIncr) {
 #pragma unroll
             for (int q = 0; q < P; ++q) {
                 const int po = PM * t.px + (q >> 1) * pitch + (q & 1);         // pixels from the base, r / g / dr geometry
-                cp_async16(sl + q * FT, rb + po * psr);
-                uint4* sa = sl + (P + q) * FT;
+                cp_async16_s(h + q * kVec, rb + po * psr);
+                const uint32_t sa = h + (P + q) * kVec;
                 if (KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL) {
-                    cp_async16(sa, gb + po * psg);
+                    cp_async16_s(sa, gb + po * psg);
                 } else if (KIND == SRC_BLEND_PS) {
 #pragma unroll
                     for (int ij = 0; ij < 4; ++ij)
-                        cp_async4(reinterpret_cast<uint32_t*>(sa) + ij, gb + (2 * t.gpx + (ij >> 1) * gpitch + (ij & 1)) * psg);
+                        cp_async4_s(sa + 4 * ij, gb + (2 * t.gpx + (ij >> 1) * gpitch + (ij & 1)) * psg);
                 } else if (KIND == SRC_OUTER) {
                     const int64_t pix = ((int64_t)n * a.r.H + r0) * a.r.W + (p0 + i * pstep);
-                    cp_async4(reinterpret_cast<uint32_t*>(sa), a.y + pix);
-                    cp_async4(reinterpret_cast<uint32_t*>(sa) + 1, a.dy + pix);
+                    cp_async4_s(sa, a.y + pix);
+                    cp_async4_s(sa + 4, a.dy + pix);
                 }
             }
-            if (POOL) cp_async16(sl + 2 * P * FT, hb + t.hpx * psh);
+            if (POOL) cp_async16_s(h + 2 * P * kVec, hb + t.hpx * psh);
             return;
         }
+        const int sidx = (int)h;
+        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
         const int pi = p0 + i * pstep;
         int uy, ux;
         unit_row_col(pi, UW, fp.uw_magic, uy, ux);
@@ -544,7 +563,14 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         }
         if (POOL) cp_async16(sl + 2 * P * FT, a.gpool.at(n, uy, ux, cv * 8));
     };
-    auto fetch = [&](int sidx, Raw<P, POOL>& w) {
+    auto fetch = [&](uint32_t h, Raw<P, POOL>& w) {
+        if constexpr (kIncr) {
+#pragma unroll
+            for (int q = 0; q < P; ++q) { w.r[q] = ld_shared_v4(h + q * kVec); w.a[q] = ld_shared_v4(h + (P + q) * kVec); }
+            if (POOL) w.gp = ld_shared_v4(h + 2 * P * kVec);
+            return;
+        }
+        const int sidx = (int)h;
         const uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
 #pragma unroll
         for (int q = 0; q < P; ++q) { w.r[q] = sl[q * FT]; w.a[q] = sl[(P + q) * FT]; }
@@ -558,18 +584,20 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
     UnitTrk ti{0, 0, 0, 0};                            // position of the next unit to issue (kIncr)
     if constexpr (kIncr) ti = trk_at(p0, UW, pitch, hpitch, gpitch);
+    [[maybe_unused]] uint32_t hi = sbase, hf = sbase;  // handles of the next slot to issue into / to fetch from (kIncr)
 #pragma unroll
     for (int i = 0; i < S; ++i) {
         if (i < nu) {
-            issue(i, slot_of(i), ti);
-            if constexpr (kIncr) trk_fwd(ti, fp.ts, UW);
+            issue(i, kIncr ? hi : (uint32_t)slot_of(i), ti);
+            if constexpr (kIncr) { trk_fwd(ti, fp.ts, UW); hi = hnext(hi); }
         }
         cp_async_commit();
     }
     for (int i = 0; i < nu; ++i) {
         cp_async_wait<S - 1>();
         Raw<P, POOL> w;
-        fetch(slot_of(i), w);
+        fetch(kIncr ? hf : (uint32_t)slot_of(i), w);
+        if constexpr (kIncr) hf = hnext(hf);
         float rv[P][8], dz[P][8], act[8], dl = 0.f;
         grads_from_raw<KIND, P>(c, w, al, wv, rv, dz, dl, act);
 #pragma unroll
@@ -582,8 +610,8 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
             if (cvl == 0) sdl += dl;
         }
         if (i + S < nu) {                                      // the streaming slot just consumed (or a fresh one)
-            issue(i + S, slot_of(i + S), ti);
-            if constexpr (kIncr) trk_fwd(ti, fp.ts, UW);
+            issue(i + S, kIncr ? hi : (uint32_t)slot_of(i + S), ti);
+            if constexpr (kIncr) { trk_fwd(ti, fp.ts, UW); hi = hnext(hi); }
         }
         cp_async_commit();
     }
@@ -594,7 +622,7 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     for (int t = 0; t < S; ++t) {
         if (t < nstream) {
             if constexpr (kIncr) trk_bwd(ti, fp.ts, UW);
-            issue(nu - 1 - t, K + t, ti);
+            issue(nu - 1 - t, kIncr ? swrap0 + t * kSlot : (uint32_t)(K + t), ti);
         }
         cp_async_commit();
     }
@@ -708,21 +736,24 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     };
     UnitTrk tc{0, 0, 0, 0};                            // cached units: ascending from the thread's first unit
     if constexpr (kIncr) tc = trk_at(p0, UW, pitch, hpitch, gpitch);
+    hf = sbase;
     for (int i = 0; i < K && i < nu; ++i) {
         Raw<P, POOL> w;
-        fetch(i, w);
+        fetch(kIncr ? hf : (uint32_t)i, w);
         apply(i, w, tc);
-        if constexpr (kIncr) trk_fwd(tc, fp.ts, UW);
+        if constexpr (kIncr) { trk_fwd(tc, fp.ts, UW); hf += kSlot; }
     }
+    hf = swrap0;
     for (int t = 0; t < nstream; ++t) {                // streamed units: descending from unit nu - 1
         cp_async_wait<S - 1>();
         Raw<P, POOL> w;
-        fetch(K + t % S, w);
-        if constexpr (kIncr) trk_bwd(ta, fp.ts, UW);
+        const uint32_t hs = kIncr ? hf : (uint32_t)(K + t % S);       // streaming slot t % S: fetched, then refilled
+        fetch(hs, w);
+        if constexpr (kIncr) { trk_bwd(ta, fp.ts, UW); hf = hnext(hf); }
         apply(nu - 1 - t, w, ta);
         if (t + S < nstream) {
             if constexpr (kIncr) trk_bwd(ti, fp.ts, UW);
-            issue(nu - 1 - (t + S), K + t % S, ti);
+            issue(nu - 1 - (t + S), hs, ti);
         }
         cp_async_commit();
     }
@@ -787,6 +818,10 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
     pl.fp.uw_magic = ((1ull << 40) + (unsigned)UW - 1) / (unsigned)UW;
     pl.fp.ts = trk_steps(FT / ncv, UW, a.r.W + 2, a.g.W + 2);
+    pl.fp.psr = a.r.ps ? a.r.ps : a.r.C;
+    pl.fp.psg = a.g.ps ? a.g.ps : a.g.C;
+    pl.fp.psd = a.dr.ps ? a.dr.ps : a.dr.C;
+    pl.fp.psh = POOL ? (a.gpool.ps ? a.gpool.ps : a.gpool.C) : 0;
 #ifdef MRISR_GNBWD_INCR
     {
         // 32-bit element offsets inside a sample, and the operand geometries the incremental form assumes

@@ -56,20 +56,43 @@ static void replay(const Cfg& c) {
                         expect(pix(n, 2 * c.H, 2 * c.W, 2 * uy + (ij >> 1), 2 * ux + (ij & 1)) ==
                                    gbase + 2 * t.gpx + (ij >> 1) * gpitch + (ij & 1), c, "pixel-shuffle", rank, tid, i);
             };
+            // slot handles of the incremental build, in slot units: advance by one, wrap over the S streaming slots
+            auto slot_of = [&](int i) { return i < K ? i : K + (i - K) % S; };
+            auto hnext = [&](int h) { ++h; return h == K + S ? K : h; };
             // ---- phase 1 (same order as the kernel)
             UnitTrk ti = trk_at(p0, UW, pitch, hpitch, gpitch);
+            int hi = 0, hf = 0;
             for (int i = 0; i < S; ++i)
-                if (i < nu) { check(i, ti, "issue"); issued[i]++; trk_fwd(ti, ts, UW); }
-            for (int i = 0; i < nu; ++i)
-                if (i + S < nu) { check(i + S, ti, "issue"); issued[i + S]++; trk_fwd(ti, ts, UW); }
+                if (i < nu) {
+                    check(i, ti, "issue"); issued[i]++;
+                    expect(hi == slot_of(i), c, "issue slot", rank, tid, i);
+                    trk_fwd(ti, ts, UW); hi = hnext(hi);
+                }
+            for (int i = 0; i < nu; ++i) {
+                expect(hf == slot_of(i), c, "fetch slot", rank, tid, i);
+                hf = hnext(hf);
+                if (i + S < nu) {
+                    check(i + S, ti, "issue"); issued[i + S]++;
+                    expect(hi == slot_of(i + S), c, "issue slot", rank, tid, i + S);
+                    trk_fwd(ti, ts, UW); hi = hnext(hi);
+                }
+            }
             const int nstream = nu > K ? nu - K : 0;
             UnitTrk ta = ti;
             for (int t = 0; t < S; ++t)
                 if (t < nstream) { trk_bwd(ti, ts, UW); check(nu - 1 - t, ti, "reload"); reissued[nu - 1 - t]++; }
             // ---- phase 2
             UnitTrk tc = trk_at(p0, UW, pitch, hpitch, gpitch);
-            for (int i = 0; i < K && i < nu; ++i) { check(i, tc, "apply cached"); applied[i]++; trk_fwd(tc, ts, UW); }
+            hf = 0;
+            for (int i = 0; i < K && i < nu; ++i) {
+                check(i, tc, "apply cached"); applied[i]++;
+                expect(hf == i, c, "cached slot", rank, tid, i);
+                trk_fwd(tc, ts, UW); ++hf;
+            }
+            hf = K;
             for (int t = 0; t < nstream; ++t) {
+                expect(hf == K + t % S, c, "streamed slot", rank, tid, nu - 1 - t);
+                hf = hnext(hf);
                 trk_bwd(ta, ts, UW);
                 check(nu - 1 - t, ta, "apply streamed");
                 applied[nu - 1 - t]++;
