@@ -88,30 +88,55 @@ __device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, u
                  ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
 }
 
+// `#pragma unroll` for functions that are also compiled for the host (the host pass would warn about the unknown pragma)
+#ifdef __CUDA_ARCH__
+#define MRISR_UNROLL _Pragma("unroll")
+#else
+#define MRISR_UNROLL
+#endif
+
 // 8-channel vector load/store (16 B for bf16, 32 B for fp32); pointers must be 8-element aligned.
-__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+// __host__ __device__: kernel bodies written as plain functions of (block, thread) also run on the CPU in tests/native/.
+__host__ __device__ __forceinline__ float bits_to_float(uint32_t u) {
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+__host__ __device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
     const float4 a = *reinterpret_cast<const float4*>(p);
     const float4 b = *reinterpret_cast<const float4*>(p + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
-__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+__host__ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
     const uint4 r = *reinterpret_cast<const uint4*>(p);
     const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#ifdef __CUDA_ARCH__
 #pragma unroll
+#endif
     for (int i = 0; i < 4; ++i) {
-        v[2 * i] = __uint_as_float(w[i] << 16);
-        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        v[2 * i] = bits_to_float(w[i] << 16);
+        v[2 * i + 1] = bits_to_float(w[i] & 0xffff0000u);
     }
 }
-__device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
+__host__ __device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
     *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
     *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+__host__ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+#ifdef __CUDA_ARCH__
     return *reinterpret_cast<uint32_t*>(&t);
+#else
+    uint32_t u;
+    memcpy(&u, &t, 4);
+    return u;
+#endif
 }
-__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+__host__ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
     uint4 r;
     r.x = pack_bf16x2(v[0], v[1]); r.y = pack_bf16x2(v[2], v[3]);
     r.z = pack_bf16x2(v[4], v[5]); r.w = pack_bf16x2(v[6], v[7]);
@@ -131,7 +156,7 @@ __host__ __device__ __forceinline__ float up_scale(int in_size) {
     const int out_size = 2 * in_size;
     return out_size > 1 ? (float)(in_size - 1) / (float)(out_size - 1) : 0.f;
 }
-__device__ __forceinline__ Lerp up_coord(int dst, int in_size, float scale) {
+__host__ __device__ __forceinline__ Lerp up_coord(int dst, int in_size, float scale) {
     const float s = scale * (float)dst;
     Lerp l;
     l.i0 = (int)s;
@@ -147,7 +172,7 @@ __device__ __forceinline__ Lerp up_coord(int dst, int in_size, float scale) {
 // constants and per-channel partial sums live in registers) and walks columns x0, x0 + xstep, ...
 struct RowMap { int cv, x0, xstep; bool active; };
 template <typename T>
-__device__ __forceinline__ RowMap row_map(const Act<T>& t, int nthr, int tid) {
+__host__ __device__ __forceinline__ RowMap row_map(const Act<T>& t, int nthr, int tid) {
     const int nv = t.C / 8;
     RowMap m;
     if (t.planar()) {

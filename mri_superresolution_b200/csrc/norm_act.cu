@@ -7,6 +7,7 @@
 #include <mutex>
 #include <vector>
 #include "kernels.cuh"
+#include "upsample_slide.cuh"
 
 namespace mrisr {
 namespace {
@@ -517,6 +518,18 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     ProfScope prof_("upsample2x", s);
+#ifdef MRISR_UPSAMPLE_SLIDE
+    // staged: columns stay with a thread, source rows slide through registers (upsample_slide.cuh); 16 destination rows per
+    // block re-read 1 - 2 of their 9 - 10 source rows from the neighbouring blocks' (L2)
+    if ((int64_t)(src.W + 2) * (src.ps ? src.ps : src.C) < (1ll << 31) / (src.H + 2) &&
+        (int64_t)(dst.W + 2) * (dst.ps ? dst.ps : dst.C) < (1ll << 31) / (dst.H + 2)) {
+        const int rows = dst.H >= 64 ? 16 : 8;
+        dim3 grid_s(ceil_div(dst.H, rows), dst.N);
+        upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
+        MRISR_LAUNCH_CHECK();
+        return 0;
+    }
+#endif
     const int rpb = rows_per_block(dst.W, dst.C / 8, NTHR, 8);
     dim3 grid(ceil_div(dst.H, rpb), dst.N);
     upsample2x_kernel<T><<<grid, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rpb);

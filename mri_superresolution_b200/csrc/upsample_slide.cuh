@@ -1,0 +1,93 @@
+// Bilinear x2 (align_corners=True) with the two source rows of a destination column kept in registers
+// (staged build, -DMRISR_UPSAMPLE_SLIDE; the default is upsample2x_kernel in norm_act.cu).
+//
+// upsample2x_kernel gathers 4 source vectors and evaluates 5 Act::at address chains per destination vector: 325 SASS
+// instructions per two destination vectors, issue-bound at ~42 % of the HBM copy rate (profiles/r01_elementwise_issue.md).
+// Here a thread owns destination columns (fixed horizontal taps and weights, base pointers computed once) and walks the
+// block's destination rows: consecutive rows share at least one source row, so each step needs at most one new source row
+// (2 loads, horizontal blend) and one vertical blend.  Same expression tree as the default kernel:
+//   out = h0 * (a0 * s[i0y][i0x] + a1 * s[i0y][i1x]) + h1 * (a0 * s[i1y][i0x] + a1 * s[i1y][i1x]).
+// The body is a plain function of (sample, block, thread) so that tests/native/upsample_slide_host.cu runs it on the CPU.
+#pragma once
+#include "common.cuh"
+
+namespace mrisr {
+
+template <typename T, int UB>
+__host__ __device__ __forceinline__ void upsample2x_slide_body(const Act<T>& src, const Act<T>& dst, float sy, float sx, int rows_pb,
+                                                               int n, int block, int tid, int nthr) {
+    const RowMap m = row_map(dst, nthr, tid);
+    if (!m.active) return;
+    const int Y0 = block * rows_pb, Y1 = Y0 + rows_pb < dst.H ? Y0 + rows_pb : dst.H;
+    const int pss = src.ps ? src.ps : src.C, psd = dst.ps ? dst.ps : dst.C;
+    const int srs = (src.W + 2) * pss, drs = (dst.W + 2) * psd;           // row strides in elements (< 2^31: host check)
+    for (int X0 = m.x0; X0 < dst.W; X0 += UB * m.xstep) {
+        const T* sp[UB];
+        T* dp[UB];
+        int d1[UB];
+        float a1[UB];
+        bool on[UB];
+MRISR_UNROLL
+        for (int u = 0; u < UB; ++u) {
+            const int X = X0 + u * m.xstep;
+            on[u] = X < dst.W;
+            const int Xc = on[u] ? X : dst.W - 1;                         // clamped duplicate: loaded, never stored
+            const Lerp lx = up_coord(Xc, src.W, sx);
+            a1[u] = lx.w1;
+            sp[u] = src.at(n, 0, lx.i0, m.cv * 8);
+            d1[u] = (lx.i1 - lx.i0) * pss;
+            dp[u] = dst.at(n, 0, Xc, m.cv * 8);
+        }
+        float top[UB][8], bot[UB][8];
+        int ti = -1, bi = -1;                                             // source rows held in top / bot
+        auto load_row = [&](int r, float (&out)[UB][8]) {
+            float v0[UB][8], v1[UB][8];
+MRISR_UNROLL
+            for (int u = 0; u < UB; ++u) {
+                load8(sp[u] + (int64_t)r * srs, v0[u]);
+                load8(sp[u] + (int64_t)r * srs + d1[u], v1[u]);
+            }
+MRISR_UNROLL
+            for (int u = 0; u < UB; ++u) {
+                const float a0 = 1.f - a1[u];
+MRISR_UNROLL
+                for (int k = 0; k < 8; ++k) out[u][k] = a0 * v0[u][k] + a1[u] * v1[u][k];
+            }
+        };
+        auto copy_row = [&](const float (&from)[UB][8], float (&to)[UB][8]) {
+MRISR_UNROLL
+            for (int u = 0; u < UB; ++u)
+MRISR_UNROLL
+                for (int k = 0; k < 8; ++k) to[u][k] = from[u][k];
+        };
+        for (int Y = Y0; Y < Y1; ++Y) {
+            const Lerp ly = up_coord(Y, src.H, sy);
+            if (ly.i0 != ti) {
+                if (ly.i0 == bi) copy_row(bot, top); else load_row(ly.i0, top);
+                ti = ly.i0;
+            }
+            if (ly.i1 != bi) {
+                if (ly.i1 == ti) copy_row(top, bot); else load_row(ly.i1, bot);
+                bi = ly.i1;
+            }
+            const float h1 = ly.w1, h0 = 1.f - h1;
+MRISR_UNROLL
+            for (int u = 0; u < UB; ++u) {
+                if (!on[u]) continue;
+                float o[8];
+MRISR_UNROLL
+                for (int k = 0; k < 8; ++k) o[k] = h0 * top[u][k] + h1 * bot[u][k];
+                store8(dp[u] + (int64_t)Y * drs, o);
+            }
+        }
+    }
+}
+
+#ifdef __CUDACC__
+template <typename T, int UB, int NT>
+__global__ void __launch_bounds__(NT) upsample2x_slide_kernel(Act<T> src, Act<T> dst, float sy, float sx, int rows_pb) {
+    upsample2x_slide_body<T, UB>(src, dst, sy, sx, rows_pb, blockIdx.y, blockIdx.x, threadIdx.x, NT);
+}
+#endif
+
+}  // namespace mrisr

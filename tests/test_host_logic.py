@@ -308,6 +308,25 @@ def test_gn_bwd_incremental_addressing_replay(tmp_path):
     assert res.stdout.startswith("ok ")
 
 
+def test_upsample_slide_body_runs_on_host(tmp_path):
+    """csrc/upsample_slide.cuh (staged -DMRISR_UPSAMPLE_SLIDE kernel): the kernel body is a __host__ __device__ function of
+    (sample, block, thread); tests/native/upsample_slide_host.cu executes every thread of the launch grid on the CPU (NHWC and
+    planar-8, fp32 and bf16, odd and one-row shapes) and compares bit for bit with the default kernel's direct form."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "upsample_slide_host")
+    subprocess.run([nvcc, "-std=c++17", "-O1", "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets", "-I",
+                    os.path.join(root, "mri_superresolution_b200", "csrc"),
+                    os.path.join(root, "tests", "native", "upsample_slide_host.cu"), "-o", exe], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert res.stdout.startswith("ok ")
+
+
 def test_library_variant_selection_fails_loudly():
     """_native.py: MRISR_B200_VARIANT=<name> selects lib/libmrisr_b200_<name>.so; a variant that was not built raises (no
     silent fall-back to the default build or to a CPU path)."""
