@@ -8,6 +8,7 @@
 #include <vector>
 #include "kernels.cuh"
 #include "upsample_slide.cuh"
+#include "upsample_bwd_slide.cuh"
 
 namespace mrisr {
 namespace {
@@ -546,6 +547,22 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
+#ifdef MRISR_UPSAMPLE_BWD_SLIDE
+    // staged: scatter-along-rows form (upsample_bwd_slide.cuh): one horizontal reduction per destination row instead of one per
+    // (source row, destination row) pair; 16 source rows per block
+    static_assert(sizeof(UpAdjTap) == sizeof(AdjTap5), "tap table layouts must agree");
+    if ((int64_t)(ddst.W + 2) * (ddst.ps ? ddst.ps : ddst.C) < (1ll << 31) / (ddst.H + 2) && dsrc.W <= kAdjMaxW) {
+        const AdjTap5* ty = adj_table(dsrc.H, s);
+        const AdjTap5* tx = dsrc.W == dsrc.H ? ty : adj_table(dsrc.W, s);
+        if (!ty || !tx) { set_error("upsample2x_bwd: tap table allocation failed"); return -1; }
+        const int rows = dsrc.H >= 32 ? 16 : 8;
+        dim3 grid_s(ceil_div(dsrc.H, rows), dsrc.N);
+        upsample2x_bwd_slide_kernel<T, NTHR><<<grid_s, NTHR, 0, s>>>(ddst, addend, dsrc, reinterpret_cast<const UpAdjTap*>(ty),
+                                                                    reinterpret_cast<const UpAdjTap*>(tx), up_scale(dsrc.H), rows);
+        MRISR_LAUNCH_CHECK();
+        return 0;
+    }
+#endif
     if constexpr (sizeof(T) == 2) {
         UpBwdTile tp;
         size_t smem = 0;

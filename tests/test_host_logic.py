@@ -308,6 +308,29 @@ def test_gn_bwd_incremental_addressing_replay(tmp_path):
     assert res.stdout.startswith("ok ")
 
 
+def _run_host_kernel_body(tmp_path, name):
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / name)
+    subprocess.run([nvcc, "-std=c++17", "-O1", "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets", "-I",
+                    os.path.join(root, "mri_superresolution_b200", "csrc"),
+                    os.path.join(root, "tests", "native", name + ".cu"), "-o", exe], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert res.stdout.startswith("ok ")
+
+
+def test_upsample_bwd_slide_body_runs_on_host(tmp_path):
+    """csrc/upsample_bwd_slide.cuh (staged -DMRISR_UPSAMPLE_BWD_SLIDE kernel): scatter-along-rows adjoint of bilinear x2,
+    every thread of 14 launch grids executed on the CPU and compared bit for bit with the gather form of the shipped kernels
+    (same taps, weights and summation order), with and without the addend, NHWC / planar-8, fp32 / bf16."""
+    _run_host_kernel_body(tmp_path, "upsample_bwd_slide_host")
+
+
 def test_upsample_slide_body_runs_on_host(tmp_path):
     """csrc/upsample_slide.cuh (staged -DMRISR_UPSAMPLE_SLIDE kernel): the kernel body is a __host__ __device__ function of
     (sample, block, thread); tests/native/upsample_slide_host.cu executes every thread of the launch grid on the CPU (NHWC and

@@ -1,6 +1,7 @@
 #!/bin/bash
-# A/B of a staged build against the measured default: `gpurun -- 'bash tools/ab_variant.sh incr'` after
-#   make -C mri_superresolution_b200/csrc VARIANT=incr EXTRA=-DMRISR_GNBWD_INCR        (here; the .so travels with the snapshot)
+# A/B of a staged build against the measured default: `gpurun -- 'bash tools/ab_variant.sh incr'` after `bash tools/build_variants.sh`
+# (run here; the .so files travel with the snapshot).  Variants: incr (gn_bwd constant-step addressing), ups (sliding bilinear x2
+# forward + scatter-form adjoint), all (the three together).
 # Runs the GPU parity tests under the variant first (a variant that fails them is not timed), then the default bench twice
 # around the variant's (same box, back to back), with per-layer reports.
 cd "${GRAFT_REPO_ROOT:-.}"
