@@ -34,6 +34,22 @@ inline double gn_bwd_chunk_bytes() {
 
 template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
 
+// Builds with -DMRISR_DALPHA_FUSED: the blend kinds also accumulate  sum g * lrelu(z)  per channel (third partial-sum row, as
+// SRC_OUTER does for the 1x1 weights) and the finalize kernel writes the per-parameter-channel totals to `dwvec`; the caller
+// (unet_run.cu) forms d(alpha) = s(1-s) * (sum over the bilinear branch - sum over the pixel-shuffle branch) from the two
+// vectors instead of launching blend_dalpha_kernel, which re-reads both branches and the gradient (0.37 ms of the 17.7 ms
+// step) for one scalar.  Staged, not measured yet.
+#ifdef MRISR_DALPHA_FUSED
+constexpr bool kDalpha = true;
+#else
+constexpr bool kDalpha = false;
+#endif
+template <int KIND> struct ThirdRow {
+    static constexpr bool blend = kDalpha && (KIND == SRC_BLEND_BIL || KIND == SRC_BLEND_PS);
+    static constexpr bool on = KIND == SRC_OUTER || blend;
+};
+
+
 // Per-thread context for 8 channels of one sample: GroupNorm folded into z = r * sc + sh
 struct ChanCtx {
     float sc[8], sh[8];
@@ -70,6 +86,10 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
         } else if (KIND == SRC_BLEND_BIL) {
             const float al = 1.f / (1.f + __expf(-a.alpha[0]));
             load8(a.g.at(n, y, x, cv * 8), dA);
+            if (ThirdRow<KIND>::blend) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) act_out[k] = dA[k] * lrelu(z[q][k]);
+            }
 #pragma unroll
             for (int k = 0; k < 8; ++k) dA[k] *= al;
         } else if (KIND == SRC_BLEND_PS) {
@@ -77,7 +97,13 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const int ch = cv * 8 + k, cs = ch >> 2, i = (ch >> 1) & 1, j = ch & 1;
+#ifdef MRISR_DALPHA_FUSED
+                const float graw = to_f(*a.g.at(n, 2 * y + i, 2 * x + j, cs));
+                act_out[k] = graw * lrelu(z[q][k]);
+                dA[k] = om * graw;
+#else
                 dA[k] = om * to_f(*a.g.at(n, 2 * y + i, 2 * x + j, cs));
+#endif
             }
         } else if (KIND == SRC_OUTER) {
             const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
@@ -160,6 +186,9 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_reduce_kernel(GnBwdArgs<T> a, int
 #pragma unroll
                         for (int k = 0; k < 8; ++k) s3[k] += dl[u] * act[u][k];
                         if (m.cv == 0) sdl += dl[u];
+                    } else if (ThirdRow<KIND>::blend) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) s3[k] += act[u][k];
                     }
                 }
             }
@@ -237,10 +266,8 @@ __global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, i
             const double mean = (double)a.stats[(n * kGroups + g) * 2], rstd = (double)a.stats[(n * kGroups + g) * 2 + 1];
             d1 += (double)q[ch];
             d2 += rstd * ((double)q[row + ch] - mean * (double)q[ch]);
-            if (KIND == SRC_OUTER) {
-                d3 += (double)q[2 * row + ch];
-                if (pc == 0) d4 += (double)q[C];
-            }
+            if (ThirdRow<KIND>::on) d3 += (double)q[2 * row + ch];
+            if (KIND == SRC_OUTER && pc == 0) d4 += (double)q[C];
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -259,6 +286,8 @@ __global__ void __launch_bounds__(FTHR) gn_bwd_finalize_kernel(GnBwdArgs<T> a, i
             if (KIND == SRC_OUTER) {
                 a.dwvec[pc] = (float)d3;
                 if (pc == 0) a.dbias[0] = (float)d4;
+            } else if (ThirdRow<KIND>::blend) {
+                if (a.dwvec) a.dwvec[pc] = (float)d3;            // sum g * lrelu(z) of this parameter channel (d(alpha) term)
             }
         }
     }
@@ -349,14 +378,26 @@ __device__ __forceinline__ void grads_from_raw(const ChanCtx& c, const Raw<P, Ki
             unpack8(w.a[q], dA);
         } else if (KIND == SRC_BLEND_BIL) {
             unpack8(w.a[q], dA);
+            if (ThirdRow<KIND>::blend) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) act_out[k] = dA[k] * lrelu(z[q][k]);
+            }
 #pragma unroll
             for (int k = 0; k < 8; ++k) dA[k] *= al;
         } else if (KIND == SRC_BLEND_PS) {
             const uint32_t t[4] = {w.a[q].x, w.a[q].y, w.a[q].z, w.a[q].w};
 #pragma unroll
             for (int ij = 0; ij < 4; ++ij) {
+#ifdef MRISR_DALPHA_FUSED
+                const float g0 = __uint_as_float(t[ij] << 16), g1 = __uint_as_float(t[ij] & 0xffff0000u);
+                act_out[ij] = g0 * lrelu(z[q][ij]);
+                act_out[4 + ij] = g1 * lrelu(z[q][4 + ij]);
+                dA[ij] = al * g0;
+                dA[4 + ij] = al * g1;
+#else
                 dA[ij] = al * __uint_as_float(t[ij] << 16);
                 dA[4 + ij] = al * __uint_as_float(t[ij] & 0xffff0000u);
+#endif
             }
         } else if (KIND == SRC_OUTER) {
             const float yy = __uint_as_float(w.a[q].x);
@@ -608,6 +649,9 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
 #pragma unroll
             for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
             if (cvl == 0) sdl += dl;
+        } else if (ThirdRow<KIND>::blend) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s3[k] += act[k];
         }
         if (i + S < nu) {                                      // the streaming slot just consumed (or a fresh one)
             issue(i + S, kIncr ? hi : (uint32_t)slot_of(i + S), ti);
@@ -632,7 +676,7 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         for (int o = 16; o >= ncv; o >>= 1) {
             s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], o);
             s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], o);
-            if (KIND == SRC_OUTER) s3[k] += __shfl_xor_sync(0xffffffffu, s3[k], o);
+            if (ThirdRow<KIND>::on) s3[k] += __shfl_xor_sync(0xffffffffu, s3[k], o);
         }
     }
     if (lane < ncv) {

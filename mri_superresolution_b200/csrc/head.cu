@@ -125,6 +125,22 @@ __global__ void dalpha_finalize_kernel(const float* __restrict__ scratch, int nb
     }
 }
 
+#ifdef MRISR_DALPHA_FUSED
+// -DMRISR_DALPHA_FUSED builds: d(alpha) from the per-channel sums  sum g * xb  (bilinear branch) and  sum g * xp  (pixel-shuffle
+// branch) that gn_bwd's finalize kernels of the two branches leave in `sums` ([2][nch]); one warp
+__global__ void dalpha_from_channels_kernel(const float* __restrict__ sums, int nch, const float* __restrict__ alpha,
+                                            float* __restrict__ dalpha) {
+    double t = 0.0;
+    for (int i = threadIdx.x; i < nch; i += 32) t += (double)sums[i] - (double)sums[nch + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (threadIdx.x == 0) {
+        const float s = sigmoidf_(alpha[0]);
+        dalpha[0] = (float)(t * (double)(s * (1.f - s)));
+    }
+}
+#endif
+
 // one thread per output pixel: all Ch channels (Ch = f/2: 8 or 16 ... up to 64); one block = rows of ONE sample so the
 // folded GroupNorm scale/shift and the 1x1 weights sit in shared memory
 template <typename T>
@@ -228,6 +244,15 @@ int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float*
     MRISR_LAUNCH_CHECK();
     return 0;
 }
+
+#ifdef MRISR_DALPHA_FUSED
+int launch_dalpha_from_channels(const float* sums, int nch, const float* alpha, float* dalpha, cudaStream_t s) {
+    ProfScope prof_("blend_dalpha", s);
+    dalpha_from_channels_kernel<<<1, 32, 0, s>>>(sums, nch, alpha, dalpha);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+#endif
 
 template <typename T>
 int launch_final_head(Act<T> r, const float* stats, const float* gamma, const float* beta, const float* w1x1,

@@ -1,7 +1,7 @@
 #!/bin/bash
 # A/B of a staged build against the measured default: `gpurun -- 'bash tools/ab_variant.sh incr'` after `bash tools/build_variants.sh`
 # (run here; the .so files travel with the snapshot).  Variants: incr (gn_bwd constant-step addressing), ups (sliding bilinear x2
-# forward + scatter-form adjoint), all (the three together).
+# forward + scatter-form adjoint), dalpha (d(alpha) sums inside gn_bwd instead of blend_dalpha_kernel), all (everything).
 # Runs the GPU parity tests under the variant first (a variant that fails them is not timed), then the default bench twice
 # around the variant's (same box, back to back), with per-layer reports.
 cd "${GRAFT_REPO_ROOT:-.}"
@@ -17,5 +17,5 @@ for arm in default $v default2; do
       > gpurun_out/ab_${v}_${arm}_bench.log 2>&1
   echo "$arm: $(cut -c1-160 gpurun_out/ab_${v}_${arm}_bench.log | tail -1)"
 done
-grep -h "gn_bwd" gpurun_out/ab_${v}_default_layers.txt | head -12
-grep -h "gn_bwd" gpurun_out/ab_${v}_${v}_layers.txt | head -12
+grep -h "gn_bwd\|upsample\|blend" gpurun_out/ab_${v}_default_layers.txt | head -24
+grep -h "gn_bwd\|upsample\|blend" gpurun_out/ab_${v}_${v}_layers.txt | head -24

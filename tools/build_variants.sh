@@ -5,5 +5,6 @@ set -e
 cd "$(dirname "$0")/../mri_superresolution_b200/csrc"
 make -j"$(nproc)" VARIANT=incr EXTRA="-DMRISR_GNBWD_INCR"
 make -j"$(nproc)" VARIANT=ups EXTRA="-DMRISR_UPSAMPLE_SLIDE -DMRISR_UPSAMPLE_BWD_SLIDE"
-make -j"$(nproc)" VARIANT=all EXTRA="-DMRISR_GNBWD_INCR -DMRISR_UPSAMPLE_SLIDE -DMRISR_UPSAMPLE_BWD_SLIDE"
+make -j"$(nproc)" VARIANT=dalpha EXTRA="-DMRISR_DALPHA_FUSED"
+make -j"$(nproc)" VARIANT=all EXTRA="-DMRISR_GNBWD_INCR -DMRISR_UPSAMPLE_SLIDE -DMRISR_UPSAMPLE_BWD_SLIDE -DMRISR_DALPHA_FUSED"
 ls -la ../lib
