@@ -503,12 +503,17 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
     }
     ProfScope prof_(tag, s);
     const int nv = r.C / 8;
+    // vectors per thread and block (MRISR_GNAPPLY_UPT, MRISR_GNAPPLY_POOL_UPT; defaults = the measured build): the per-channel
+    // constants cost a block ~370 instructions and 32 dependent-free scalar loads before its first vector, about a quarter of
+    // a 16-vector thread's work (profiles/r01_elementwise_issue.md); longer blocks amortise it at the price of fewer waves
+    static const int upt = [] { const char* e = getenv("MRISR_GNAPPLY_UPT"); const int v = e ? atoi(e) : 16; return v > 0 ? v : 16; }();
+    static const int upt_pool = [] { const char* e = getenv("MRISR_GNAPPLY_POOL_UPT"); const int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();
     if (pooled.p) {
-        const int rpb = rows_per_block(r.W / 2, nv, NTHR, 4);
+        const int rpb = rows_per_block(r.W / 2, nv, NTHR, upt_pool);
         dim3 grid(ceil_div(r.H / 2, rpb), r.N);
         gn_apply_kernel<T, true><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     } else {
-        const int rpb = rows_per_block(r.W, nv, NTHR, 16);
+        const int rpb = rows_per_block(r.W, nv, NTHR, upt);
         dim3 grid(ceil_div(r.H, rpb), r.N);
         gn_apply_kernel<T, false><<<grid, NTHR, 0, s>>>(r, stats, gamma, beta, a, pooled, rpb);
     }
@@ -524,7 +529,8 @@ int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     // block re-read 1 - 2 of their 9 - 10 source rows from the neighbouring blocks' (L2)
     if ((int64_t)(src.W + 2) * (src.ps ? src.ps : src.C) < (1ll << 31) / (src.H + 2) &&
         (int64_t)(dst.W + 2) * (dst.ps ? dst.ps : dst.C) < (1ll << 31) / (dst.H + 2)) {
-        const int rows = dst.H >= 64 ? 16 : 8;
+        static const int rows_env = [] { const char* e = getenv("MRISR_UPSLIDE_ROWS"); return e ? atoi(e) : 0; }();
+        const int rows = rows_env > 0 ? rows_env : (dst.H >= 64 ? 16 : 8);
         dim3 grid_s(ceil_div(dst.H, rows), dst.N);
         upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
         MRISR_LAUNCH_CHECK();
@@ -555,7 +561,8 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         const AdjTap5* ty = adj_table(dsrc.H, s);
         const AdjTap5* tx = dsrc.W == dsrc.H ? ty : adj_table(dsrc.W, s);
         if (!ty || !tx) { set_error("upsample2x_bwd: tap table allocation failed"); return -1; }
-        const int rows = dsrc.H >= 32 ? 16 : 8;
+        static const int rows_env = [] { const char* e = getenv("MRISR_UPBWD_SLIDE_ROWS"); return e ? atoi(e) : 0; }();
+        const int rows = rows_env > 0 ? rows_env : (dsrc.H >= 32 ? 16 : 8);
         dim3 grid_s(ceil_div(dsrc.H, rows), dsrc.N);
         upsample2x_bwd_slide_kernel<T, NTHR><<<grid_s, NTHR, 0, s>>>(ddst, addend, dsrc, reinterpret_cast<const UpAdjTap*>(ty),
                                                                     reinterpret_cast<const UpAdjTap*>(tx), up_scale(dsrc.H), rows);
