@@ -6,13 +6,25 @@
 // uses the same mapping with 72 accumulators per thread and a fixed-order block / grid reduction (deterministic).
 // bf16 only (the fp32 parity mode keeps conv_generic.cu); the output / gradient tensor may be planar-8 or NHWC (the layout of
 // level 0 at wide images, unet_plan.cuh: level_is_planar) - RowMap gives the thread mapping of either.
+#include <stdlib.h>
 #include "kernels.cuh"
 
 namespace mrisr {
 namespace {
 using bf16 = __nv_bfloat16;
 constexpr int NTHR = 256;
-constexpr int kUnitsFwd = 16, kUnitsBwd = 64;
+constexpr int kUnitsBwd = 64;
+// output vectors per thread and block of conv_first_kernel: 16 in the measured build.  A block pays a fixed price around its
+// rows (72 scalar weight loads, a serial shared-memory reduction of the GroupNorm statistics, two barriers) that is comparable
+// to 16 vectors of work; MRISR_CONVFIRST_UPT (>= 16, so the statistics scratch sized for 16 still fits) lengthens the blocks.
+inline int units_fwd() {
+    static const int v = [] {
+        const char* e = getenv("MRISR_CONVFIRST_UPT");
+        const int u = e ? atoi(e) : 16;
+        return u < 16 ? 16 : (u > 4096 ? 4096 : u);
+    }();
+    return v;
+}
 
 // x: [N][H+2][W+2][1] (zero border), w: packed [tap][1][Cout] bf16, dst planar-8 [Cout]
 __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf16* __restrict__ w, Act<bf16> dst,
@@ -165,7 +177,7 @@ bool conv_first_supported(const Act<__nv_bfloat16>& src, const Act<__nv_bfloat16
     const int nv = dst.C / 8;
     return ks == 3 && src.C == 1 && dst.C % 8 == 0 && dst.C <= 64 && (NTHR / nv) % 32 == 0 && NTHR % nv == 0 && 32 % nv == 0;
 }
-int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsFwd)); }
+int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_per_block(W, Cout / 8, NTHR, units_fwd())); }
 size_t wgrad_first_scratch_elems(int N, int H, int W, int Cout) {
     return (size_t)N * ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsBwd)) * 9 * Cout;
 }
@@ -179,7 +191,7 @@ int launch_conv_first(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s) {
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-    const int rpb = rows_per_block(a.dst.W, a.dst.C / 8, NTHR, kUnitsFwd);
+    const int rpb = rows_per_block(a.dst.W, a.dst.C / 8, NTHR, units_fwd());
     conv_first_kernel<<<dim3(ceil_div(a.dst.H, rpb), a.dst.N), NTHR, 0, s>>>(a.src1, a.w, a.dst, a.stat_part, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
