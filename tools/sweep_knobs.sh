@@ -1,0 +1,25 @@
+#!/bin/bash
+# One GPU call that times the unswept block-size knobs and the env-selected staged kernels against the default:
+#   gpurun --timeout 1500 -- 'bash tools/sweep_knobs.sh'
+# Each arm = the default train bench (batch 64, 256^2) with one setting changed; prints the step time and the affected
+# per-family lines of the layer report.  Kernel variants that need another library are handled by tools/ab_variant.sh.
+cd "${GRAFT_REPO_ROOT:-.}"
+run() {   # name, grep pattern, env assignments...
+  local name=$1 pat=$2; shift 2
+  env "$@" timeout 400 python bench.py --no-cpu-baseline --steps 10 --warmup 3 --layer-report gpurun_out/sweep_${name}_layers.txt \
+      > gpurun_out/sweep_${name}.log 2>&1
+  local ms=$(tail -1 gpurun_out/sweep_${name}.log | python -c "import sys,json; print('%.3f' % json.loads(sys.stdin.readline())['ms_per_step'])" 2>/dev/null)
+  echo "== $name: ${ms:-FAILED} ms/step"
+  grep -h "$pat" gpurun_out/sweep_${name}_layers.txt 2>/dev/null | awk '{printf "   %-44s %s ms\n", $1, $5}' | head -8
+}
+run default "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
+run default_again "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
+for u in 32 64 128; do run gnapply_upt$u "gn_apply:pool0" MRISR_GNAPPLY_UPT=$u; done
+for u in 8 16; do run gnapply_pool_upt$u "gn_apply:pool1" MRISR_GNAPPLY_POOL_UPT=$u; done
+for u in 64 256; do run convfirst_upt$u "conv_first" MRISR_CONVFIRST_UPT=$u; done
+# the two-kernel SSIM only after its parity test passes
+if MRISR_TEST_STAGED=1 timeout 300 python -m pytest tests/test_gpu_knobs.py -q -k staged > gpurun_out/sweep_ssim_split_test.log 2>&1; then
+  run ssim_split "l1_ssim" MRISR_SSIM_SPLIT=1
+else
+  echo "== ssim_split: parity test failed (gpurun_out/sweep_ssim_split_test.log)"; tail -5 gpurun_out/sweep_ssim_split_test.log
+fi
