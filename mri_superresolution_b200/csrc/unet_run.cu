@@ -1,4 +1,5 @@
 // Forward and backward schedules of UNetSuperRes over the workspace (see unet_plan.cuh).
+#include <stdlib.h>
 #include "../../include/mrisr.h"
 #include "unet_plan.cuh"
 
@@ -14,6 +15,37 @@ static int64_t grads_final_from(const ParamLayout& pl, const ConvDesc (&conv)[kN
     if (l >= 19 || l == 17) return pl.off[conv[19].w];
     if (l == 18) return pl.off[conv[17].w];
     return l <= 0 ? 0 : pl.off[conv[l].w];
+}
+
+// MRISR_BWD_SIDE=1 (staged, default off, not measured yet): weight-gradient kernels run on a second, lower-priority stream,
+// forked from the main stream once their layer's dR is ready and joined before a gradient-readiness mark is recorded / at the
+// end of backward.  They only read activations and dR (never rewritten during backward: every tensor of the workspace has its
+// own buffer) and write the gradient arena and their own partial-sum scratch, so they are independent of the data-gradient
+// chain; the chain is the critical path and its small deep-level kernels leave SMs idle that the weight gradients can use.
+// Created on first use outside stream capture (the graph helpers warm up eagerly first); fork / join by events, which a
+// capturing stream records as graph dependencies.
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork_ev[kNumConv] = {};
+    cudaEvent_t join_ev = nullptr;
+    bool ok = false;
+};
+static SideStream* side_stream() {
+    static const bool enabled = [] { const char* e = getenv("MRISR_BWD_SIDE"); return e && e[0] == '1'; }();
+    if (!enabled) return nullptr;
+    static SideStream ss;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        int lo = 0, hi = 0;
+        bool good = cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess &&
+                    cudaStreamCreateWithPriority(&ss.stream, cudaStreamNonBlocking, lo) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&ss.join_ev, cudaEventDisableTiming) == cudaSuccess;
+        for (int l = 0; good && l < kNumConv; ++l) good = cudaEventCreateWithFlags(&ss.fork_ev[l], cudaEventDisableTiming) == cudaSuccess;
+        ss.ok = good;
+        if (!good) cudaGetLastError();
+    }
+    return ss.ok ? &ss : nullptr;
 }
 
 template <typename T>
@@ -136,10 +168,21 @@ struct Runner {
     const int64_t* mark_off = nullptr;
     void* const* mark_ev = nullptr;
     unsigned marks_done = 0;
+    SideStream* side = nullptr;           // weight gradients on a second stream (MRISR_BWD_SIDE=1), else nullptr
+    bool side_pending = false;
+    int side_join() {
+        if (side && side_pending) {
+            MRISR_CUDA_CHECK(cudaEventRecord(side->join_ev, side->stream));
+            MRISR_CUDA_CHECK(cudaStreamWaitEvent(s, side->join_ev, 0));
+            side_pending = false;
+        }
+        return 0;
+    }
     int block_done(int l) {
         const int64_t from = grads_final_from(pl, ws.conv, l);
         for (int k = 0; k < n_marks; ++k)
             if (!(marks_done >> k & 1u) && mark_off[k] >= from) {
+                TRY(side_join());                               // the mark covers weight gradients still on the side stream
                 MRISR_CUDA_CHECK(cudaEventRecord((cudaEvent_t)mark_ev[k], s));
                 marks_done |= 1u << k;
             }
@@ -165,16 +208,23 @@ struct Runner {
         const int e = eng(l);
         const bool use_tc = e != ENG_GENERIC;
         bool done = false;
+        cudaStream_t sw = s;                                    // stream of the weight-gradient kernels
+        if (side) {
+            MRISR_CUDA_CHECK(cudaEventRecord(side->fork_ev[l], s));          // dy (and everything before it) is ready
+            MRISR_CUDA_CHECK(cudaStreamWaitEvent(side->stream, side->fork_ev[l], 0));
+            sw = side->stream;
+            side_pending = true;
+        }
         if constexpr (sizeof(T) == 2) {
             if (use_tc) {
                 const int c2 = src2.p ? src2.C : 0;
-                if (e == ENG_RING && wgrad_rows_supported(dy.N, dy.H, dy.W, src1.C, c2, dy.C, c.ks)) TRY(launch_wgrad_rows(w, s));
-                else TRY(e == ENG_RING ? launch_wgrad_ring(w, s) : launch_wgrad_tc(w, s));
+                if (e == ENG_RING && wgrad_rows_supported(dy.N, dy.H, dy.W, src1.C, c2, dy.C, c.ks)) TRY(launch_wgrad_rows(w, sw));
+                else TRY(e == ENG_RING ? launch_wgrad_ring(w, sw) : launch_wgrad_tc(w, sw));
                 done = true;
             }
-            else if (l == 0 && conv_first_supported(src1, dy, c.ks)) { TRY(launch_wgrad_first(w, s)); done = true; }
+            else if (l == 0 && conv_first_supported(src1, dy, c.ks)) { TRY(launch_wgrad_first(w, sw)); done = true; }
         }
-        if (!done) TRY(launch_wgrad_generic<T>(w, s));
+        if (!done) TRY(launch_wgrad_generic<T>(w, sw));
         if (want_dgrad) {
             ConvArgs<T> a;
             a.src1 = dy; a.src2 = none; a.w = ws.wd[l]; a.bias = nullptr; a.dst = ws.G[l]; a.stat_part = nullptr; a.ks = c.ks;
@@ -262,6 +312,7 @@ struct Runner {
         TRY(block_bwd(1, SRC_DIRECT_POOL, ws.G[15], 0, ws.G[2], ws.A[0], none));
         TRY(block_done(1));
         TRY(block_bwd(0, SRC_DIRECT, ws.G[1], 0, none, ws.X0, none, false));
+        TRY(side_join());
         TRY(block_done(0));
         return 0;
     }
@@ -286,7 +337,10 @@ static int backward_t(const float* params, const float* dy, const float* y, floa
     ParamLayout pl(f);
     Runner<T> r{ws, pl, params, s};
     r.n_marks = n_marks; r.mark_off = mark_off; r.mark_ev = mark_ev;
-    return r.backward(dy, y, grads);
+    r.side = side_stream();
+    const int rc = r.backward(dy, y, grads);
+    if (rc && r.side_pending) r.side_join();                    // never leave forked work unjoined (stream capture would fail to end)
+    return rc;
 }
 
 template <typename T>

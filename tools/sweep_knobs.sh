@@ -17,9 +17,19 @@ run default_again "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
 for u in 32 64 128; do run gnapply_upt$u "gn_apply:pool0" MRISR_GNAPPLY_UPT=$u; done
 for u in 8 16; do run gnapply_pool_upt$u "gn_apply:pool1" MRISR_GNAPPLY_POOL_UPT=$u; done
 for u in 64 256; do run convfirst_upt$u "conv_first" MRISR_CONVFIRST_UPT=$u; done
-# the two-kernel SSIM only after its parity test passes
-if MRISR_TEST_STAGED=1 timeout 300 python -m pytest tests/test_gpu_knobs.py -q -k staged > gpurun_out/sweep_ssim_split_test.log 2>&1; then
+# the env-selected staged paths, each only after its parity test passes
+if MRISR_TEST_STAGED=1 timeout 300 python -m pytest tests/test_gpu_knobs.py -q -k staged_ssim > gpurun_out/sweep_ssim_split_test.log 2>&1; then
   run ssim_split "l1_ssim" MRISR_SSIM_SPLIT=1
 else
   echo "== ssim_split: parity test failed (gpurun_out/sweep_ssim_split_test.log)"; tail -5 gpurun_out/sweep_ssim_split_test.log
 fi
+if MRISR_TEST_STAGED=1 timeout 300 python -m pytest tests/test_gpu_knobs.py -q -k staged_side > gpurun_out/sweep_bwd_side_test.log 2>&1; then
+  run bwd_side "wgrad\|conv_tc:k3:256" MRISR_BWD_SIDE=1
+  MRISR_BWD_SIDE=1 timeout 300 python -m pytest tests/test_gpu_parity.py -q -k "graph" > gpurun_out/sweep_bwd_side_graph_test.log 2>&1
+  echo "   graph tests under MRISR_BWD_SIDE=1: $(tail -1 gpurun_out/sweep_bwd_side_graph_test.log)"
+else
+  echo "== bwd_side: parity test failed (gpurun_out/sweep_bwd_side_test.log)"; tail -5 gpurun_out/sweep_bwd_side_test.log
+fi
+# library variants: bit-level comparison with the default on the probe shape (the full parity suite + timing: tools/ab_variant.sh)
+MRISR_TEST_STAGED=1 timeout 600 python -m pytest tests/test_gpu_knobs.py -q -k staged_library > gpurun_out/sweep_libs_test.log 2>&1
+echo "== staged libraries vs default: $(tail -1 gpurun_out/sweep_libs_test.log)"
