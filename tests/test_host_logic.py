@@ -406,3 +406,17 @@ def test_graph_and_driver_entry_points_fail_loudly_without_cuda(tmp_path):
         super_resolve(model, torch.zeros(4, 16, 16))
     with pytest.raises(ValueError):
         FusedAdam(model).step(closure=lambda: None)
+
+
+def test_gpu_helper_scripts_parse():
+    """tools/*.sh are the commands handed to gpurun (one call costs GPU minutes even when it dies on a typo): bash -n each."""
+    import glob
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    scripts = sorted(glob.glob(os.path.join(root, "tools", "*.sh")))
+    assert scripts
+    for sh in scripts:
+        res = subprocess.run(["bash", "-n", sh], capture_output=True, text=True)
+        assert res.returncode == 0, (sh, res.stderr)
+    for py in sorted(glob.glob(os.path.join(root, "tools", "*.py"))):
+        compile(open(py).read(), py, "exec")
