@@ -420,3 +420,27 @@ def test_gpu_helper_scripts_parse():
         assert res.returncode == 0, (sh, res.stderr)
     for py in sorted(glob.glob(os.path.join(root, "tools", "*.py"))):
         compile(open(py).read(), py, "exec")
+
+
+def test_dalpha_from_branch_sums_identity():
+    """csrc/gn_bwd.cu (-DMRISR_DALPHA_FUSED) + csrc/head.cu: dalpha_from_channels_kernel forms d(alpha) as
+    s(1-s) * (sum_c sum g*xb - sum_c sum g*xp) from per-channel sums the two blend-kind gn_bwd launches accumulate, where the
+    pixel-shuffle branch is summed over RAW channels 4c+2i+j at low resolution.  Checks that identity (sign, factor, the
+    shuffle re-indexing) against autograd of the reference blend (models/unet_model.py:206-207) in float64."""
+    torch.manual_seed(3)
+    n, c, h, w = 2, 4, 6, 5
+    alpha = torch.tensor(0.37, dtype=torch.float64, requires_grad=True)
+    xb = torch.randn(n, c, 2 * h, 2 * w, dtype=torch.float64)
+    raw = torch.randn(n, 4 * c, h, w, dtype=torch.float64)              # pixel-shuffle branch before the shuffle
+    xp = torch.nn.functional.pixel_shuffle(raw, 2)
+    g = torch.randn(n, c, 2 * h, 2 * w, dtype=torch.float64)
+    s = torch.sigmoid(alpha)
+    ((s * xb + (1 - s) * xp) * g).sum().backward()
+    # what the kernels accumulate: per parameter channel, the bilinear branch at high resolution ...
+    sum_bil = (g * xb).sum(dim=(0, 2, 3))
+    # ... and the shuffle branch per RAW channel at low resolution with g gathered at (2y+i, 2x+j), folded 4 -> 1
+    g_raw = torch.nn.functional.pixel_unshuffle(g, 2)                    # channel 4c + 2i + j  <-  g[c, 2y+i, 2x+j]
+    sum_ps = (g_raw * raw).sum(dim=(0, 2, 3)).reshape(c, 4).sum(dim=1)
+    sv = float(s)
+    want = sv * (1 - sv) * float(sum_bil.sum() - sum_ps.sum())
+    assert abs(want - float(alpha.grad)) <= 1e-12 * max(1.0, abs(float(alpha.grad)))
