@@ -17,6 +17,10 @@ run default_again "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
 for u in 32 64 128; do run gnapply_upt$u "gn_apply:pool0" MRISR_GNAPPLY_UPT=$u; done
 for u in 8 16; do run gnapply_pool_upt$u "gn_apply:pool1" MRISR_GNAPPLY_POOL_UPT=$u; done
 for u in 64 256; do run convfirst_upt$u "conv_first" MRISR_CONVFIRST_UPT=$u; done
+# GroupNorm backward: do the L2-sized alternatives look different now that the step replays as one CUDA graph (no launch gaps)?
+# (eager measurements: profiles/r01_gn_bwd_chunking.md, r01_gn_bwd_fused.md - chunking and clusters > 2 both lost)
+for mb in 48 96; do run gnbwd_chunk${mb} "gn_bwd:kind0" MRISR_GNBWD_FUSED=0 MRISR_GNBWD_CHUNK_MB=$mb; done
+for cs in 4 8; do run gnbwd_cs${cs} "gn_bwd:kind0" MRISR_GNBWD_CS=$cs; done
 # the env-selected staged paths, each only after its parity test passes
 if MRISR_TEST_STAGED=1 timeout 300 python -m pytest tests/test_gpu_knobs.py -q -k staged_ssim > gpurun_out/sweep_ssim_split_test.log 2>&1; then
   run ssim_split "l1_ssim" MRISR_SSIM_SPLIT=1
