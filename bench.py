@@ -231,7 +231,15 @@ def workload_config(mode: str, world: int, per_gpu_batch: int, perceptual: float
                          f"{'training step, ' + loss + ' loss, Adam' if mode == 'train' else 'inference forward'}, "
                          f"batch {per_gpu_batch}/GPU, {H}x{W} input -> {2 * H}x{2 * W} output"),
             "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * world, "input": [H, W],
-            "parallelism": f"dp{world}", "l2": "working set per step (>= 8 GB of activations) >> 126 MB L2; inputs re-read from HBM"}
+            "parallelism": f"dp{world}", "l2": "working set per step (>= 8 GB of activations) >> 126 MB L2; inputs re-read from HBM",
+            **_non_default_build()}
+
+
+def _non_default_build():
+    """A/B runs are self-describing: the staged library variant and every MRISR_* kernel knob set in the environment (none in the
+    driver's runs: the measured default build)."""
+    knobs = {k: v for k, v in sorted(os.environ.items()) if k.startswith("MRISR_") and k != "MRISR_NONE"}
+    return {"knobs": knobs} if knobs else {}
 
 
 # ----------------------------------------------------------------------------------------- our arm
