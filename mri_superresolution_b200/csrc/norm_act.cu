@@ -532,7 +532,9 @@ int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
         static const int rows_env = [] { const char* e = getenv("MRISR_UPSLIDE_ROWS"); return e ? atoi(e) : 0; }();
         const int rows = rows_env > 0 ? rows_env : (dst.H >= 64 ? 16 : 8);
         dim3 grid_s(ceil_div(dst.H, rows), dst.N);
-        upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
+        static const bool pf = [] { const char* e = getenv("MRISR_UPSLIDE_PF"); return e && e[0] == '1'; }();
+        if (pf) upsample2x_slide_kernel<T, 1, NTHR, true><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
+        else upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
         MRISR_LAUNCH_CHECK();
         return 0;
     }

@@ -13,7 +13,28 @@
 
 namespace mrisr {
 
-template <typename T, int UB>
+// 8-channel vector held as loaded (4 registers for bf16): what the prefetch keeps in flight; unpack_raw gives load8's values
+template <typename T> struct RawVec;
+template <> struct RawVec<float> { float4 a, b; };
+template <> struct RawVec<__nv_bfloat16> { uint4 a; };
+__host__ __device__ __forceinline__ void load_raw(const float* p, RawVec<float>& r) {
+    r.a = *reinterpret_cast<const float4*>(p);
+    r.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__host__ __device__ __forceinline__ void load_raw(const __nv_bfloat16* p, RawVec<__nv_bfloat16>& r) { r.a = *reinterpret_cast<const uint4*>(p); }
+__host__ __device__ __forceinline__ void unpack_raw(const RawVec<float>& r, float (&v)[8]) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+}
+__host__ __device__ __forceinline__ void unpack_raw(const RawVec<__nv_bfloat16>& r, float (&v)[8]) {
+    v[0] = bits_to_float(r.a.x << 16); v[1] = bits_to_float(r.a.x & 0xffff0000u);
+    v[2] = bits_to_float(r.a.y << 16); v[3] = bits_to_float(r.a.y & 0xffff0000u);
+    v[4] = bits_to_float(r.a.z << 16); v[5] = bits_to_float(r.a.z & 0xffff0000u);
+    v[6] = bits_to_float(r.a.w << 16); v[7] = bits_to_float(r.a.w & 0xffff0000u);
+}
+
+// PF: the source row the NEXT destination row will need is loaded (raw) before the current row is blended and stored, so its
+// latency overlaps that work instead of stalling the next iteration (16 more registers per column).
+template <typename T, int UB, bool PF = false>
 __host__ __device__ __forceinline__ void upsample2x_slide_body(const Act<T>& src, const Act<T>& dst, float sy, float sx, int rows_pb,
                                                                int n, int block, int tid, int nthr) {
     const RowMap m = row_map(dst, nthr, tid);
@@ -40,12 +61,26 @@ MRISR_UNROLL
         }
         float top[UB][8], bot[UB][8];
         int ti = -1, bi = -1;                                             // source rows held in top / bot
+        RawVec<T> p0[PF ? UB : 1], p1[PF ? UB : 1];                       // PF: raw taps of source row pr, loaded one step ahead
+        int pr = -1;
+        auto fetch_row = [&](int r) {
+MRISR_UNROLL
+            for (int u = 0; u < (PF ? UB : 1); ++u) {
+                load_raw(sp[u] + (int64_t)r * srs, p0[u]);
+                load_raw(sp[u] + (int64_t)r * srs + d1[u], p1[u]);
+            }
+        };
         auto load_row = [&](int r, float (&out)[UB][8]) {
             float v0[UB][8], v1[UB][8];
+            if (PF && r == pr) {
 MRISR_UNROLL
-            for (int u = 0; u < UB; ++u) {
-                load8(sp[u] + (int64_t)r * srs, v0[u]);
-                load8(sp[u] + (int64_t)r * srs + d1[u], v1[u]);
+                for (int u = 0; u < UB; ++u) { unpack_raw(p0[PF ? u : 0], v0[u]); unpack_raw(p1[PF ? u : 0], v1[u]); }
+            } else {
+MRISR_UNROLL
+                for (int u = 0; u < UB; ++u) {
+                    load8(sp[u] + (int64_t)r * srs, v0[u]);
+                    load8(sp[u] + (int64_t)r * srs + d1[u], v1[u]);
+                }
             }
 MRISR_UNROLL
             for (int u = 0; u < UB; ++u) {
@@ -70,6 +105,11 @@ MRISR_UNROLL
                 if (ly.i1 == ti) copy_row(top, bot); else load_row(ly.i1, bot);
                 bi = ly.i1;
             }
+            if (PF && Y + 1 < Y1) {                                       // the row the next step will have to load, if any
+                const Lerp ln = up_coord(Y + 1, src.H, sy);
+                const int want = ln.i0 != ti && ln.i0 != bi ? ln.i0 : (ln.i1 != bi && ln.i1 != ti && ln.i1 != ln.i0 ? ln.i1 : -1);
+                if (want >= 0 && want != pr) { fetch_row(want); pr = want; }
+            }
             const float h1 = ly.w1, h0 = 1.f - h1;
 MRISR_UNROLL
             for (int u = 0; u < UB; ++u) {
@@ -84,9 +124,9 @@ MRISR_UNROLL
 }
 
 #ifdef __CUDACC__
-template <typename T, int UB, int NT>
+template <typename T, int UB, int NT, bool PF = false>
 __global__ void __launch_bounds__(NT) upsample2x_slide_kernel(Act<T> src, Act<T> dst, float sy, float sx, int rows_pb) {
-    upsample2x_slide_body<T, UB>(src, dst, sy, sx, rows_pb, blockIdx.y, blockIdx.x, threadIdx.x, NT);
+    upsample2x_slide_body<T, UB, PF>(src, dst, sy, sx, rows_pb, blockIdx.y, blockIdx.x, threadIdx.x, NT);
 }
 #endif
 

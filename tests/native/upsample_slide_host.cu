@@ -34,7 +34,7 @@ static Act<T> make(std::vector<T>& buf, int N, int H, int W, int C, bool planar,
 
 static int fails = 0;
 
-template <typename T, int UB>
+template <typename T, int UB, bool PF = false>
 static void run(int N, int H, int W, int C, bool src_planar, bool dst_planar, int rows_pb, int nthr) {
     std::vector<T> sb, db, rb;
     Act<T> src = make(sb, N, H, W, C, src_planar, 0.f);
@@ -66,13 +66,13 @@ static void run(int N, int H, int W, int C, bool src_planar, bool dst_planar, in
     const int blocks = (2 * H + rows_pb - 1) / rows_pb;
     for (int n = 0; n < N; ++n)
         for (int b = 0; b < blocks; ++b)
-            for (int tid = 0; tid < nthr; ++tid) upsample2x_slide_body<T, UB>(src, dst, sy, sx, rows_pb, n, b, tid, nthr);
+            for (int tid = 0; tid < nthr; ++tid) upsample2x_slide_body<T, UB, PF>(src, dst, sy, sx, rows_pb, n, b, tid, nthr);
     size_t bad = 0;
     for (size_t i = 0; i < db.size(); ++i) bad += memcmp(&db[i], &rb[i], sizeof(T)) != 0;
     if (bad) {
         ++fails;
         fprintf(stderr, "mismatch: %zu of %zu elements (N=%d H=%d W=%d C=%d src_planar=%d dst_planar=%d rows=%d UB=%d %s)\n", bad,
-                db.size(), N, H, W, C, (int)src_planar, (int)dst_planar, rows_pb, UB, sizeof(T) == 2 ? "bf16" : "fp32");
+                db.size(), N, H, W, C, (int)src_planar, (int)dst_planar, rows_pb, UB * (PF ? -1 : 1), sizeof(T) == 2 ? "bf16" : "fp32");
     }
 }
 
@@ -92,7 +92,15 @@ int main() {
     run<float, 1>(2, 16, 16, 64, false, false, 8, NT);
     run<float, 2>(1, 13, 11, 32, false, false, 16, NT);
     run<float, 1>(1, 1, 1, 8, false, false, 8, NT);
+    // the same with the one-step-ahead prefetch of the next source row
+    run<__nv_bfloat16, 1, true>(2, 32, 32, 32, false, true, 16, NT);
+    run<__nv_bfloat16, 1, true>(2, 64, 64, 32, true, true, 16, NT);
+    run<__nv_bfloat16, 2, true>(1, 40, 24, 16, true, false, 16, NT);
+    run<__nv_bfloat16, 1, true>(1, 7, 5, 8, false, false, 8, NT);
+    run<__nv_bfloat16, 1, true>(3, 1, 9, 24, false, false, 8, NT);
+    run<__nv_bfloat16, 1, true>(1, 9, 1, 16, false, false, 5, NT);
+    run<float, 1, true>(1, 13, 11, 32, false, false, 16, NT);
     if (fails) { fprintf(stderr, "%d configurations differ\n", fails); return 1; }
-    printf("ok 13 configurations\n");
+    printf("ok 20 configurations\n");
     return 0;
 }

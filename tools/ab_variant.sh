@@ -17,5 +17,11 @@ for arm in default $v default2; do
       > gpurun_out/ab_${v}_${arm}_bench.log 2>&1
   echo "$arm: $(cut -c1-160 gpurun_out/ab_${v}_${arm}_bench.log | tail -1)"
 done
+if [ "$v" = ups ] || [ "$v" = all ]; then      # the forward kernel with the next source row prefetched one step ahead
+  MRISR_B200_VARIANT=$v MRISR_UPSLIDE_PF=1 timeout 600 python bench.py --no-cpu-baseline --layer-report gpurun_out/ab_${v}_pf_layers.txt \
+      > gpurun_out/ab_${v}_pf_bench.log 2>&1
+  echo "$v + MRISR_UPSLIDE_PF=1: $(cut -c1-160 gpurun_out/ab_${v}_pf_bench.log | tail -1)"
+  grep -h "upsample2x " gpurun_out/ab_${v}_pf_layers.txt | head -2
+fi
 grep -h "gn_bwd\|upsample\|blend" gpurun_out/ab_${v}_default_layers.txt | head -24
 grep -h "gn_bwd\|upsample\|blend" gpurun_out/ab_${v}_${v}_layers.txt | head -24
