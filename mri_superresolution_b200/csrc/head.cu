@@ -1,6 +1,7 @@
 // Dual-branch head of UNetSuperRes (models/unet_model.py:202-211): blend of the bilinear and the
 // PixelShuffle branch with sigmoid(alpha), and the fused GroupNorm+LeakyReLU -> conv1x1(+bias) ->
 // sigmoid tail; plus d(alpha) and the per-channel column sum used for conv-bias gradients.
+#include <stdlib.h>
 #include "kernels.cuh"
 
 namespace mrisr {
@@ -221,7 +222,11 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ scratch, float*
 template <typename T>
 int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s) {
     ProfScope prof_("head_blend", s);
-    const int rpb = rows_per_block(a.r_ps.W, a.xm.C / 8, NTHR, 2);
+    // 2x2 quads per thread and block (MRISR_HEADBLEND_UPT; 2 in the measured build).  A block first folds both branches'
+    // GroupNorm into 80 per-thread constants (160 scalar loads, 40 integer divisions: load_blend_ctx), which at 2 quads per
+    // thread is about as long as the blend itself (527 instructions per quad); not swept yet.
+    static const int upt = [] { const char* e = getenv("MRISR_HEADBLEND_UPT"); const int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
+    const int rpb = rows_per_block(a.r_ps.W, a.xm.C / 8, NTHR, upt);
     head_blend_kernel<T><<<dim3(ceil_div(a.r_ps.H, rpb), a.xm.N), NTHR, 0, s>>>(a, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;

@@ -12,11 +12,12 @@ run() {   # name, grep pattern, env assignments...
   echo "== $name: ${ms:-FAILED} ms/step"
   grep -h "$pat" gpurun_out/sweep_${name}_layers.txt 2>/dev/null | awk '{printf "   %-44s %s ms\n", $1, $5}' | head -8
 }
-run default "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
-run default_again "gn_apply\|conv_first\|l1_ssim" MRISR_NONE=1
+run default "gn_apply\|conv_first\|l1_ssim\|head_blend" MRISR_NONE=1
+run default_again "gn_apply\|conv_first\|l1_ssim\|head_blend" MRISR_NONE=1
 for u in 32 64 128; do run gnapply_upt$u "gn_apply:pool0" MRISR_GNAPPLY_UPT=$u; done
 for u in 8 16; do run gnapply_pool_upt$u "gn_apply:pool1" MRISR_GNAPPLY_POOL_UPT=$u; done
 for u in 64 256; do run convfirst_upt$u "conv_first" MRISR_CONVFIRST_UPT=$u; done
+for u in 8 32; do run headblend_upt$u "head_blend" MRISR_HEADBLEND_UPT=$u; done
 # GroupNorm backward: do the L2-sized alternatives look different now that the step replays as one CUDA graph (no launch gaps)?
 # (eager measurements: profiles/r01_gn_bwd_chunking.md, r01_gn_bwd_fused.md - chunking and clusters > 2 both lost)
 for mb in 48 96; do run gnbwd_chunk${mb} "gn_bwd:kind0" MRISR_GNBWD_FUSED=0 MRISR_GNBWD_CHUNK_MB=$mb; done
