@@ -98,11 +98,37 @@ def tag_bytes(tag: str, n: int) -> float:
     return 0.0
 
 
-# DRAM bytes per step of a kernel family from the committed ncu capture (profiles/r01_launches_step_v2.md, batch 64 train
-# step): dram__bytes_read.sum + dram__bytes_write.sum summed over the family's launches.  Reported per launch as
-# roofline.traffic when the bench runs the same workload.
-NCU_TRAFFIC_PER_STEP = {"gn_bwd": (13758 + 3462) * 1e6, "gn_apply": (1969 + 1334 + 478 + 433) * 1e6,
-                        "upsample2x_bwd": (1825 + 326) * 1e6, "l1_ssim": (134 + 43) * 1e6}
+def source_hash() -> str:
+    """sha256 over the CUDA sources the library is built from: ties an ncu capture to the build it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "mri_superresolution_b200", "csrc")
+    for name in sorted(os.listdir(csrc)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            h.update(name.encode())
+            h.update(open(os.path.join(csrc, name), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic():
+    """DRAM bytes per step of each kernel family (dram__bytes_read.sum + dram__bytes_write.sum over the family's launches) from
+    the newest committed ncu launch list profiles/rNN_traffic.json (tools/ncu_launch_list.py --json).  Only used when the capture
+    was taken from THIS source tree (source_hash) and workload; otherwise roofline.traffic is null and says why."""
+    prof = os.path.join(ROOT, "profiles")
+    best = None
+    for name in sorted(os.listdir(prof)) if os.path.isdir(prof) else []:
+        if name.endswith("_traffic.json"):
+            best = os.path.join(prof, name)
+    if best is None:
+        return None, "no ncu traffic capture committed"
+    try:
+        d = json.load(open(best))
+    except Exception as exc:
+        return None, f"{os.path.basename(best)} unreadable: {exc}"
+    if d.get("source_hash") != source_hash():
+        return None, (f"{os.path.basename(best)} was captured from source {d.get('source_hash')}, this build is "
+                      f"{source_hash()}: stale, not reported")
+    return d, "profiles/" + os.path.basename(best)
 
 
 def peaks():
@@ -168,9 +194,13 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------- reference / CPU arm
+CPU_BATCH = 4                   # BASELINE.json configs[0]: the reference's own CPU-runnable case is batch 4
+
+
 def cpu_oracle_run(mode: str, steps: int, warmup: int, budget_s: float):
     """Times the oracle (reference algorithm, plain PyTorch fp32, all host threads) on a bounded sample of the
-    workload: per step one batch of `b` slices of 256x256, b chosen so the whole run fits `budget_s`."""
+    workload: per step one batch of `b` slices of 256x256; b = 4 (BASELINE.json configs[0]: "batch 4, L1+SSIM, fp32 on CPU via
+    the scripts/train.py path"), reduced only if the whole run would not fit `budget_s`."""
     import torch
     from oracle import unet_oracle as UO
     from oracle.synth import make_pairs
@@ -192,7 +222,7 @@ def cpu_oracle_run(mode: str, steps: int, warmup: int, budget_s: float):
     one(1, SEED)                                    # page-in / thread-pool warm-up, not counted
     t1 = one(1, SEED + 1)
     total = max(1, steps + warmup)
-    b = int(max(1, min(8, (budget_s / total) / max(t1, 1e-3))))
+    b = int(max(1, min(CPU_BATCH, (budget_s / total) / max(t1, 1e-3))))
     for i in range(warmup):
         one(b, SEED + 10 + i)
     dt = 0.0
@@ -209,13 +239,18 @@ def run_reference(args):
     mode = args.mode
     r = cpu_oracle_run(mode, args.steps, args.warmup, budget_s=150.0)
     unit = "slices/s"
-    sample = (f"{r['batch']} slices of {H}x{W} per step x {args.steps} steps, oracle ({'train step' if mode == 'train' else 'forward'}"
+    sample = (f"batch {r['batch']} slices of {H}x{W} per step x {args.steps} steps (BASELINE.json configs[0] batch size, the "
+              f"bounded sample of the batch-{args.batch} workload), oracle ({'train step' if mode == 'train' else 'forward'}"
               f", fp32, torch CPU, {r['threads']} threads)")
+    cfg = workload_config(mode, max(1, args.gpus), args.batch)
+    cfg["reference_arm_batch_per_step"] = r["batch"]
+    cfg["reference_arm_note"] = (f"the CPU arm runs batch {r['batch']} per step (configs[0] as written), not batch {args.batch}: "
+                                 "slices/s is per-slice throughput, batch-size independent on the host within a few %")
     line = {
         "impl": "reference", "metric": METRIC if mode == "train" else INFER_METRIC, "value": r["value"], "unit": unit,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": workload_config(mode, max(1, args.gpus), args.batch),
+        "config": cfg,
         "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["threads"], "kind": "port", "sample": sample},
         "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -240,6 +275,134 @@ def _non_default_build():
     driver's runs: the measured default build)."""
     knobs = {k: v for k, v in sorted(os.environ.items()) if k.startswith("MRISR_") and k != "MRISR_NONE"}
     return {"knobs": knobs} if knobs else {}
+
+
+# ----------------------------------------------------------------------------------------- GPU eager baseline
+def gpu_eager_run(dev, mode: str, nb: int, steps: int, warmup: int, amp: bool):
+    """The reference algorithm in PyTorch eager on the SAME GPU (cuDNN / ATen kernels, one per op): oracle/ = the reference
+    modules restated, fp32 with TF32 off, or under autocast(bf16) as scripts/train.py:304-311 runs with --use_amp.  This is the
+    bar SURVEY.md names for a repository that ships no kernels of its own; a reported baseline, like cpu_baseline."""
+    import torch
+    from oracle import losses_oracle as LO
+    from oracle import unet_oracle as UO
+    from oracle.synth import make_pairs
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        params = {k: v.to(dev).requires_grad_(mode == "train") for k, v in UO.init_params(BASE_FILTERS, seed=SEED).items()}
+        opt = torch.optim.Adam(list(params.values()), lr=LR, weight_decay=WD) if mode == "train" else None
+        x, t = [v.to(dev) for v in make_pairs(nb, H, W, seed=SEED)]
+
+        def one():
+            if mode == "train":
+                opt.zero_grad(set_to_none=True)
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                    out = UO.unet_forward(params, x)
+                    loss = LO.combined_loss(out, t, ssim_weight=SSIM_WEIGHT)
+                loss.backward()
+                opt.step()
+            else:
+                with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                    torch.clamp(UO.unet_forward(params, x), 0, 1)
+
+        for _ in range(warmup):
+            one()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            one()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / steps
+        peak_gb = torch.cuda.max_memory_allocated(dev) / 2 ** 30
+        return {"value": nb / (ms * 1e-3), "unit": "slices/s", "ms_per_step": ms, "batch": nb, "steps": steps,
+                "peak_memory_gib": round(peak_gb, 1)}
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+        del params
+        torch.cuda.empty_cache()
+
+
+# ----------------------------------------------------------------------------------------- per-kernel attribution
+def attribute(rep, prof_steps: int, nb: int, mode: str, ms_step: float):
+    """Per-family table and roofline records from the live CUDA-event attribution (`rep` = [(tag, calls, total_ms)]).
+
+    roofline            : the dominant family of the step (the contract's record)
+    rooflines.loss_kernel : fused L1 + SSIM loss-and-gradient kernel against HBM (north_star: >= 70 %)
+    rooflines.conv_layers : every convolution / weight-gradient family together against the sustained bf16 peak (north_star:
+                            >= 60 %), algorithmic FLOPs = 2 Cin Cout k^2 H W per launch
+    traffic             : DRAM bytes per launch from the committed ncu capture of THIS source tree, else null."""
+    pk = peaks()
+    traffic_db, traffic_src = ncu_traffic()
+    fam = {}
+    for tag, calls, tms in rep:
+        name = tag.split(":")[0]
+        f = fam.setdefault(name, {"ms": 0.0, "calls": 0, "flops": 0.0, "bytes": 0.0})
+        f["ms"] += tms / prof_steps
+        f["calls"] += calls // prof_steps
+        f["flops"] += tag_flops(tag, nb) * calls / prof_steps
+        f["bytes"] += tag_bytes(tag, nb) * calls / prof_steps
+    if "l1_ssim" in fam:
+        # fp32 pred + fp32 target read, fp32 gradient written (SURVEY.md 8(d) fp32 mode: 12 B per HR pixel); forward-only: 8 B
+        fam["l1_ssim"]["bytes"] = (12.0 if mode == "train" else 8.0) * nb * (2 * H) * (2 * W) * fam["l1_ssim"]["calls"]
+    total_ms = sum(f["ms"] for f in fam.values()) or 1.0
+    families = []
+    for name, f in sorted(fam.items(), key=lambda kv: -kv[1]["ms"]):
+        families.append({"kernel": name, "ms_per_step": round(f["ms"], 4), "launches_per_step": f["calls"],
+                         "share": round(f["ms"] / total_ms, 4),
+                         "tflops": round(f["flops"] / (f["ms"] * 1e-3) / 1e12, 2) if f["flops"] else None,
+                         "gbs": round(f["bytes"] / (f["ms"] * 1e-3) / 1e9, 1) if f["bytes"] and not f["flops"] else None})
+
+    def traffic_of(name, calls):
+        if traffic_db is None:
+            return None, traffic_src
+        if traffic_db.get("workload") != f"{mode}:{nb}x{H}x{W}":
+            return None, f"{traffic_src} is a capture of {traffic_db.get('workload')}, not of this workload"
+        v = traffic_db.get("families", {}).get(name)
+        return (v / max(calls, 1), traffic_src) if v is not None else (None, f"{name} not in {traffic_src}")
+
+    def record(name):
+        f = fam[name]
+        share = round(f["ms"] / total_ms, 4)
+        base = {"kernel": name, "ms_per_step": round(f["ms"], 4), "launches_per_step": f["calls"], "share_of_step": share}
+        tr, tr_src = traffic_of(name, f["calls"])
+        if f["flops"] > 0:
+            ach = f["flops"] / (f["ms"] * 1e-3) / 1e12
+            return {**base, "bound": "tensor", "achieved": round(ach, 2), "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                    "frac": round(ach / pk["bf16_tflops_sustained"], 4), "traffic": tr, "traffic_source": tr_src,
+                    "peak_source": pk["source"] + " (sustained bf16: kernel timed inside a long step)",
+                    "flops_per_launch": f["flops"] / max(f["calls"], 1)}
+        if f["bytes"] > 0:
+            ach = f["bytes"] / (f["ms"] * 1e-3) / 1e9
+            return {**base, "bound": "hbm", "achieved": round(ach, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                    "frac": round(ach / pk["hbm_gbs"], 4), "traffic": tr, "traffic_source": tr_src, "peak_source": pk["source"],
+                    "bytes_per_launch": f["bytes"] / max(f["calls"], 1),
+                    "note": "algorithmic bytes = minimum passes x tensor size (DESIGN.md 4)"}
+        return {**base, "bound": "hbm", "achieved": None, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": tr,
+                "traffic_source": tr_src, "note": "helper kernel without an algorithmic-byte model; its time counts against the step"}
+
+    roofline = record(families[0]["kernel"])
+    rooflines = {}
+    if "l1_ssim" in fam:
+        rooflines["loss_kernel"] = record("l1_ssim")
+    conv = [(k, v) for k, v in fam.items() if v["flops"] > 0]
+    if conv:
+        fl, t = sum(v["flops"] for _, v in conv), sum(v["ms"] for _, v in conv)
+        ach = fl / (t * 1e-3) / 1e12
+        rooflines["conv_layers"] = {
+            "kernels": sorted(k for k, _ in conv), "bound": "tensor", "achieved": round(ach, 2),
+            "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": round(ach / pk["bf16_tflops_sustained"], 4),
+            "ms_per_step": round(t, 4), "share_of_step": round(t / total_ms, 4), "flops_per_step": fl,
+            "per_family": {k: {"tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1), "ms": round(v["ms"], 4),
+                               "frac": round(v["flops"] / (v["ms"] * 1e-3) / 1e12 / pk["bf16_tflops_sustained"], 4)}
+                           for k, v in sorted(conv, key=lambda kv: -kv[1]["ms"])}}
+    flops_step = unet_flops_per_slice(BASE_FILTERS, H, W, mode == "train") * nb
+    whole = {"unet_conv_tflops": round(flops_step / (ms_step * 1e-3) / 1e12, 2),
+             "frac_of_bf16_sustained": round(flops_step / (ms_step * 1e-3) / 1e12 / pk["bf16_tflops_sustained"], 4),
+             "attributed_ms": round(total_ms, 4)}
+    return families, roofline, rooflines, whole
 
 
 # ----------------------------------------------------------------------------------------- our arm
@@ -323,19 +486,20 @@ def run_ours(args):
     step(x_dev, t_dev)
     launches_per_step = _native.launch_count() - l0
     graphed = None
+    graphed_obj = None
     graph_note = None
     try:
         if mode == "train" and not args.no_graph:
             from mri_superresolution_b200.utils.graph import GraphedTrainStep
-            graphed = GraphedTrainStep(model, crit, opt, x_dev, t_dev, buckets=buckets)
+            graphed = graphed_obj = GraphedTrainStep(model, crit, opt, x_dev, t_dev, buckets=buckets)
         elif mode == "infer" and not args.no_graph:
             from mri_superresolution_b200.utils.graph import GraphedForward
-            gfwd = GraphedForward(model, x_dev)
+            graphed_obj = gfwd = GraphedForward(model, x_dev)
             graphed = lambda x, t: gfwd(x)                               # noqa: E731
     except Exception as exc:             # same kernels either way: a failed capture only changes how they are launched
         if world > 1:
             raise                        # ranks must not diverge (one replaying, one launching eagerly would still match, but say so loudly)
-        graphed, graph_note = None, f"graph capture failed, eager launches: {type(exc).__name__}: {exc}"
+        graphed, graphed_obj, graph_note = None, None, f"graph capture failed, eager launches: {type(exc).__name__}: {exc}"
         print("bench.py: " + graph_note, file=sys.stderr, flush=True)
         torch.cuda.synchronize()
     run_step = (lambda x, t: graphed(x, t)) if graphed is not None else step
@@ -356,6 +520,7 @@ def run_ours(args):
     # i+1 runs on a side stream while step i computes; utils/prefetch.py), as a training loop built on this package would.
     from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
     d2h = [0]
+    out_pin = [None]
     e2e_steps = max(2, min(args.steps, 10))
 
     def host_batches():
@@ -373,8 +538,11 @@ def run_ours(args):
             r.item()                                 # scripts/train.py:321 reads the loss every step
             d2h[0] = 4
         else:
-            r[:1].cpu()                              # first super-resolved slice back to the host
-            d2h[0] = r[:1].numel() * 4
+            if out_pin[0] is None:
+                out_pin[0] = torch.empty(r.shape, dtype=r.dtype).pin_memory()
+            out_pin[0].copy_(r, non_blocking=True)   # the step's result is the whole super-resolved batch
+            torch.cuda.current_stream().synchronize()
+            d2h[0] = r.numel() * r.element_size()
 
     e2e_step()
     bytes0 = feeder.bytes_copied
@@ -383,7 +551,7 @@ def run_ours(args):
     h2d = (feeder.bytes_copied - bytes0) // e2e_steps          # counted from the tensors copied inside the timed region
 
     # ---- per-kernel attribution (same workload, CUDA events on the launching stream) ---------
-    roofline, families = None, []
+    roofline, rooflines, families, whole = None, None, [], None
     prof_steps = 2
     barrier()
     if rank == 0:
@@ -392,7 +560,6 @@ def run_ours(args):
         step(x_dev, t_dev)
     barrier()
     if rank == 0:
-        pk = peaks()
         rep = _native.profile_report()
         _native.profile(False)
         if args.layer_report:
@@ -402,72 +569,64 @@ def run_ours(args):
                     ms_t = tms / prof_steps
                     fh.write("%-44s calls/step %3d  ms/step %8.4f  TFLOP/s %s\n" % (
                         tag, calls // prof_steps, ms_t, ("%.1f" % (fl / (ms_t * 1e-3) / 1e12)) if fl else "-"))
-        fam = {}
-        for tag, calls, tms in rep:
-            name = tag.split(":")[0]
-            f = fam.setdefault(name, {"ms": 0.0, "calls": 0, "flops": 0.0, "bytes": 0.0})
-            f["ms"] += tms / prof_steps
-            f["calls"] += calls // prof_steps
-            f["flops"] += tag_flops(tag, nb) * calls / prof_steps
-            f["bytes"] += tag_bytes(tag, nb) * calls / prof_steps
-        total_ms = sum(f["ms"] for f in fam.values()) or 1.0
-        for name, f in sorted(fam.items(), key=lambda kv: -kv[1]["ms"]):
-            families.append({"kernel": name, "ms_per_step": round(f["ms"], 4), "launches_per_step": f["calls"],
-                             "share": round(f["ms"] / total_ms, 4),
-                             "tflops": round(f["flops"] / (f["ms"] * 1e-3) / 1e12, 2) if f["flops"] else None})
-        top = families[0]
-        tf = fam[top["kernel"]]
-        if tf["flops"] > 0:
-            achieved = tf["flops"] / (tf["ms"] * 1e-3) / 1e12
-            peak = pk["bf16_tflops_sustained"]
-            roofline = {"kernel": top["kernel"], "bound": "tensor", "achieved": round(achieved, 2), "peak": peak,
-                        "unit": "TFLOP/s", "frac": round(achieved / peak, 4), "traffic": None,
-                        "peak_source": pk["source"] + " (sustained bf16: kernel timed inside a long step)",
-                        "flops_per_step": tf["flops"], "ms_per_step": round(tf["ms"], 4),
-                        "launches_per_step": tf["calls"], "share_of_step": top["share"]}
-        elif top["kernel"] in ("l1_ssim",):
-            nbytes = 12.0 * nb * (2 * H) * (2 * W)   # fp32 pred + target read, fp32 grad written
-            achieved = nbytes / (tf["ms"] * 1e-3) / 1e9
-            roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
-                        "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": None,
-                        "peak_source": pk["source"], "share_of_step": top["share"]}
-        elif tf["bytes"] > 0:
-            achieved = tf["bytes"] / (tf["ms"] * 1e-3) / 1e9
-            roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
-                        "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4),
-                        "traffic": (NCU_TRAFFIC_PER_STEP[top["kernel"]] / max(tf["calls"], 1)
-                                    if top["kernel"] in NCU_TRAFFIC_PER_STEP and nb == PER_GPU_BATCH and mode == "train" else None),
-                        "traffic_source": "profiles/r01_launches_step_v2.md (ncu dram bytes of the family / launches)",
-                        "peak_source": pk["source"], "bytes_per_step": tf["bytes"],
-                        "bytes_per_launch": tf["bytes"] / max(tf["calls"], 1), "ms_per_step": round(tf["ms"], 4),
-                        "launches_per_step": tf["calls"], "share_of_step": top["share"],
-                        "note": "elementwise kernel family; algorithmic bytes = minimum passes x bf16 tensor size (DESIGN.md 4)"}
-        else:
-            roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": None, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                        "frac": None, "traffic": None, "share_of_step": top["share"],
-                        "note": "elementwise helper kernel dominates; its bytes count against the conv roofline"}
-        conv_fams = [(k, v) for k, v in fam.items() if v["flops"] > 0]
-        conv_roofline = None
-        if conv_fams:
-            k, v = max(conv_fams, key=lambda kv: kv[1]["ms"])
-            ach = v["flops"] / (v["ms"] * 1e-3) / 1e12
-            conv_roofline = {"kernel": k, "bound": "tensor", "achieved": round(ach, 2), "peak": pk["bf16_tflops_sustained"],
-                             "unit": "TFLOP/s", "frac": round(ach / pk["bf16_tflops_sustained"], 4),
-                             "ms_per_step": round(v["ms"], 4), "launches_per_step": v["calls"]}
-        flops_step = unet_flops_per_slice(BASE_FILTERS, H, W, mode == "train") * nb
-        whole = {"unet_conv_tflops": round(flops_step / (ms / args.steps * 1e-3) / 1e12, 2),
-                 "frac_of_bf16_sustained": round(flops_step / (ms / args.steps * 1e-3) / 1e12 / pk["bf16_tflops_sustained"], 4),
-                 "top_conv_kernel": conv_roofline}
-    else:
-        whole = None
+        families, roofline, rooflines, whole = attribute(rep, prof_steps, nb, mode, ms / args.steps)
+
+    # ---- the metric is "train & infer": the inference forward of the same model / batch, inside the same line --------------
+    infer = None
+    if mode == "train" and not args.no_infer:
+        from mri_superresolution_b200.utils.graph import GraphedForward
+        model.eval()
+        gf = GraphedForward(model, x_dev)
+        l0 = _native.launch_count()
+        with torch.no_grad():
+            model(x_dev)
+        infer_launches = _native.launch_count() - l0
+        for _ in range(3):
+            gf(x_dev)
+        ms_i = timed(lambda: gf(x_dev), args.steps)
+        feeder_i = DevicePrefetcher(((x_pin,) for _ in iter(int, 1)), dev)
+        y_pin = torch.empty((nb, 1, 2 * H, 2 * W), dtype=torch.float32).pin_memory()
+
+        def infer_e2e():
+            (xb,) = next(feeder_i)
+            y_pin.copy_(gf(xb), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        infer_e2e()
+        b0 = feeder_i.bytes_copied
+        ms_ie = timed(infer_e2e, e2e_steps)
+        infer = {"metric": INFER_METRIC, "value": nb * world * args.steps / (ms_i * 1e-3), "unit": "slices/s",
+                 "ms_per_step": ms_i / args.steps, "steps": args.steps, "gpu_launches": infer_launches * args.steps,
+                 "e2e": {"value": nb * world * e2e_steps / (ms_ie * 1e-3), "unit": "slices/s",
+                         "h2d_bytes_per_step": (feeder_i.bytes_copied - b0) // e2e_steps,
+                         "d2h_bytes_per_step": y_pin.numel() * 4, "ms_per_step": ms_ie / e2e_steps,
+                         "pipeline": "pinned host batch -> DevicePrefetcher -> GraphedForward -> whole output batch copied to "
+                                     "pinned host memory every step"},
+                 "workload": f"inference forward (scripts/infer.py:268-276) of the same model, batch {nb}/GPU, {H}x{W} -> {2 * H}x{2 * W}",
+                 "unet_conv_tflops": round(unet_flops_per_slice(BASE_FILTERS, H, W, False) * nb / (ms_i / args.steps * 1e-3) / 1e12, 2)}
+        gf.close()
+        del gf, feeder_i
+        model.train()
+
+    # ---- the reference algorithm in PyTorch eager on the same GPU (rank 0, N = 1 only) ------------------------------------
+    eager = None
+    if rank == 0 and world == 1 and not args.no_eager_baseline:
+        eager = {"what": "oracle/ (= the reference modules' algorithm) in PyTorch eager on this GPU: cuDNN/ATen kernels, one per "
+                         "op, same batch; a reported baseline (SURVEY.md: the reference ships no kernels of its own)"}
+        for key, amp in (("fp32_tf32_off", False), ("autocast_bf16", True)):
+            try:
+                eager[key] = gpu_eager_run(dev, mode, nb, steps=5, warmup=3, amp=amp)
+            except Exception as exc:                      # e.g. out of memory beside the resident workspaces
+                eager[key] = {"unavailable": f"{type(exc).__name__}: {str(exc)[:200]}"}
+                torch.cuda.empty_cache()
 
     # ---- CPU baseline (rank 0, N = 1 only) ----------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_oracle_run(mode, steps=3, warmup=1, budget_s=25.0)
+        r = cpu_oracle_run(mode, steps=4, warmup=1, budget_s=25.0)
         cpu = {"value": r["value"], "unit": "slices/s", "cores": r["threads"], "kind": "port",
-               "sample": f"{r['batch']} slices of {H}x{W} per step x 3 steps of the oracle "
-                         f"({'train step' if mode == 'train' else 'forward'}, fp32, torch CPU)"}
+               "sample": f"batch {r['batch']} slices of {H}x{W} per step x 4 steps of the oracle "
+                         f"({'train step' if mode == 'train' else 'forward'}, fp32, torch CPU; BASELINE.json configs[0] batch size)"}
 
     if rank == 0:
         line = {
@@ -481,12 +640,31 @@ def run_ours(args):
                                 "-> " + (("GraphedTrainStep" if mode == "train" else "GraphedForward") + " (whole step replayed as one CUDA graph)" if graphed is not None else "public modules (eager launches)")
                                 + " -> result read back every step"},
             "gpu_launches": launches, "launch_mode": ("cuda graph replay of the eagerly counted step" if graphed is not None else (graph_note or "eager")),
-            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "clocks": clocks, "roofline": roofline, "rooflines": rooflines, "cpu_baseline": cpu,
+            "infer": infer, "gpu_eager_baseline": eager,
             "kernels": families, "whole_step": whole,
         }
         print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    # Teardown order matters under data parallelism: the recorded step holds captured NCCL all-reduces, and NCCL's communicator
+    # teardown waits for every graph that references it.  Destroy the graph, the prefetcher and the buckets first; the JSON line
+    # is already out, so a watchdog ends the process if the communicator still refuses to go (round 1: rc 124 at N = 2).
+    if hasattr(graphed_obj, "close"):
+        graphed_obj.close()
+    del graphed, graphed_obj, run_step, feeder
+    if buckets is not None:
+        buckets.close()
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+        watchdog = threading.Timer(20.0, lambda: os._exit(0))
+        watchdog.daemon = True
+        watchdog.start()
         dist.destroy_process_group()
+        watchdog.cancel()
 
 
 def main():
@@ -499,6 +677,8 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="slices per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-infer", action="store_true", help="skip the inference sub-record of a training run")
+    ap.add_argument("--no-eager-baseline", action="store_true", help="skip the PyTorch-eager-on-GPU baseline leg")
     ap.add_argument("--no-graph", action="store_true", help="end-to-end leg with eager launches instead of the CUDA graph")
     ap.add_argument("--perceptual", type=float, default=0.0,
                     help="weight of the VGG19[:36] perceptual term (BASELINE.json configs[2] uses 0.1); 0 = configs[1]")

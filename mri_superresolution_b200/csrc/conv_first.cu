@@ -14,17 +14,9 @@ namespace {
 using bf16 = __nv_bfloat16;
 constexpr int NTHR = 256;
 constexpr int kUnitsBwd = 64;
-// output vectors per thread and block of conv_first_kernel: 16 in the measured build.  A block pays a fixed price around its
-// rows (72 scalar weight loads, a serial shared-memory reduction of the GroupNorm statistics, two barriers) that is comparable
-// to 16 vectors of work; MRISR_CONVFIRST_UPT (>= 16, so the statistics scratch sized for 16 still fits) lengthens the blocks.
-inline int units_fwd() {
-    static const int v = [] {
-        const char* e = getenv("MRISR_CONVFIRST_UPT");
-        const int u = e ? atoi(e) : 16;
-        return u < 16 ? 16 : (u > 4096 ? 4096 : u);
-    }();
-    return v;
-}
+// output vectors per thread and block of conv_first_kernel.  Swept on B200 in round 2 (64, 256 vectors): 0.199 -> 0.206, 0.217 ms,
+// the fixed per-block price (72 scalar weight loads, the statistics reduction) is not what bounds it.
+inline int units_fwd() { return 16; }
 
 // x: [N][H+2][W+2][1] (zero border), w: packed [tap][1][Cout] bf16, dst planar-8 [Cout]
 __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf16* __restrict__ w, Act<bf16> dst,

@@ -498,8 +498,7 @@ static int launch_wres(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUt
 template <int BN, int BK>
 static int wres_stages(const ConvTcParams& p, int grid) {
     using Cfg = ConvTcCfg<BN, BK, true>;
-    static const bool enabled = [] { const char* e = getenv("MRISR_CONV_TC_WRES"); return !(e && e[0] == '0'); }();
-    if (!enabled || p.n_blocks != 1 || p.num_tiles < 4 * grid) return 0;      // the one-off weight fetch must amortise
+    if (p.n_blocks != 1 || p.num_tiles < 4 * grid) return 0;      // the one-off weight fetch must amortise
     // measured (profiles/r01_conv_tc_epilogue.md): a gain where the weight tiles dominate a stage (Cout = 128: 3 x 16 KB beside
     // a 17 KB activation tile; 32-channel chunks), a loss for Cout <= 64 with 64-channel chunks (64>64, 128>64, 64>32)
     if (!(BN >= 128 || BK == 32)) return 0;
@@ -597,11 +596,8 @@ int launch_conv_tc(const ConvArgs<bf16>& a, cudaStream_t s) {
     const int64_t rows = (int64_t)N * (H + 2) * (W + 2);
     const int taps = a.ks * a.ks;
     const int BNsel = Cout > 256 ? 256 : Cout;
-    // 32-channel chunks use the 64-byte swizzle: the same row-shifted descriptor start works (MRISR_CONV_TC_MERGE3_BK32=0 disables)
-    static const bool bk32_ok = [] { const char* e = getenv("MRISR_CONV_TC_MERGE3_BK32"); return !(e && e[0] == '0'); }();
-    // 16-channel chunks (32-byte swizzle, the NHWC fallback of the 2x head at wide images): same trick, MRISR_CONV_TC_MERGE3_BK16=0 disables
-    static const bool bk16_ok = [] { const char* e = getenv("MRISR_CONV_TC_MERGE3_BK16"); return !(e && e[0] == '0'); }();
-    const bool merge3 = conv_tc_merge3_enabled() && taps == 9 && (bk == 64 || (bk == 32 && bk32_ok) || (bk == 16 && bk16_ok)) && BNsel <= 128;
+    // 32- / 16-channel chunks use the 64- / 32-byte swizzle: the same row-shifted descriptor start works
+    const bool merge3 = conv_tc_merge3_enabled() && taps == 9 && BNsel <= 128;
     const uint32_t a_rows = merge3 ? 130u : 128u;
     CUtensorMap tA1, tA2, tB;
     int rc = tc::make_tmap_2d_bf16(&tA1, a.src1.p, (uint64_t)rows, (uint64_t)C1, a_rows, (uint32_t)bk);

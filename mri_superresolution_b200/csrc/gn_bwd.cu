@@ -18,32 +18,14 @@ constexpr int NTHR = 256;
 constexpr int UNITS_PER_THREAD = 32;
 constexpr int FTHR = 256;         // threads of the finalize kernel
 
-// Optional chunking of the batch (MRISR_GNBWD_CHUNK_MB > 0): reduce + apply run per chunk of samples whose (r, g, dr) fit
-// the given size, hoping for L2 hits in the apply pass.  Measured on B200 (batch 64, profiles/r01_gn_bwd_chunking.md): every
-// chunk size was SLOWER than one pass over the whole batch (launch gaps and tails of the short kernels outweigh the saved
-// HBM reads), so the default is off; the knob stays for experiments.
-inline double gn_bwd_chunk_bytes() {
-    static double v = -1.0;
-    if (v < 0.0) {
-        const char* e = getenv("MRISR_GNBWD_CHUNK_MB");
-        v = e ? atof(e) * 1048576.0 : 0.0;
-        if (v <= 0.0) v = 1e15;
-    }
-    return v;
-}
-
 template <int KIND> struct KindTraits { static constexpr bool pool = (KIND == SRC_DIRECT_POOL || KIND == SRC_POOL_ONLY); };
 
-// Builds with -DMRISR_DALPHA_FUSED: the blend kinds also accumulate  sum g * lrelu(z)  per channel (third partial-sum row, as
-// SRC_OUTER does for the 1x1 weights) and the finalize kernel writes the per-parameter-channel totals to `dwvec`; the caller
-// (unet_run.cu) forms d(alpha) = s(1-s) * (sum over the bilinear branch - sum over the pixel-shuffle branch) from the two
-// vectors instead of launching blend_dalpha_kernel, which re-reads both branches and the gradient (0.37 ms of the 17.7 ms
-// step) for one scalar.  Staged, not measured yet.
-#ifdef MRISR_DALPHA_FUSED
+// The blend kinds also accumulate  sum g * lrelu(z)  per channel (third partial-sum row, as SRC_OUTER does for the 1x1
+// weights) and the finalize kernel writes the per-parameter-channel totals to `dwvec`; the caller (unet_run.cu) forms
+// d(alpha) = s(1-s) * (sum over the bilinear branch - sum over the pixel-shuffle branch) from the two vectors.  Measured on
+// B200 (round 2, profiles/r02_staged_variants.md): the separate blend_dalpha pass it replaces cost 0.363 ms of the 17.6 ms
+// step (it re-read both branches and the gradient for one scalar); the extra sums cost 0.03 ms in the two blend launches.
 constexpr bool kDalpha = true;
-#else
-constexpr bool kDalpha = false;
-#endif
 template <int KIND> struct ThirdRow {
     static constexpr bool blend = kDalpha && (KIND == SRC_BLEND_BIL || KIND == SRC_BLEND_PS);
     static constexpr bool on = KIND == SRC_OUTER || blend;
@@ -97,13 +79,9 @@ __device__ __forceinline__ void unit_grads(const GnBwdArgs<T>& a, const ChanCtx&
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const int ch = cv * 8 + k, cs = ch >> 2, i = (ch >> 1) & 1, j = ch & 1;
-#ifdef MRISR_DALPHA_FUSED
                 const float graw = to_f(*a.g.at(n, 2 * y + i, 2 * x + j, cs));
                 act_out[k] = graw * lrelu(z[q][k]);
                 dA[k] = om * graw;
-#else
-                dA[k] = om * to_f(*a.g.at(n, 2 * y + i, 2 * x + j, cs));
-#endif
             }
         } else if (KIND == SRC_OUTER) {
             const int64_t pi = ((int64_t)n * a.r.H + y) * a.r.W + x;
@@ -346,8 +324,8 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
 // Measured on B200 (batch 64, profiles/r01_gn_bwd_fused.md): clusters of 2 are fastest (gn_bwd 6.8 -> 5.0 ms per step); larger
 // clusters lose more to gang scheduling than their bigger shared-memory share of a unit wins back, and with 2 CTAs the
 // operands kept in shared memory between the phases (K slots) are a few percent of a unit, so the second phase still
-// re-reads most operands (5 passes, now at ~70% of the HBM copy rate instead of 45%).  MRISR_GNBWD_CS / _FT / _SMEM_KB / _D / _K
-// reproduce the sweep.
+// re-reads most operands (5 passes, now at ~70% of the HBM copy rate instead of 45%).  MRISR_GNBWD_CS
+// reproduces the cluster-size sweep.
 constexpr int kFtMax = 512;             // threads per CTA of the fused kernel: 512 (2 CTAs / SM) or 256 (4 CTAs / SM)
 constexpr int kMaxUnitCh = 512;         // channels of one unit
 
@@ -388,16 +366,11 @@ __device__ __forceinline__ void grads_from_raw(const ChanCtx& c, const Raw<P, Ki
             const uint32_t t[4] = {w.a[q].x, w.a[q].y, w.a[q].z, w.a[q].w};
 #pragma unroll
             for (int ij = 0; ij < 4; ++ij) {
-#ifdef MRISR_DALPHA_FUSED
                 const float g0 = __uint_as_float(t[ij] << 16), g1 = __uint_as_float(t[ij] & 0xffff0000u);
                 act_out[ij] = g0 * lrelu(z[q][ij]);
                 act_out[4 + ij] = g1 * lrelu(z[q][4 + ij]);
                 dA[ij] = al * g0;
                 dA[4 + ij] = al * g1;
-#else
-                dA[ij] = al * __uint_as_float(t[ij] << 16);
-                dA[4 + ij] = al * __uint_as_float(t[ij] & 0xffff0000u);
-#endif
             }
         } else if (KIND == SRC_OUTER) {
             const float yy = __uint_as_float(w.a[q].x);
@@ -445,30 +418,22 @@ struct FusedParams {
     int slots;         // shared-memory slots per thread (K, or K + S)
     int K;             // units per thread kept in shared memory between the phases (plus S streaming slots)
     double inv_count;
-    // ceil(2^40 / UW), used only by builds with -DMRISR_GNBWD_FASTDIV: unit index -> (row, column) by multiply-shift instead of
-    // an integer division (exact for indices < 2^24 and UW >= 8, tests/test_host_logic.py).  ncu of the kind-0 kernel:
-    // stall_not_selected 31 %, math 15 %, long scoreboard 3 %, ~417 thread instructions per 16-byte unit, i.e. issue-bound,
-    // and the two divisions per unit per pass are ~18 % of that stream (profiles/r01_gn_bwd_issue_bound.md).  Staged, not
-    // measured yet: build with `make EXTRA=-DMRISR_GNBWD_FASTDIV` to A/B it.
-    unsigned long long uw_magic;
-    // Builds with -DMRISR_GNBWD_INCR: operand addresses by constant steps (gn_bwd_trk.h) instead of a division and 64-bit
-    // index arithmetic per unit (~100 of the 203 SASS instructions of the kind-0 phase-1 loop).  Staged, not measured yet.
+    // Incremental form (the plain-tensor kinds, kIncr below): operand addresses by constant steps (gn_bwd_trk.h) instead of a
+    // division and 64-bit index arithmetic per unit (~100 of the 203 SASS instructions of the kind-0 phase-1 loop; the kernel
+    // was issue-bound at 417 thread instructions per 16-byte unit, profiles/r01_gn_bwd_issue_bound.md).
     TrkStep ts;
     int psr, psg, psd, psh;      // pixel strides (elements) of r, g, dr, gpool
 };
 
-#ifdef MRISR_GNBWD_INCR
-constexpr bool kIncr = true;
-#else
-constexpr bool kIncr = false;
-#endif
+// Which kinds use the incremental addressing: measured per kind on B200 (round 2, batch 64 train step, ms per step summed over
+// the launches of the kind, division form -> incremental form): plain tensor 2.39 -> 1.90, + max-pool routing 0.748 -> 0.746,
+// final-head outer product 0.639 -> 0.710, blend 0.571 -> 0.490 and pixel-shuffle 0.706 -> 0.625 -- but the last two lose
+// 0.39 ms once they also carry the d(alpha) sums (register pressure at 64 registers per thread), which is more than the
+// 0.16 ms the incremental form wins there and more than the blend_dalpha pass the sums replace, so they keep the division form.
+template <int KIND> struct Incr { static constexpr bool on = KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL; };
 
-__device__ __forceinline__ void unit_row_col(int pi, int UW, unsigned long long magic, int& row, int& col) {
-#ifdef MRISR_GNBWD_FASTDIV
-    row = (int)(((unsigned long long)(unsigned)pi * magic) >> 40);
-#else
+__device__ __forceinline__ void unit_row_col(int pi, int UW, int& row, int& col) {
     row = pi / UW;
-#endif
     col = pi - row * UW;
 }
 
@@ -501,6 +466,7 @@ template <int KIND, int FT, int S>
 __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / FT)) gn_bwd_fused_kernel(GnBwdArgs<__nv_bfloat16> a, FusedParams fp) {
     using T = __nv_bfloat16;
     constexpr bool POOL = KindTraits<KIND>::pool;
+    constexpr bool kIncr = Incr<KIND>::on;
     constexpr int P = POOL ? 4 : 1;
     constexpr int RAWV = 2 * P + (POOL ? 1 : 0);
     constexpr int NW = FT / 32;
@@ -580,7 +546,7 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
         const int pi = p0 + i * pstep;
         int uy, ux;
-        unit_row_col(pi, UW, fp.uw_magic, uy, ux);
+        unit_row_col(pi, UW, uy, ux);
         uy += r0;
 #pragma unroll
         for (int q = 0; q < P; ++q) {
@@ -760,7 +726,7 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
         [[maybe_unused]] int uy = 0, ux = 0;
         if constexpr (!kIncr) {
             const int pi = p0 + i * pstep;
-            unit_row_col(pi, UW, fp.uw_magic, uy, ux);
+            unit_row_col(pi, UW, uy, ux);
             uy += r0;
         }
         float rv[P][8], dz[P][8], act[8], dl = 0.f;
@@ -811,8 +777,7 @@ inline int env_int(const char* name, int dflt) {
 }
 
 inline int fused_threads() {
-    static const int ft = env_int("MRISR_GNBWD_FT", 512) == 256 ? 256 : 512;
-    return ft;
+    return 512;                       // 2 CTAs / SM; 256 (4 CTAs / SM) measured slower in round 1 (profiles/r01_gn_bwd_fused.md)
 }
 
 template <int KIND>
@@ -825,8 +790,7 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     static const int enabled = env_int("MRISR_GNBWD_FUSED", 1);
     // two CTAs per SM (64 registers) for the one-pixel kinds; the 2x2-window kinds need 128 registers -> one CTA with all the SM's
     // shared memory
-    static const int smem_kb = env_int(POOL ? "MRISR_GNBWD_POOL_SMEM_KB" : "MRISR_GNBWD_SMEM_KB",
-                                       FT == 512 ? (POOL ? 190 : 96) : (POOL ? 95 : 40));
+    const int smem_kb = FT == 512 ? (POOL ? 190 : 96) : (POOL ? 95 : 40);
     static const int cs_env = env_int("MRISR_GNBWD_CS", 0);
     if (!enabled) return pl;
     const int C = a.r.C, nv = C / 8, gs = C / kGroups;
@@ -846,10 +810,9 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     pl.fp.ups = nv / ncv;
     pl.fp.rows_pc = ceil_div(UH, cs);
     const int iters = (int)ceil_div64((int64_t)pl.fp.rows_pc * UW * ncv, FT);
-    // pipeline depth S (= streaming slots): 2 for the 2x2-window kinds (9 vectors per unit), else 4, or 8 with MRISR_GNBWD_D=8
-    static const int d_env = env_int("MRISR_GNBWD_D", 4);
-    const int S = POOL ? 2 : (d_env == 8 ? 8 : 4);
-    static const int k_env = env_int("MRISR_GNBWD_K", -1);
+    // pipeline depth S (= streaming slots): 2 for the 2x2-window kinds (9 vectors per unit), else 4
+    const int S = POOL ? 2 : 4;
+    const int k_env = -1;
     int slots;                                                     // shared-memory slots per thread
     if (iters <= kmax && k_env < 0) { pl.fp.K = iters; slots = iters; }      // everything stays resident: no streaming slots
     else {
@@ -860,14 +823,12 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     }
     pl.depth = S;
     pl.fp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
-    pl.fp.uw_magic = ((1ull << 40) + (unsigned)UW - 1) / (unsigned)UW;
     pl.fp.ts = trk_steps(FT / ncv, UW, a.r.W + 2, a.g.W + 2);
     pl.fp.psr = a.r.ps ? a.r.ps : a.r.C;
     pl.fp.psg = a.g.ps ? a.g.ps : a.g.C;
     pl.fp.psd = a.dr.ps ? a.dr.ps : a.dr.C;
     pl.fp.psh = POOL ? (a.gpool.ps ? a.gpool.ps : a.gpool.C) : 0;
-#ifdef MRISR_GNBWD_INCR
-    {
+    if (Incr<KIND>::on) {
         // 32-bit element offsets inside a sample, and the operand geometries the incremental form assumes
         auto elems = [](const Act<__nv_bfloat16>& t) { return (double)t.sample_pixels() * (t.ps ? t.ps : t.C); };
         const bool same_res = KIND == SRC_DIRECT || KIND == SRC_DIRECT_POOL || KIND == SRC_BLEND_BIL;
@@ -878,10 +839,6 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
         if (KIND == SRC_BLEND_PS && (a.g.W != 2 * a.r.W || a.g.H != 2 * a.r.H)) return pl;
         if (POOL && (a.gpool.W != UW || a.gpool.H != UH || elems(a.gpool) >= 2147483648.0)) return pl;
     }
-#endif
-#ifdef MRISR_GNBWD_FASTDIV
-    if (UW < 8 || (int64_t)pl.fp.rows_pc * UW >= (1 << 24)) return pl;            // outside the exact range: unfused path
-#endif
     pl.smem = (size_t)slots * RAWV * FT * 16 + red_bytes;
     pl.fp.slots = slots;
     pl.units = a.r.N * pl.fp.ups;
@@ -926,8 +883,7 @@ int run(const GnBwdArgs<T>& a, cudaStream_t s) {
         const FusedPlan fpl = fused_plan<KIND>(a);
         if (fpl.ok) {
             constexpr int S0 = KindTraits<KIND>::pool ? 2 : 4;
-            if (fpl.depth == 8) return fpl.ft == 256 ? run_fused<KIND, 256, 8>(a, fpl, s) : run_fused<KIND, 512, 8>(a, fpl, s);
-            return fpl.ft == 256 ? run_fused<KIND, 256, S0>(a, fpl, s) : run_fused<KIND, 512, S0>(a, fpl, s);
+            return run_fused<KIND, 512, S0>(a, fpl, s);
         }
     }
     const int UH = a.r.H / (P == 4 ? 2 : 1), UW = a.r.W / (P == 4 ? 2 : 1);
@@ -936,21 +892,14 @@ int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     const int pcs = KIND == SRC_BLEND_PS ? C / 4 : C;
     const double inv_count = 1.0 / ((double)(C / kGroups) * a.r.H * a.r.W);
     const int rows_ap = rows_per_block(UW, nv, NTHR, 8);
-    // Samples are processed in chunks small enough for the r / g tensors of a chunk to stay in L2 between the reduce pass
-    // and the apply pass (GroupNorm couples a whole sample, so the two passes cannot be one): 5 -> 3 HBM passes.
-    const double sample_bytes = 3.0 * sizeof(T) * (double)C * a.r.H * a.r.W;          // r + g read, dr written
-    const double chunk_d = gn_bwd_chunk_bytes() / sample_bytes;
-    int chunk = chunk_d >= (double)a.r.N ? a.r.N : (int)chunk_d;
-    if (chunk < 1) chunk = 1;
-    for (int n0 = 0; n0 < a.r.N; n0 += chunk) {
-        const int nn = a.r.N - n0 < chunk ? a.r.N - n0 : chunk;
-        gn_bwd_reduce_kernel<T, KIND><<<dim3(slots, nn), NTHR, 0, s>>>(a, rows_pb, n0);
-        MRISR_LAUNCH_CHECK();
-        gn_bwd_finalize_kernel<T, KIND><<<nn * kGroups, FTHR, 0, s>>>(a, slots, inv_count, n0, nn, 0);
-        MRISR_LAUNCH_CHECK();
-        gn_bwd_apply_kernel<T, KIND><<<dim3(ceil_div(UH, rows_ap), nn), NTHR, 0, s>>>(a, rows_ap, n0);
-        MRISR_LAUNCH_CHECK();
-    }
+    // (per-chunk reduce + apply for L2 reuse was measured and rejected: profiles/r01_gn_bwd_chunking.md)
+    const int n0 = 0, nn = a.r.N;
+    gn_bwd_reduce_kernel<T, KIND><<<dim3(slots, nn), NTHR, 0, s>>>(a, rows_pb, n0);
+    MRISR_LAUNCH_CHECK();
+    gn_bwd_finalize_kernel<T, KIND><<<nn * kGroups, FTHR, 0, s>>>(a, slots, inv_count, n0, nn, 0);
+    MRISR_LAUNCH_CHECK();
+    gn_bwd_apply_kernel<T, KIND><<<dim3(ceil_div(UH, rows_ap), nn), NTHR, 0, s>>>(a, rows_ap, n0);
+    MRISR_LAUNCH_CHECK();
     gn_bwd_finalize_kernel<T, KIND><<<pcs, FTHR, 0, s>>>(a, slots, inv_count, 0, a.r.N, 1);
     MRISR_LAUNCH_CHECK();
     return 0;

@@ -79,55 +79,7 @@ __global__ void __launch_bounds__(NTHR, 2) head_blend_kernel(BlendArgs<T> a, int
         }
 }
 
-// scratch[n * gridDim.x + blockIdx.x] = sum over the block's quads of dxm * (xb - xp)
-template <typename T>
-__global__ void __launch_bounds__(NTHR, 2) blend_dalpha_kernel(BlendArgs<T> a, Act<T> dxm, float* __restrict__ scratch, int rows_pb) {
-    __shared__ float s_w[NTHR / 32];
-    const int n = blockIdx.y;
-    const RowMap m = row_map(a.xm, NTHR, threadIdx.x);
-    float acc = 0.f;
-    if (m.active) {
-        BlendCtx c;
-        load_blend_ctx(a, n, m.cv, c);
-        const int h = a.r_ps.H, w = a.r_ps.W;
-        const int y_end = min(h, (int)(blockIdx.x + 1) * rows_pb);
-        for (int y = blockIdx.x * rows_pb; y < y_end; ++y)
-            for (int x = m.x0; x < w; x += m.xstep) {
-                float xb[4][8], xp[4][8];
-                quad_values(a, c, n, y, x, m.cv, xb, xp);
-#pragma unroll
-                for (int ij = 0; ij < 4; ++ij) {
-                    float g[8];
-                    load8(dxm.at(n, 2 * y + (ij >> 1), 2 * x + (ij & 1), m.cv * 8), g);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) acc = fmaf(g[k], xb[ij][k] - xp[ij][k], acc);
-                }
-            }
-    }
-    acc = warp_sum(acc);
-    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float t = 0.f;
-        for (int w = 0; w < NTHR / 32; ++w) t += s_w[w];
-        scratch[(int64_t)n * gridDim.x + blockIdx.x] = t;
-    }
-}
-
-__global__ void dalpha_finalize_kernel(const float* __restrict__ scratch, int nblocks, const float* __restrict__ alpha,
-                                       float* __restrict__ dalpha) {
-    double t = 0.0;
-    for (int i = threadIdx.x; i < nblocks; i += 32) t += (double)scratch[i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (threadIdx.x == 0) {
-        const float s = sigmoidf_(alpha[0]);
-        dalpha[0] = (float)(t * (double)(s * (1.f - s)));
-    }
-}
-
-#ifdef MRISR_DALPHA_FUSED
-// -DMRISR_DALPHA_FUSED builds: d(alpha) from the per-channel sums  sum g * xb  (bilinear branch) and  sum g * xp  (pixel-shuffle
+// d(alpha) from the per-channel sums  sum g * xb  (bilinear branch) and  sum g * xp  (pixel-shuffle
 // branch) that gn_bwd's finalize kernels of the two branches leave in `sums` ([2][nch]); one warp
 __global__ void dalpha_from_channels_kernel(const float* __restrict__ sums, int nch, const float* __restrict__ alpha,
                                             float* __restrict__ dalpha) {
@@ -140,7 +92,6 @@ __global__ void dalpha_from_channels_kernel(const float* __restrict__ sums, int 
         dalpha[0] = (float)(t * (double)(s * (1.f - s)));
     }
 }
-#endif
 
 // one thread per output pixel: all Ch channels (Ch = f/2: 8 or 16 ... up to 64); one block = rows of ONE sample so the
 // folded GroupNorm scale/shift and the 1x1 weights sit in shared memory
@@ -225,39 +176,19 @@ int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s) {
     // 2x2 quads per thread and block (MRISR_HEADBLEND_UPT; 2 in the measured build).  A block first folds both branches'
     // GroupNorm into 80 per-thread constants (160 scalar loads, 40 integer divisions: load_blend_ctx), which at 2 quads per
     // thread is about as long as the blend itself (527 instructions per quad); not swept yet.
-    static const int upt = [] { const char* e = getenv("MRISR_HEADBLEND_UPT"); const int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
+    constexpr int upt = 8;       // 2x2 quads per thread: swept on B200 in round 2, 2 -> 8: 0.471 -> 0.392 ms per step
     const int rpb = rows_per_block(a.r_ps.W, a.xm.C / 8, NTHR, upt);
     head_blend_kernel<T><<<dim3(ceil_div(a.r_ps.H, rpb), a.xm.N), NTHR, 0, s>>>(a, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
 
-static inline int dalpha_rows(int W, int nv) { return rows_per_block(W, nv, NTHR, 4); }
-size_t blend_dalpha_scratch_elems(int N, int H2, int W2) {
-    // one partial per (sample, block of low-resolution rows); nv >= 1 gives the upper bound on the block count
-    return (size_t)N * ceil_div(H2 / 2, dalpha_rows(W2 / 2, 32));
-}
-
-template <typename T>
-int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float* scratch, cudaStream_t s) {
-    ProfScope prof_("blend_dalpha", s);
-    const int rpb = dalpha_rows(a.r_ps.W, a.xm.C / 8);
-    const int slots = ceil_div(a.r_ps.H, rpb);
-    blend_dalpha_kernel<T><<<dim3(slots, a.xm.N), NTHR, 0, s>>>(a, dxm, scratch, rpb);
-    MRISR_LAUNCH_CHECK();
-    dalpha_finalize_kernel<<<1, 32, 0, s>>>(scratch, slots * a.xm.N, a.alpha, dalpha);
-    MRISR_LAUNCH_CHECK();
-    return 0;
-}
-
-#ifdef MRISR_DALPHA_FUSED
 int launch_dalpha_from_channels(const float* sums, int nch, const float* alpha, float* dalpha, cudaStream_t s) {
     ProfScope prof_("blend_dalpha", s);
     dalpha_from_channels_kernel<<<1, 32, 0, s>>>(sums, nch, alpha, dalpha);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
-#endif
 
 template <typename T>
 int launch_final_head(Act<T> r, const float* stats, const float* gamma, const float* beta, const float* w1x1,
@@ -289,7 +220,6 @@ int launch_colsum(Act<T> t, float* out, float* scratch, cudaStream_t s) {
 
 #define INST(T)                                                                                                  \
     template int launch_head_blend<T>(const BlendArgs<T>&, cudaStream_t);                                        \
-    template int launch_blend_dalpha<T>(const BlendArgs<T>&, Act<T>, float*, float*, cudaStream_t);              \
     template int launch_final_head<T>(Act<T>, const float*, const float*, const float*, const float*,            \
                                       const float*, float*, cudaStream_t);                                       \
     template int launch_colsum<T>(Act<T>, float*, float*, cudaStream_t);

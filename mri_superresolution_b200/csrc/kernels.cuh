@@ -103,11 +103,8 @@ struct BlendArgs {
     Act<T> xm;                                                                      // [N,2H,2W,Ch]
 };
 template <typename T> int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s);
-// d(alpha) = sigmoid'(alpha) * sum( dxm * (xb - xp) ); scratch >= blend_dalpha_scratch_elems floats
-size_t blend_dalpha_scratch_elems(int N, int H2, int W2);
-template <typename T>
-int launch_blend_dalpha(const BlendArgs<T>& a, Act<T> dxm, float* dalpha, float* scratch, cudaStream_t s);
-// staged (-DMRISR_DALPHA_FUSED): d(alpha) from the per-channel sums the two blend-kind gn_bwd launches write ([2][nch])
+// d(alpha) = sigmoid'(alpha) * sum( dxm * (xb - xp) ) from the per-channel sums  sum g * xb,  sum g * xp  that the two
+// blend-kind gn_bwd launches write ([2][nch])
 int launch_dalpha_from_channels(const float* sums, int nch, const float* alpha, float* dalpha, cudaStream_t s);
 
 // y = sigmoid( w1x1 . lrelu(gn(r)) + b )      (final_conv.1..3 + sigmoid, models/unet_model.py:169-172,211)

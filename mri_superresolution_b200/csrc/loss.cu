@@ -375,7 +375,8 @@ int dispatch_split(int win, const float* pred, const float* tgt, float* dpred, f
 }
 
 bool ssim_split_enabled() {
-    static const bool on = [] { const char* e = getenv("MRISR_SSIM_SPLIT"); return e && e[0] == '1'; }();
+    // on by default: measured on B200 in round 2, 0.627 -> 0.558 ms per 64 x 512^2 batch; MRISR_SSIM_SPLIT=0 = the fused kernel
+    static const bool on = [] { const char* e = getenv("MRISR_SSIM_SPLIT"); return !(e && e[0] == '0'); }();
     return on;
 }
 

@@ -8,7 +8,6 @@
 #include <vector>
 #include "kernels.cuh"
 #include "upsample_slide.cuh"
-#include "upsample_bwd_slide.cuh"
 
 namespace mrisr {
 namespace {
@@ -425,8 +424,7 @@ static int max_span(const std::vector<int>& lo, const std::vector<int>& hi, int 
 }
 
 static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>& dsrc, UpBwdTile& tp, size_t& smem) {
-    static const bool on = [] { const char* e = getenv("MRISR_UPBWD_TILED"); return !(e && e[0] == '0'); }();
-    if (!on || dsrc.C % 8) return false;
+    if (dsrc.C % 8) return false;
     if (ddst.planar() != dsrc.planar()) return false;      // level 1 -> level 0 boundary: per-vector strided stores, the gather form is faster
     const int nv = dsrc.C / 8;
     // the staged tensor is the (4x larger) destination gradient: units follow ITS layout (a plane, or all channels of an NHWC
@@ -503,11 +501,9 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
     }
     ProfScope prof_(tag, s);
     const int nv = r.C / 8;
-    // vectors per thread and block (MRISR_GNAPPLY_UPT, MRISR_GNAPPLY_POOL_UPT; defaults = the measured build): the per-channel
-    // constants cost a block ~370 instructions and 32 dependent-free scalar loads before its first vector, about a quarter of
-    // a 16-vector thread's work (profiles/r01_elementwise_issue.md); longer blocks amortise it at the price of fewer waves
-    static const int upt = [] { const char* e = getenv("MRISR_GNAPPLY_UPT"); const int v = e ? atoi(e) : 16; return v > 0 ? v : 16; }();
-    static const int upt_pool = [] { const char* e = getenv("MRISR_GNAPPLY_POOL_UPT"); const int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();
+    // vectors per thread: 16 (plain) / 4 (with the pooled quarter).  Swept on B200 in round 2 (32, 64 / 8): no gain (0.99 ->
+    // 1.01, 1.08 / 0.99 ms per step), the kernels run at ~83 % of the HBM copy rate.
+    constexpr int upt = 16, upt_pool = 4;
     if (pooled.p) {
         const int rpb = rows_per_block(r.W / 2, nv, NTHR, upt_pool);
         dim3 grid(ceil_div(r.H / 2, rpb), r.N);
@@ -524,21 +520,17 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     ProfScope prof_("upsample2x", s);
-#ifdef MRISR_UPSAMPLE_SLIDE
-    // staged: columns stay with a thread, source rows slide through registers (upsample_slide.cuh); 16 destination rows per
-    // block re-read 1 - 2 of their 9 - 10 source rows from the neighbouring blocks' (L2)
+    // columns stay with a thread, source rows slide through registers (upsample_slide.cuh); 16 destination rows per block
+    // re-read 1 - 2 of their 9 - 10 source rows from the neighbouring blocks' (L2).  Measured on B200 (round 2, batch 64
+    // train step): 0.706 -> 0.556 ms per step against the gather form below, which stays for tensors beyond 32-bit offsets.
     if ((int64_t)(src.W + 2) * (src.ps ? src.ps : src.C) < (1ll << 31) / (src.H + 2) &&
         (int64_t)(dst.W + 2) * (dst.ps ? dst.ps : dst.C) < (1ll << 31) / (dst.H + 2)) {
-        static const int rows_env = [] { const char* e = getenv("MRISR_UPSLIDE_ROWS"); return e ? atoi(e) : 0; }();
-        const int rows = rows_env > 0 ? rows_env : (dst.H >= 64 ? 16 : 8);
+        const int rows = dst.H >= 64 ? 16 : 8;
         dim3 grid_s(ceil_div(dst.H, rows), dst.N);
-        static const bool pf = [] { const char* e = getenv("MRISR_UPSLIDE_PF"); return e && e[0] == '1'; }();
-        if (pf) upsample2x_slide_kernel<T, 1, NTHR, true><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
-        else upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
+        upsample2x_slide_kernel<T, 1, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows);
         MRISR_LAUNCH_CHECK();
         return 0;
     }
-#endif
     const int rpb = rows_per_block(dst.W, dst.C / 8, NTHR, 8);
     dim3 grid(ceil_div(dst.H, rpb), dst.N);
     upsample2x_kernel<T><<<grid, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rpb);
@@ -555,23 +547,6 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-#ifdef MRISR_UPSAMPLE_BWD_SLIDE
-    // staged: scatter-along-rows form (upsample_bwd_slide.cuh): one horizontal reduction per destination row instead of one per
-    // (source row, destination row) pair; 16 source rows per block
-    static_assert(sizeof(UpAdjTap) == sizeof(AdjTap5), "tap table layouts must agree");
-    if ((int64_t)(ddst.W + 2) * (ddst.ps ? ddst.ps : ddst.C) < (1ll << 31) / (ddst.H + 2) && dsrc.W <= kAdjMaxW) {
-        const AdjTap5* ty = adj_table(dsrc.H, s);
-        const AdjTap5* tx = dsrc.W == dsrc.H ? ty : adj_table(dsrc.W, s);
-        if (!ty || !tx) { set_error("upsample2x_bwd: tap table allocation failed"); return -1; }
-        static const int rows_env = [] { const char* e = getenv("MRISR_UPBWD_SLIDE_ROWS"); return e ? atoi(e) : 0; }();
-        const int rows = rows_env > 0 ? rows_env : (dsrc.H >= 32 ? 16 : 8);
-        dim3 grid_s(ceil_div(dsrc.H, rows), dsrc.N);
-        upsample2x_bwd_slide_kernel<T, NTHR><<<grid_s, NTHR, 0, s>>>(ddst, addend, dsrc, reinterpret_cast<const UpAdjTap*>(ty),
-                                                                    reinterpret_cast<const UpAdjTap*>(tx), up_scale(dsrc.H), rows);
-        MRISR_LAUNCH_CHECK();
-        return 0;
-    }
-#endif
     if constexpr (sizeof(T) == 2) {
         UpBwdTile tp;
         size_t smem = 0;

@@ -127,7 +127,7 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         gn_part = (float*)ar.take(gnp_max * sizeof(float));
         mstat = (float*)ar.take((size_t)N * kGroups * 2 * sizeof(float));
         wg_part = (float*)ar.take(wg_max * sizeof(float));
-        const size_t misc_elems = std::max({blend_dalpha_scratch_elems(N, 2 * H, 2 * W), colsum_scratch_elems(N, H, W, 2 * f), (size_t)4 * f});
+        const size_t misc_elems = std::max(colsum_scratch_elems(N, H, W, 2 * f), (size_t)4 * f);
         misc = (float*)ar.take(misc_elems * sizeof(float));
     } else {
         gn_part = mstat = wg_part = misc = nullptr;

@@ -31,7 +31,9 @@ struct SideStream {
     bool ok = false;
 };
 static SideStream* side_stream() {
-    static const bool enabled = [] { const char* e = getenv("MRISR_BWD_SIDE"); return e && e[0] == '1'; }();
+    // on by default: measured on B200 in round 2 under graph replay, 17.60 -> 17.41 ms per step (the small deep-level kernels of
+    // the data-gradient chain leave SMs idle that the weight-gradient kernels fill); MRISR_BWD_SIDE=0 keeps one stream
+    static const bool enabled = [] { const char* e = getenv("MRISR_BWD_SIDE"); return !(e && e[0] == '0'); }();
     if (!enabled) return nullptr;
     static SideStream ss;
     static bool tried = false;
@@ -262,20 +264,13 @@ struct Runner {
             TRY(launch_gn_bwd<T>(a, s));
             TRY(conv_bwd(19, ws.XM, none, ws.dR[19], true));          // G[19] = d(blend)
         }
-#ifdef MRISR_DALPHA_FUSED
-        // staged: the two blend-kind gn_bwd launches also leave  sum g * branch  per channel in ws.misc ([2][f/2]); d(alpha) is
+        // the two blend-kind gn_bwd launches also leave  sum g * branch  per channel in ws.misc ([2][f/2]); d(alpha) is
         // formed from them before colsum reuses the scratch (no separate pass over both branches and the gradient)
         TRY(block_done(19));
         const int nch = ws.R[17].C;
         TRY(block_bwd(17, SRC_BLEND_BIL, ws.G[19], 0, none, ws.UB, none, true, ws.misc));
         TRY(block_bwd(18, SRC_BLEND_PS, ws.G[19], 0, none, ws.A[16], none, true, ws.misc + nch));
         TRY(launch_dalpha_from_channels(ws.misc, nch, P(0), GP(0), s));
-#else
-        TRY(launch_blend_dalpha<T>(blend_args(), ws.G[19], GP(0), ws.misc, s));
-        TRY(block_done(19));
-        TRY(block_bwd(17, SRC_BLEND_BIL, ws.G[19], 0, none, ws.UB, none));        // G[17] = d(UB)
-        TRY(block_bwd(18, SRC_BLEND_PS, ws.G[19], 0, none, ws.A[16], none));      // G[18] = d(y3) via pixel-shuffle branch
-#endif
         TRY(launch_colsum<T>(ws.dR[18], GP(ws.conv[18].bias), ws.misc, s));
         TRY(block_done(18));
         TRY(launch_upsample2x_bwd<T>(ws.G[17], ws.G[18], ws.DY3, s));

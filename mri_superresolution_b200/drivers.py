@@ -205,6 +205,8 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
     if rank == 0:
         torch.save({"epoch": epoch, "model_state_dict": model.state_dict(), "optimizer_state_dict": optimizer.state_dict(),
                     "val_loss": val_loss, "val_ssim": val_ssim}, final_path)       # :467-477
+    if graphed is not None:
+        graphed.close()                    # a recorded step that holds NCCL work must go before the caller destroys the group
     if buckets is not None:
         buckets.close()
     log_message(f"Training completed. Final model saved to {final_path}", stream=log_stream)

@@ -20,6 +20,7 @@ import torch
 import torch.nn as nn
 
 from .. import _native
+from ..utils.workspace import WorkspaceCache
 
 __all__ = ["UNetSuperRes", "param_specs"]
 
@@ -113,7 +114,7 @@ class UNetSuperRes(nn.Module):
             node.register_parameter(parts[-1], nn.Parameter(torch.empty(shape, dtype=torch.float32)))
         self._flat = None
         self._grad_arenas: List[torch.Tensor] = []
-        self._workspaces: Dict[tuple, torch.Tensor] = {}
+        self._workspaces = WorkspaceCache()
         self._ticket = 0
         self._last_train_key = None
         self._marks = None                 # (int64 offsets array, void* events array, n) set by parallel.GradientBuckets
@@ -169,7 +170,7 @@ class UNetSuperRes(nn.Module):
             p.data = flat[o:o + n].view(p.shape)
         self._flat = flat
         self._grad_arenas = []
-        self._workspaces = {}
+        self._workspaces.clear()
 
     def _apply(self, fn, *args, **kwargs):
         out = super()._apply(fn, *args, **kwargs)
@@ -195,17 +196,24 @@ class UNetSuperRes(nn.Module):
     def _workspace(self, n: int, h: int, w: int, train: bool) -> torch.Tensor:
         prec = _precision_code(self.precision)
         key = (n, h, w, prec, train, self._flat.device)
-        ws = self._workspaces.get(key)
-        if ws is None:
+
+        def alloc():
             nbytes = _native.lib().mrisr_unet_workspace_bytes(n, h, w, self.base_filters, prec, int(train))
             if nbytes == 0:
                 _native.check(-2, "mrisr_unet_workspace_bytes")
-            # drop other shapes of the same kind: activations for one shape already take GBs
-            for k in [k for k in self._workspaces if k[4] == train]:
-                del self._workspaces[k]
-            ws = torch.zeros(nbytes, dtype=torch.uint8, device=self._flat.device)   # zero borders: one-time invariant
-            self._workspaces[key] = ws
-        return ws
+            return torch.zeros(nbytes, dtype=torch.uint8, device=self._flat.device)   # zero borders: one-time invariant
+
+        # other un-pinned shapes of the same kind are dropped beyond the two most recent (a workspace is GBs); entries a
+        # recorded CUDA graph points into are pinned and never dropped (utils/workspace.py)
+        return self._workspaces.get(key, bool(train), alloc)
+
+    def pin_workspaces(self):
+        """Keeps every workspace allocated so far alive until ``unpin_workspaces(token)`` (utils/graph.py: a recorded step
+        holds raw pointers into them)."""
+        return self._workspaces.pin_all()
+
+    def unpin_workspaces(self, token) -> None:
+        self._workspaces.unpin(token)
 
     def _run_forward(self, x: torch.Tensor, train: bool) -> torch.Tensor:
         if x.dim() != 4 or x.shape[1] != 1:

@@ -16,6 +16,23 @@ from __future__ import annotations
 import torch
 
 
+def _pin_all(*roots):
+    """Pins the workspaces of every module under ``roots`` that caches C-ABI workspaces (UNetSuperRes, VGGFeatureExtractor)."""
+    pins, seen = [], set()
+    for root in roots:
+        mods = root.modules() if hasattr(root, "modules") else [root]
+        for m in mods:
+            if id(m) not in seen and hasattr(m, "pin_workspaces"):
+                seen.add(id(m))
+                pins.append((m, m.pin_workspaces()))
+    return pins
+
+
+def _unpin_all(pins) -> None:
+    for m, token in pins or ():
+        m.unpin_workspaces(token)
+
+
 class GraphedTrainStep:
     def __init__(self, model, criterion, optimizer, x_example: torch.Tensor, t_example: torch.Tensor, warmup: int = 2,
                  buckets=None, record_metric: bool = False):
@@ -45,6 +62,9 @@ class GraphedTrainStep:
                 self._eager()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        # the recorded launches hold raw pointers into the workspaces the warm-up steps allocated: pin them so that no other
+        # shape (ragged last batch, validation under no_grad) can evict them while the graph lives
+        self._pins = _pin_all(model, criterion)
         self.graph = torch.cuda.CUDAGraph()
         optimizer.zero_grad(set_to_none=True)
         with torch.cuda.graph(self.graph):
@@ -70,8 +90,29 @@ class GraphedTrainStep:
             self.loss_and_metric = torch.stack([loss.detach(), ssim])
         return loss.detach()
 
+    def close(self) -> None:
+        """Destroys the recorded graph.  A graph that captured NCCL all-reduces keeps the communicator busy:
+        ``dist.destroy_process_group()`` waits for every such graph to be destroyed first, so data-parallel callers must
+        close the step before tearing the group down (bench.py, drivers.train, tools/check_graph_dp.py)."""
+        g, self.graph = getattr(self, "graph", None), None
+        if g is not None:
+            torch.cuda.synchronize(self.x.device)
+            g.reset()
+        _unpin_all(getattr(self, "_pins", None))
+        self._pins = None
+        self.loss = None
+        self.loss_and_metric = None
+
+    def __del__(self):
+        try:
+            _unpin_all(getattr(self, "_pins", None))
+        except Exception:
+            pass
+
     def __call__(self, x: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
         """One training step on (x, t); returns the loss as a 0-dim device tensor that the NEXT call overwrites."""
+        if self.graph is None:
+            raise RuntimeError("GraphedTrainStep has been closed")
         if x.shape != self.x.shape or t.shape != self.t.shape:
             raise ValueError(f"GraphedTrainStep was recorded for {tuple(self.x.shape)} / {tuple(self.t.shape)}, "
                              f"got {tuple(x.shape)} / {tuple(t.shape)}")
@@ -100,6 +141,7 @@ class GraphedForward:
                 self._eager()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        self._pins = _pin_all(model)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.y = self._eager()
@@ -109,7 +151,24 @@ class GraphedForward:
         with torch.no_grad():
             return torch.clamp(self.model(self.x), 0, 1)
 
+    def close(self) -> None:
+        g, self.graph = getattr(self, "graph", None), None
+        if g is not None:
+            torch.cuda.synchronize(self.x.device)
+            g.reset()
+        _unpin_all(getattr(self, "_pins", None))
+        self._pins = None
+        self.y = None
+
+    def __del__(self):
+        try:
+            _unpin_all(getattr(self, "_pins", None))
+        except Exception:
+            pass
+
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if self.graph is None:
+            raise RuntimeError("GraphedForward has been closed")
         if x.shape != self.x.shape:
             raise ValueError(f"GraphedForward was recorded for {tuple(self.x.shape)}, got {tuple(x.shape)}")
         self.x.copy_(x, non_blocking=True)

@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 
 from .. import _native
+from .workspace import WorkspaceCache
 
 VGG_MEAN = [0.485, 0.456, 0.406]        # utils/losses.py:7
 VGG_STD = [0.229, 0.224, 0.225]         # utils/losses.py:8
@@ -73,7 +74,7 @@ class VGGFeatureExtractor(nn.Module):
         self.register_buffer("std", torch.tensor(VGG_STD).view(1, 3, 1, 1))
         self.cfg = [k[1] if k[0] == "conv" else -1 for k in kinds if k[0] != "relu"]
         self._packed = None            # (device, flat fp32 weights, packed bf16 operands)
-        self._ws = {}
+        self._ws = WorkspaceCache()
 
     # ---- native plumbing ------------------------------------------------------------------
     def _cfg_array(self):
@@ -97,16 +98,23 @@ class VGGFeatureExtractor(nn.Module):
 
     def _workspace(self, n, h, w, grad, device):
         key = (n, h, w, bool(grad), device)
-        ws = self._ws.get(key)
-        if ws is None:
+
+        def alloc():
             arr, nc = self._cfg_array()
             nbytes = _native.lib().mrisr_vgg_workspace_bytes(n, h, w, arr, nc, 1 if grad else 0)
             if nbytes == 0:
                 raise ValueError(_native.lib().mrisr_last_error().decode())
-            self._ws.clear()
-            ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)     # zero borders are an invariant of the kernels
-            self._ws[key] = ws
-        return ws
+            return torch.zeros(nbytes, dtype=torch.uint8, device=device)     # zero borders are an invariant of the kernels
+
+        # grad / no-grad workspaces coexist (training step vs validation pass); entries a recorded CUDA graph points into
+        # are pinned and never dropped (utils/workspace.py)
+        return self._ws.get(key, bool(grad), alloc)
+
+    def pin_workspaces(self):
+        return self._ws.pin_all()
+
+    def unpin_workspaces(self, token) -> None:
+        self._ws.unpin(token)
 
     @staticmethod
     def _gray(x: torch.Tensor, name: str) -> torch.Tensor:

@@ -42,6 +42,10 @@ KNOBS = [
     ("gn_bwd_cluster8", {"MRISR_GNBWD_CS": "8"}, False),
     ("wgrad_tc_per_tap", {"MRISR_WGRAD_TC3": "0"}, False),
     ("rows_one_cta", {"MRISR_ROWS_CTAS": "1"}, False),
+    # weight gradients on the main stream instead of the side stream: same kernels, same inputs (bit-equal, checked below)
+    ("bwd_one_stream", {"MRISR_BWD_SIDE": "0"}, False),
+    # the fused halo-2R loss kernel instead of the forward-maps + gradient pair
+    ("ssim_fused", {"MRISR_SSIM_SPLIT": "0"}, False),
     ("conv_tc_per_tap", {"MRISR_CONV_TC_MERGE3": "0"}, True),
     ("ring_one_cta", {"MRISR_RING_CTAS": "1"}, True),
     # the wide-image fallback (unet_plan.cuh: level_is_planar): levels <= 0 in NHWC on the TMA kernels, as at 512 x 512 input
@@ -67,66 +71,6 @@ def test_knob_variant_matches_default(tmp_path, baseline, name, env, fwd):
         # forward knobs <= 2.9e-2 on weights and 3.2e-2 on GroupNorm / bias vectors
         tol = (0.2 if kind == "vector" else 6e-2) if fwd else 5e-3
         assert rel < tol, (name, k, rel)
+        if name == "bwd_one_stream":
+            assert np.array_equal(v[k], baseline[k]), k          # only the stream changes: identical to the bit
     print(name, {k: (round(r, 6), n) for k, (r, n) in worst.items()})
-
-
-# Staged kernel variants: written and compiled, NOT yet measured or parity-checked on a B200 (the round's GPU budget ended first).
-# They are off in the shipped build; `MRISR_TEST_STAGED=1 python -m pytest tests/test_gpu_knobs.py -m gpu -k staged` is the first
-# thing to run on them.  MRISR_SSIM_SPLIT=1: forward-maps + gradient kernels instead of the fused halo-2R loss kernel
-# (csrc/loss.cu); every value comes from the same filter calls in the same order, so the gradients should match to the bit.
-@pytest.mark.skipif(os.environ.get("MRISR_TEST_STAGED") != "1", reason="staged variants are opt-in until measured")
-def test_staged_ssim_split_matches_default(tmp_path, baseline):
-    v = _probe(tmp_path, "ssim_split", {"MRISR_SSIM_SPLIT": "1"})
-    assert abs(float(v["loss"]) - float(baseline["loss"])) <= 1e-6 * abs(float(baseline["loss"]))
-    for k, b in baseline.items():
-        if k == "loss":
-            continue
-        a = v[k].astype(np.float64).ravel()
-        b = b.astype(np.float64).ravel()
-        assert np.linalg.norm(a - b) <= 1e-5 * max(np.linalg.norm(b), 1e-12), k
-
-
-# MRISR_BWD_SIDE=1: weight gradients on a second stream (csrc/unet_run.cu: SideStream).  Same kernels, same inputs, only the
-# stream they run on changes, so every gradient must match the default to the bit.
-@pytest.mark.skipif(os.environ.get("MRISR_TEST_STAGED") != "1", reason="staged variants are opt-in until measured")
-def test_staged_side_stream_wgrad_matches_default(tmp_path, baseline):
-    v = _probe(tmp_path, "bwd_side", {"MRISR_BWD_SIDE": "1"})
-    assert float(v["loss"]) == float(baseline["loss"])
-    for k, b in baseline.items():
-        if k != "loss":
-            assert np.array_equal(v[k], b), k
-
-
-# Library variants built by tools/build_variants.sh (compile-time switches, loaded with MRISR_B200_VARIANT):
-#   incr    gn_bwd addressing only: identical arithmetic, everything equal to the bit
-#   dalpha  d(alpha) summed inside gn_bwd instead of blend_dalpha_kernel: only alpha's gradient may move (summation order)
-#   ups     bilinear x2 forward and adjoint: same expression trees as the default kernels (bit-identical when run on the CPU,
-#           tests/native/), but nvcc may contract the multiply-adds differently in the two kernels, which re-rounds a few bf16
-#           activations: forward-knob tolerances
-#   all     the three together
-STAGED_LIBS = [("incr", "exact"), ("dalpha", "alpha"), ("ups", "forward"), ("all", "forward")]
-
-
-@pytest.mark.skipif(os.environ.get("MRISR_TEST_STAGED") != "1", reason="staged variants are opt-in until measured")
-@pytest.mark.parametrize("variant,mode", STAGED_LIBS, ids=[v[0] for v in STAGED_LIBS])
-def test_staged_library_variant_matches_default(tmp_path, baseline, variant, mode):
-    lib = os.path.join(ROOT, "mri_superresolution_b200", "lib", f"libmrisr_b200_{variant}.so")
-    if not os.path.exists(lib):
-        pytest.skip(f"{lib} not built (tools/build_variants.sh)")
-    v = _probe(tmp_path, "lib_" + variant, {"MRISR_B200_VARIANT": variant})
-    if mode != "forward":
-        assert float(v["loss"]) == float(baseline["loss"])
-    else:
-        assert abs(float(v["loss"]) - float(baseline["loss"])) <= 2e-3 * abs(float(baseline["loss"]))
-    for k, b in baseline.items():
-        if k == "loss":
-            continue
-        a64, b64 = v[k].astype(np.float64).ravel(), b.astype(np.float64).ravel()
-        rel = np.linalg.norm(a64 - b64) / max(np.linalg.norm(b64), 1e-12)
-        is_alpha = k.split(":")[-1].split(".")[-1] == "alpha"
-        if mode == "forward":
-            assert rel < (0.2 if v[k].ndim <= 1 else 6e-2), (variant, k, rel)
-        elif is_alpha and mode == "alpha":
-            assert rel < 1e-4, (variant, k, rel)
-        else:
-            assert np.array_equal(v[k], b), (variant, k, rel)

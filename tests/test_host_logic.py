@@ -281,21 +281,8 @@ def test_fused_adam_state_dict_is_stock_adam_layout():
     assert opt.lr == 1.5e-4
 
 
-def test_multiply_shift_row_index_is_exact():
-    """csrc/gn_bwd.cu: unit_row_col (staged -DMRISR_GNBWD_FASTDIV variant): row = (pi * ceil(2^40 / UW)) >> 40 must equal
-    pi // UW for every unit index below 2^24 and every row width the kernels see (UW >= 8)."""
-    rng = np.random.default_rng(0)
-    for uw in list(range(8, 1100)) + [2048, 4096]:
-        magic = ((1 << 40) + uw - 1) // uw
-        n = np.concatenate([np.arange(0, 4 * uw + 8, dtype=np.uint64), rng.integers(0, 1 << 24, size=2048, dtype=np.uint64),
-                            np.array([(1 << 24) - 1, uw * 4095 + uw - 1], dtype=np.uint64)])
-        assert int(n.max()) * magic < (1 << 64)
-        q = (n * np.uint64(magic)) >> np.uint64(40)
-        assert np.array_equal(q, n // np.uint64(uw)), uw
-
-
 def test_gn_bwd_incremental_addressing_replay(tmp_path):
-    """csrc/gn_bwd_trk.h (staged -DMRISR_GNBWD_INCR variant of gn_bwd_fused_kernel): tests/native/gn_bwd_trk_replay.cpp walks every
+    """csrc/gn_bwd_trk.h (incremental addressing of gn_bwd_fused_kernel, plain-tensor kinds): tests/native/gn_bwd_trk_replay.cpp walks every
     (cluster rank, thread) through the kernel's issue / reload / apply order with the constant-step tracker and compares every
     operand index with the direct padded-pixel form of the default build; each unit must be issued and applied exactly once."""
     import subprocess
@@ -324,15 +311,8 @@ def _run_host_kernel_body(tmp_path, name):
     assert res.stdout.startswith("ok ")
 
 
-def test_upsample_bwd_slide_body_runs_on_host(tmp_path):
-    """csrc/upsample_bwd_slide.cuh (staged -DMRISR_UPSAMPLE_BWD_SLIDE kernel): scatter-along-rows adjoint of bilinear x2,
-    every thread of 14 launch grids executed on the CPU and compared bit for bit with the gather form of the shipped kernels
-    (same taps, weights and summation order), with and without the addend, NHWC / planar-8, fp32 / bf16."""
-    _run_host_kernel_body(tmp_path, "upsample_bwd_slide_host")
-
-
 def test_upsample_slide_body_runs_on_host(tmp_path):
-    """csrc/upsample_slide.cuh (staged -DMRISR_UPSAMPLE_SLIDE kernel): the kernel body is a __host__ __device__ function of
+    """csrc/upsample_slide.cuh (the bilinear x2 forward kernel): the kernel body is a __host__ __device__ function of
     (sample, block, thread); tests/native/upsample_slide_host.cu executes every thread of the launch grid on the CPU (NHWC and
     planar-8, fp32 and bf16, odd and one-row shapes) and compares bit for bit with the default kernel's direct form."""
     import shutil
@@ -444,3 +424,47 @@ def test_dalpha_from_branch_sums_identity():
     sv = float(s)
     want = sv * (1 - sv) * float(sum_bil.sum() - sum_ps.sum())
     assert abs(want - float(alpha.grad)) <= 1e-12 * max(1.0, abs(float(alpha.grad)))
+
+
+def test_workspace_cache_never_drops_a_pinned_entry():
+    """utils/workspace.py: a recorded CUDA graph holds raw pointers into its workspace, so pinned entries survive any number of
+    other shapes (a ragged last batch or a no-grad validation pass used to evict the graphed workspace)."""
+    import torch
+    from mri_superresolution_b200.utils.workspace import WorkspaceCache
+    made = []
+
+    def alloc(tag):
+        def f():
+            made.append(tag)
+            return torch.zeros(4)
+        return f
+
+    c = WorkspaceCache(keep=2)
+    a = c.get(("a",), True, alloc("a"))
+    assert c.get(("a",), True, alloc("a2")) is a and made == ["a"]
+    token = c.pin_all()
+    for i in range(5):                                   # five other train-kind shapes come and go
+        c.get(("t", i), True, alloc(f"t{i}"))
+    assert ("a",) in c and c.get(("a",), True, alloc("a3")) is a
+    assert sum(1 for k in c.keys() if k[0] == "t") == 2  # the two most recent un-pinned entries are kept, no more
+    assert ("t", 4) in c and ("t", 3) in c
+    e = c.get(("e",), False, alloc("e"))                 # another kind does not compete with the train kind
+    assert ("t", 4) in c and c.get(("e",), False, alloc("e2")) is e
+    # alternating between two un-pinned shapes (full and ragged batch) does not re-allocate
+    n = len(made)
+    for _ in range(3):
+        c.get(("t", 4), True, alloc("x"))
+        c.get(("t", 3), True, alloc("y"))
+    assert len(made) == n
+    c.unpin(token)
+    for i in range(5, 8):
+        c.get(("t", i), True, alloc(f"t{i}"))
+    assert ("a",) not in c                               # un-pinned: evictable again
+    tok2 = c.pin_all()
+    tok3 = c.pin_all()                                   # pins nest (two graphs over the same module)
+    c.unpin(tok2)
+    assert all(c.pinned(k) for k in tok3)
+    c.unpin(tok3)
+    assert not any(c.pinned(k) for k in c.keys())
+    c.clear()
+    assert len(c) == 0

@@ -48,6 +48,8 @@ def main():
                 losses.append(float(loss.item()))
         results.append((losses, model.flat_parameters().clone()))
         say(f"{'graph' if use_graph else 'eager'} leg done: {losses}")
+        if use_graph:
+            stepper.close()
         buckets.close()
     (l0, p0), (l1, p1) = results
     err = float((p0 - p1).abs().max() / p0.abs().max())
@@ -59,10 +61,18 @@ def main():
     ok = err < 1e-5 and spread == 0.0 and all(abs(a - b) <= 1e-6 * abs(a) for a, b in zip(l0, l1))
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    dist.destroy_process_group()
+    okay = int(flag.item()) == 1
     if rank == 0:
-        print("GRAPH_DP_OK" if int(flag.item()) == 1 else "GRAPH_DP_MISMATCH", flush=True)
-    sys.exit(0 if int(flag.item()) == 1 else 1)
+        print("GRAPH_DP_OK" if okay else "GRAPH_DP_MISMATCH", flush=True)
+    torch.cuda.synchronize()
+    dist.barrier()
+    import threading
+    wd = threading.Timer(20.0, lambda: os._exit(0 if okay else 1))
+    wd.daemon = True
+    wd.start()
+    dist.destroy_process_group()
+    wd.cancel()
+    sys.exit(0 if okay else 1)
 
 
 if __name__ == "__main__":
