@@ -35,6 +35,7 @@ static SideStream* side_stream() {
     // the data-gradient chain leave SMs idle that the weight-gradient kernels fill); MRISR_BWD_SIDE=0 keeps one stream
     static const bool enabled = [] { const char* e = getenv("MRISR_BWD_SIDE"); return !(e && e[0] == '0'); }();
     if (!enabled) return nullptr;
+    if (prof_on()) return nullptr;        // per-kernel attribution (mrisr_prof_*): one stream, so a kernel's events time it alone
     static SideStream ss;
     static bool tried = false;
     if (!tried) {

@@ -210,6 +210,86 @@ def train_case(UNetSuperRes, ref_losses):
     print("train3 losses", losses)
 
 
+def trained_case(UNetSuperRes, ref_losses):
+    """A weight set that is NOT random init: the reference model trained for 60 steps of its own loop body
+    (scripts/train.py:296-318: Adam, L1 + 0.4 SSIM) on synthetic pairs, then evaluated on two held-out pairs.  After those steps
+    the final sigmoid is no longer saturating (SSIM 0.06 -> 0.78), so the literal north_star bounds for bf16 (output and loss
+    within 1e-2 relative, SSIM within 1e-3, PSNR within 0.05 dB) can be asserted on it (tests/test_gpu_parity.py)."""
+    from oracle.unet_oracle import init_params
+    from oracle.synth import make_pairs
+    f = 16
+    model = UNetSuperRes(1, 1, base_filters=f)
+    model.load_state_dict(init_params(f, seed=1234), strict=True)
+    model.train()
+    opt = torch.optim.Adam(model.parameters(), lr=2e-3, weight_decay=1e-5)
+    crit = ref_losses.CombinedLoss(ssim_weight=0.4)
+    losses = []
+    for step in range(60):
+        x, t = make_pairs(4, 48, 48, seed=9000 + step % 16)
+        opt.zero_grad(set_to_none=True)
+        loss = crit(model(x), t)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    model.eval()
+    x, t = make_pairs(2, 64, 64, seed=777)
+    metric = ref_losses.SSIM(device=torch.device("cpu"))
+    with torch.no_grad():
+        out = model(x)
+        d = {"meta": np.array([f, 2, 64, 64]), "train_losses": np.array(losses),
+             "x_checksum": np.array([float(x.double().sum()), float(t.double().sum())]),
+             "out": out.numpy(), "loss": np.float64(crit(out, t).item()), "ssim": np.float64(metric(out, t).item()),
+             "mse": np.float64(((out - t) ** 2).mean().item())}
+    for k, v in model.state_dict().items():
+        d["param:" + k] = v.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, "trained_f16.npz"), **d)
+    print("trained_f16: loss", losses[0], "->", losses[-1], "eval ssim", d["ssim"])
+
+
+def perceptual_case_large(ref_losses):
+    """The VGG19[:36] branch at HR 256 x 256 (the 64 x 64 case leaves 4 x 4 images at the deepest layers: no multi-tile launch of the
+    512-channel kernels): features, perceptual value, total loss and the gradient wrt the prediction, stored as summaries;
+    inputs are re-derived from seeds by the test (checksums stored)."""
+    import torchvision.models as tvm
+    from oracle.losses_oracle import make_vgg_params
+    from oracle.synth import make_pairs
+    vggp = make_vgg_params(seed=1235)
+    orig = tvm.vgg19
+
+    def patched(weights=None, **kw):
+        m = orig(weights=None, **kw)
+        convs = [l for l in m.features if isinstance(l, torch.nn.Conv2d)]
+        with torch.no_grad():
+            for l, (wt, b) in zip(convs, vggp):
+                l.weight.copy_(wt)
+                l.bias.copy_(b)
+        return m
+
+    tvm.vgg19 = patched
+    try:
+        _, hr = make_pairs(1, 128, 128, seed=98)            # HR 256 x 256
+        g = torch.Generator("cpu").manual_seed(6)
+        pred0 = (hr + 0.1 * torch.randn(hr.shape, generator=g)).clamp(0, 1)
+        d = {"checksum": np.array([float(pred0.double().sum()), float(hr.double().sum())])}
+        crit = ref_losses.CombinedLoss(ssim_weight=0.4, perceptual_weight=0.1, perceptual_loss_type="l1")
+        p = pred0.clone().requires_grad_(True)
+        loss = crit(p, hr)
+        loss.backward()
+        with torch.no_grad():
+            feats = crit.perceptual_loss.feature_extractor(pred0)
+            perc = crit.perceptual_loss(pred0, hr)
+        d["loss"] = np.float64(loss.item())
+        d["perc"] = np.float64(perc.item())
+        _store_tensor(d, "feat", feats)
+        _store_tensor(d, "grad", p.grad)
+        d["grad_crop"] = p.grad[0, 0, 96:160, 96:160].numpy()
+        d["feat_shape"] = np.array(feats.shape)
+        np.savez_compressed(os.path.join(OUT, "perceptual_256.npz"), **d)
+        print("perceptual_256: loss", d["loss"], "perc", d["perc"], "feat", tuple(feats.shape))
+    finally:
+        tvm.vgg19 = orig
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(os.cpu_count() or 1)
@@ -220,6 +300,8 @@ def main():
     loss_cases(ref_losses)
     perceptual_case(ref_losses)
     train_case(UNetSuperRes, ref_losses)
+    trained_case(UNetSuperRes, ref_losses)
+    perceptual_case_large(ref_losses)
 
 
 if __name__ == "__main__":

@@ -134,3 +134,40 @@ def test_psnr_definition():
     a = torch.zeros(4, 4)
     assert LO.psnr(a, a) == 100.0
     assert abs(LO.psnr(a, a + 0.1) - 20.0) < 1e-4
+
+
+def test_oracle_matches_reference_on_trained_weights(golden_dir):
+    """tests/golden/trained_f16.npz: the reference model after 60 of its own training steps (oracle/make_golden.py:trained_case);
+    the oracle forward / loss / SSIM on those weights must reproduce the reference's evaluation."""
+    d = _load(golden_dir, "trained_f16")
+    f, n, h, w = [int(v) for v in d["meta"]]
+    params = {k[len("param:"):]: torch.from_numpy(v) for k, v in d.items() if k.startswith("param:")}
+    assert list(params.keys()) == [name for name, _ in UO.param_specs(f)]
+    x, t = make_pairs(n, h, w, seed=777)
+    np.testing.assert_allclose([float(x.double().sum()), float(t.double().sum())], d["x_checksum"], rtol=1e-12)
+    with torch.no_grad():
+        out = UO.unet_forward(params, x)
+    np.testing.assert_allclose(out.numpy(), d["out"], rtol=1e-5, atol=1e-6)
+    assert abs(float(LO.combined_loss(out, t, ssim_weight=0.4)) - float(d["loss"])) < 1e-6
+    assert abs(float(LO.ssim(out, t)) - float(d["ssim"])) < 1e-6
+    assert float(d["ssim"]) > 0.7 and d["train_losses"][-1] < 0.25 * d["train_losses"][0]       # really trained
+
+
+def test_vgg_oracle_matches_reference_at_256(golden_dir):
+    """tests/golden/perceptual_256.npz: reference CombinedLoss with the VGG19[:36] branch at HR 256 x 256 (seeded weights)."""
+    d = _load(golden_dir, "perceptual_256")
+    _, hr = make_pairs(1, 128, 128, seed=98)
+    g = torch.Generator("cpu").manual_seed(6)
+    pred = (hr + 0.1 * torch.randn(hr.shape, generator=g)).clamp(0, 1)
+    np.testing.assert_allclose([float(pred.double().sum()), float(hr.double().sum())], d["checksum"], rtol=1e-12)
+    vggp = LO.make_vgg_params(seed=1235)
+    p = pred.clone().requires_grad_(True)
+    loss = LO.combined_loss(p, hr, ssim_weight=0.4, perceptual_weight=0.1, vgg_params=vggp)
+    loss.backward()
+    assert abs(loss.item() - float(d["loss"])) < 1e-5 * float(d["loss"])
+    with torch.no_grad():
+        feat = LO.vgg_features(vggp, pred)
+    assert tuple(feat.shape) == tuple(int(v) for v in d["feat_shape"])
+    _check_tensor(d, "feat", feat, 1e-4, 1e-6)
+    _check_tensor(d, "grad", p.grad, 1e-3, 1e-9)
+    np.testing.assert_allclose(p.grad[0, 0, 96:160, 96:160].numpy(), d["grad_crop"], rtol=1e-3, atol=1e-9)
