@@ -113,6 +113,18 @@ int mrisr_l1_ssim_fwd_bwd(const float* pred, const float* target, float* dpred, 
 int mrisr_ssim_forward(const float* img1, const float* img2, float* per_sample, void* scratch,
                        int N, int H, int W, int window_size, float sigma, float val_range, void* stream);
 
+/* Allocation-free variant of mrisr_ssim_forward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same result as mrisr_ssim_forward; the kernel's block partials live in a file-scope `static __device__` array of
+ * mrisr_ssim_static_scratch_bytes() = 1 MiB that every GPU loading the library holds until the process exits, so the call
+ * takes no scratch pointer and performs no cudaMalloc / cudaFree / allocating library call.  Limit: 8 bytes per 32 x 32 tile,
+ * N * ceil(H/32) * ceil(W/32) * 8 <= 1 MiB (e.g. 128 slices of 1024 x 1024); larger problems return MRISR_E_SHAPE with a
+ * message naming the limit.  All calls on a device share the array: calls that overlap on the GPU (different streams, or
+ * concurrent graph branches) RACE -- serialise them on one stream.  Nothing in the array needs clearing between calls. */
+size_t mrisr_ssim_static_scratch_bytes(void);
+int mrisr_ssim_forward_static(const float* img1, const float* img2, float* per_sample, int N, int H, int W,
+                              int window_size, float sigma, float val_range, void* stream);
+
 /* ---- VGG perceptual term (replaces VGGFeatureExtractor / PerceptualLoss, utils/losses.py:83-151) ----------------
  * The feature network is a config list on the HOST: channels per 3x3 conv (+bias, +ReLU), -1 = MaxPool2d(2); the list must
  * end on a conv (vgg19.features[:36] = {64,64,-1,128,128,-1,256,256,256,256,-1,512,512,512,512,-1,512,512,512,512}).

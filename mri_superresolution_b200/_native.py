@@ -46,6 +46,8 @@ SIGNATURES = {
                                       c_float, c_float, c_int, c_float, c_float, c_void_p]),
     "mrisr_ssim_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                    c_int, c_float, c_float, c_void_p]),
+    "mrisr_ssim_static_scratch_bytes": (c_size_t, []),
+    "mrisr_ssim_forward_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_void_p]),
     "mrisr_unet_debug_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_void_p]),
     "mrisr_planar_geometry": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -511,3 +511,60 @@ int launch_ssim_forward(const float* a, const float* b, float* per_sample, void*
 }
 
 }  // namespace mrisr
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free SSIM metric (no counterpart in the reference; added for callers that
+// cannot allocate: code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernels as
+// launch_ssim_forward; the block partials go to a file-scope device array instead of caller scratch.  Every GPU that loads
+// the library holds the array (MRISR_SSIM_STATIC_SCRATCH_BYTES = 1 MiB) until the process exits.
+namespace mrisr {
+namespace {
+constexpr size_t kStaticScratchBytes = 1u << 20;      // 131 072 tiles of 32 x 32 pixels, e.g. 128 slices of 1024 x 1024
+static __device__ __align__(256) unsigned char g_ssim_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+
+// In host code `g_ssim_static_scratch` is a host-side stand-in, not a device address: the device address is looked up once per
+// device, with that device current, and cached.
+int static_scratch_ptr(float** out) {
+    static void* ptrs[kMaxDevices] = {};
+    int dev = -1;
+    MRISR_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { set_error("ssim_forward_static: device index %d out of range", dev); return -1; }
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        MRISR_CUDA_CHECK(cudaGetSymbolAddress(&p, g_ssim_static_scratch));
+        if (!p) { set_error("ssim_forward_static: cudaGetSymbolAddress returned a null address"); return -1; }
+        ptrs[dev] = p;
+    }
+    *out = (float*)ptrs[dev];
+    return 0;
+}
+}  // namespace
+
+size_t ssim_static_scratch_capacity() { return kStaticScratchBytes; }
+
+int launch_ssim_forward_static(const float* a, const float* b, float* per_sample, int N, int H, int W, int win, float sigma,
+                               float val_range, cudaStream_t s) {
+    const size_t need = partial_bytes(N, H, W);
+    if (need > kStaticScratchBytes) {
+        set_error("ssim_forward_static: N=%d H=%d W=%d needs %zu bytes of block partials, the static scratch holds %zu "
+                  "(use mrisr_ssim_forward with caller-owned scratch)", N, H, W, need, kStaticScratchBytes);
+        return -2;
+    }
+    float* partial = nullptr;
+    const int rc = static_scratch_ptr(&partial);
+    if (rc) return rc;
+    // nothing has to start at zero: every block of the launch overwrites its own (sum|a-b|, sum S) pair before the per-sample
+    // reduction reads exactly those pairs; whatever an earlier call left beyond them is never read
+    return launch_ssim_forward(a, b, per_sample, partial, N, H, W, win, sigma, val_range, s);
+}
+}  // namespace mrisr
+
+extern "C" int mrisr_ssim_forward_static(const float* img1, const float* img2, float* per_sample, int N, int H, int W,
+                                         int window_size, float sigma, float val_range, void* stream) {
+    using namespace mrisr;
+    if (!img1 || !img2 || !per_sample || N <= 0 || H <= 0 || W <= 0) { set_error("bad argument"); return -1; }
+    return launch_ssim_forward_static(img1, img2, per_sample, N, H, W, window_size, sigma, val_range, (cudaStream_t)stream);
+}
+
+extern "C" size_t mrisr_ssim_static_scratch_bytes(void) { return mrisr::ssim_static_scratch_capacity(); }
