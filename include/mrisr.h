@@ -162,6 +162,69 @@ int mrisr_adam_step_dev(float* params, const float* grads, float* exp_avg, float
                         float beta1, float beta2, float eps, float weight_decay, void* state32,
                         float grad_scale, void* stream);
 
+/* ---- on-device input pipeline: dense uint8 slices [N][H][W] in, float32 N x 1 x H x W out ----------
+ * Byte / index arithmetic reproduced bit for bit against the reference's PIL / numpy code (tests/test_gpu_preproc.py). */
+/* transforms.ToTensor() of utils/dataset.py:124-125: dst = src / 255 (float32 division) */
+int mrisr_u8_to_float(const uint8_t* src, float* dst, int64_t count, void* stream);
+/* preprocess_image of scripts/infer.py:97-130: per slice min = np.percentile(x, lower), max = np.percentile(x, upper) (numpy
+ * 'linear' method in float32, from a 256-bin histogram), clip, (x - min) / (max - min) when max > min (else the clipped raw
+ * values, as the reference leaves them).  minmax: N x 2 floats (device), receives (min, max) per slice.  H * W < 2^24. */
+int mrisr_percentile_normalize_u8(const uint8_t* src, float* dst, float* minmax, int N, int H, int W, float lower_percentile,
+                                  float upper_percentile, void* stream);
+/* augment_pair of utils/dataset.py:138-175 applied to one tensor of the pair (call once for the HR batch, once for the LR batch,
+ * with the same per-sample decisions): hflip -> rotate (Pillow NEAREST, 16.16 fixed point; fill = int(mean(x/255) * 255)) ->
+ * brightness -> contrast (Pillow ImageEnhance blends, truncating) -> additive noise (LR only) -> ToTensor.
+ * params: N x MRISR_AUG_PARAM_INTS int32 (device): [0] flip, [1] rotate on, [2..7] Pillow's affine matrix in 16.16 fixed point
+ *   (a0 a1 a2 / a3 a4 a5 with the half-pixel offset folded into a2, a5: utils/preprocess.py:pil_rotate_matrix), [8] brightness on,
+ *   [9] factor (float bits), [10] contrast on, [11] factor (float bits), [12] noise on, [13] noise std in gray levels (float
+ *   bits), [14] [15] Philox key.  The random DECISIONS are drawn on the host (a handful of scalars per sample, utils/dataset.py
+ *   draws them with Python's `random`); the pixels never leave the device.
+ * noise (nullable): N x H x W doubles added where noise is on (parity with np.random.normal arrays); NULL = Philox-4x32-10 +
+ *   Box-Muller on the device.  tmp: N*H*W bytes, sums: 2*N uint64 (device scratch).  dst (float32) and / or dst_u8 receive the
+ *   result.  H, W < 16384. */
+#define MRISR_AUG_PARAM_INTS 16
+int mrisr_augment_u8(const uint8_t* src, float* dst, uint8_t* dst_u8, uint8_t* tmp, uint64_t* sums, const int32_t* params,
+                     const double* noise, int N, int H, int W, void* stream);
+
+/* ---- batched evaluation ------------------------------------------------------------------------------
+ * calculate_metrics of scripts/test_comparison.py:164-202 without its SSIM (mrisr_ssim_forward): out4[n] = (MSE, RMSE, MAE,
+ * PSNR) of image n against reference n, both N x H x W float32; differences in float32 as the reference takes them, sums in
+ * float64; PSNR = 100 when MSE < 1e-10, else 10 log10(1 / MSE) (data_range 1). */
+size_t mrisr_image_metrics_scratch_bytes(int N, int H, int W);
+int mrisr_image_metrics(const float* reference, const float* image, float* out4, void* scratch, int N, int H, int W, void* stream);
+/* upscale_with_interpolation of scripts/test_comparison.py:92-134: cv2.resize(img, (2W, 2H)) on uint8 with method 0 = INTER_LINEAR,
+ * 1 = INTER_LINEAR followed by filter2D([[-1,-1,-1],[-1,9,-1],[-1,-1,-1]]) ("sharp_bilinear"), 2 = INTER_CUBIC; dst = result / 255
+ * (float32, N x 2H x 2W) and / or dst_u8.  Bit-exact against cv2 4.13's x86 build (fixed-point coefficients of 1/2048; the
+ * cubic vertical pass in float32 for groups of four columns, as its SIMD body does).  tmp: N*2H*2W bytes. */
+int mrisr_upscale2x_u8(const uint8_t* src, float* dst, uint8_t* dst_u8, uint8_t* tmp, int N, int H, int W, int method, void* stream);
+/* skimage.exposure.match_histograms(source[n], reference[n]) of scripts/infer.py:303-307 for N image pairs (float32; the
+ * reference image may have another size): out = interp(cdf_source(value), cdf_reference, reference values) in float64,
+ * stored as float32 (the caller clips to [0, 1], infer.py:309).  Sorting is cub::DeviceRadixSort inside caller scratch. */
+size_t mrisr_match_histograms_scratch_bytes(int N, int H, int W, int Href, int Wref);
+int mrisr_match_histograms(const float* source, const float* reference, float* out, void* scratch, size_t scratch_bytes, int N, int H,
+                           int W, int Href, int Wref, void* stream);
+
+/* ---- k-space low-field simulation ---------------------------------------------------------------------
+ * simulate_low_field_mri of utils/preprocessing.py:225-293 for N slices (float32 in [0,1], N x H x W): fft2 (single precision,
+ * as numpy 2.x transforms a float32 array) -> keep the centre int(H*f) x int(W*f) block of the shifted spectrum -> add complex
+ * Gaussian noise of standard deviation (noise_std / 255) * sqrt(H*W) / 10 (:271) -> ifft2 (complex128) -> magnitude ->
+ * min-max rescaled to the input slice's own range.  out: N x H x W float64.  noise_real / noise_imag (both or neither):
+ * N x H x W float64 arrays on the SHIFTED grid, exactly what np.random.normal would have produced (parity); NULL = Philox
+ * + Box-Muller on the device keyed by `seed`.  cuFFT plans are cached per (device, N, H, W) and work inside `scratch`. */
+size_t mrisr_kspace_scratch_bytes(int N, int H, int W);
+int mrisr_simulate_low_field(const float* data, double* out, const double* noise_real, const double* noise_imag, void* scratch,
+                             size_t scratch_bytes, int N, int H, int W, double kspace_crop_factor, double noise_std,
+                             uint64_t seed, void* stream);
+/* utils/extraction_utils.py:143-165: [clip(x, 0, 1) ->] cv2.resize(INTER_AREA) to exactly half size on float64 (H, W even)
+ * [-> clip(x * 255, 0, 255) truncated to uint8, the PNG the reference writes].  dst (float64) and / or dst_u8: N x H/2 x W/2. */
+int mrisr_area_half_f64(const double* src, double* dst, uint8_t* dst_u8, int N, int H, int W, int clip01, void* stream);
+/* robust_normalize of utils/preprocessing.py:126-163 on N float64 slices: np.percentile(lower / upper) (float64, order
+ * statistics from a segmented sort in scratch), clip, min-max to [target_lo, target_hi], float32 result; constant slices give
+ * zeros.  window (nullable): N x 2 float64 (lower, upper). */
+size_t mrisr_robust_normalize_scratch_bytes(int N, int H, int W);
+int mrisr_robust_normalize_f64(const double* src, float* dst, double* window, void* scratch, size_t scratch_bytes, int N, int H, int W,
+                               double lower_percentile, double upper_percentile, double target_lo, double target_hi, void* stream);
+
 /* ---- convolution building block over padded NHWC bf16 tensors ---------------------------------
  * The implicit-GEMM kernels behind every nn.Conv2d of models/unet_model.py:29,34,72,101,152,168 (and of the VGG19
  * feature stack, utils/losses.py:90-95), exposed one layer at a time: the parity tests call them with both engines.

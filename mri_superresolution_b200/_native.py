@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes
 import os
 import subprocess
-from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p
+from ctypes import c_char_p, c_double, c_float, c_int, c_int64, c_size_t, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # MRISR_B200_VARIANT=<name> loads lib/libmrisr_b200_<name>.so, a staged build made with `make VARIANT=<name> EXTRA=-D...`
@@ -48,6 +48,21 @@ SIGNATURES = {
                                    c_int, c_float, c_float, c_void_p]),
     "mrisr_ssim_static_scratch_bytes": (c_size_t, []),
     "mrisr_ssim_forward_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    "mrisr_u8_to_float": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "mrisr_percentile_normalize_u8": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    "mrisr_augment_u8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "mrisr_image_metrics_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mrisr_image_metrics": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "mrisr_upscale2x_u8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_match_histograms_scratch_bytes": (c_size_t, [c_int] * 5),
+    "mrisr_match_histograms": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_kspace_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mrisr_simulate_low_field": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                         c_double, c_double, c_uint64, c_void_p]),
+    "mrisr_area_half_f64": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mrisr_robust_normalize_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mrisr_robust_normalize_f64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                           c_double, c_double, c_double, c_double, c_void_p]),
     "mrisr_unet_debug_tensor": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_void_p]),
     "mrisr_planar_geometry": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),

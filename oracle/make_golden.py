@@ -290,6 +290,93 @@ def perceptual_case_large(ref_losses):
         tvm.vgg19 = orig
 
 
+def preproc_case():
+    """Input-pipeline goldens from the reference's own code: scripts/infer.py preprocess_image (needs
+    matplotlib / skimage at import: stubbed, they are not on its path) on PNG files, and utils/dataset.py
+    MRISuperResDataset.augment_pair + transforms.ToTensor under seeded `random` / `np.random`."""
+    import random
+    import tempfile
+    from unittest import mock
+    from PIL import Image
+    for name in ("matplotlib", "matplotlib.pyplot", "skimage", "skimage.exposure", "skimage.metrics", "nibabel"):
+        sys.modules.setdefault(name, mock.MagicMock())
+    sys.path.insert(0, REF)
+    sys.path.insert(0, os.path.join(REF, "scripts"))
+    from scripts.infer import preprocess_image
+    from utils.dataset import MRISuperResDataset
+    import torchvision.transforms as T
+    sys.path.pop(0)
+    sys.path.pop(0)
+    rng = np.random.default_rng(2024)
+    d = {}
+    shapes = [(64, 48), (40, 72), (17, 23), (32, 32)]
+    with tempfile.TemporaryDirectory() as tmp:
+        for i, (h, w) in enumerate(shapes):
+            if i == 3:
+                img = np.full((h, w), 77, np.uint8)                      # constant image: max == min, left un-normalised
+            elif i == 2:
+                img = rng.integers(0, 256, (h, w)).astype(np.uint8)       # flat histogram: the percentiles fall between levels
+            else:
+                img = rng.normal(90 + 30 * i, 45, (h, w)).clip(0, 255).astype(np.uint8)
+            path = os.path.join(tmp, f"s{i}.png")
+            Image.fromarray(img).save(path)
+            _, t = preprocess_image(path)
+            d[f"pp{i}:img"] = img
+            d[f"pp{i}:out"] = t[0, 0].numpy()
+    ds = object.__new__(MRISuperResDataset)
+    ds.aug_params = {"flip_prob": 0.5, "rotate_prob": 0.5, "rotate_range": (-5, 5), "brightness_prob": 0.3, "brightness_range": (0.9, 1.1),
+                     "contrast_prob": 0.3, "contrast_range": (0.9, 1.1), "noise_prob": 0.2, "noise_std": 0.01}
+    to_tensor = T.ToTensor()
+    seeds = [7, 8, 4, 24, 736, 5, 10, 50]          # chosen so that every branch (and all / none together) occurs
+    d["aug:seeds"] = np.array(seeds)
+    for i, seed in enumerate(seeds):
+        h, w = 24 + 8 * (i % 3), 40 - 8 * (i % 2)
+        hr = rng.normal(110, 50, (2 * h, 2 * w)).clip(0, 255).astype(np.uint8)
+        lr = rng.normal(110, 50, (h, w)).clip(0, 255).astype(np.uint8)
+        random.seed(seed)
+        np.random.seed(seed)
+        f, l = ds.augment_pair(Image.fromarray(hr), Image.fromarray(lr))
+        d[f"aug{i}:hr"], d[f"aug{i}:lr"] = hr, lr
+        d[f"aug{i}:out_hr"], d[f"aug{i}:out_lr"] = np.array(f), np.array(l)
+        d[f"aug{i}:tensor_lr"] = to_tensor(l)[0].numpy()
+    np.savez_compressed(os.path.join(OUT, "preproc.npz"), **d)
+    print("preproc: ", len(shapes), "preprocess cases,", len(seeds), "augmented pairs")
+
+
+def eval_case():
+    """Evaluation / LR-synthesis goldens: cv2's own x2 upscalers as scripts/test_comparison.py:92-134
+    calls them, and the reference's utils/preprocessing.py robust_normalize / simulate_low_field_mri / letterbox_resize(AREA)
+    under a seeded np.random (the two normal draws are stored so that the other side can be fed the same noise)."""
+    import cv2
+    sys.path.insert(0, REF)
+    from utils.preprocessing import InterpolationMethod, letterbox_resize, robust_normalize, simulate_low_field_mri
+    sys.path.pop(0)
+    rng = np.random.default_rng(77)
+    d = {}
+    kern = np.array([[-1, -1, -1], [-1, 9, -1], [-1, -1, -1]])
+    for i, (h, w) in enumerate([(48, 64), (33, 21), (7, 5)]):
+        img = rng.normal(120, 60, (h, w)).clip(0, 255).astype(np.uint8)
+        d[f"up{i}:img"] = img
+        lin = cv2.resize(img, (2 * w, 2 * h), interpolation=cv2.INTER_LINEAR)
+        d[f"up{i}:bilinear"] = lin
+        d[f"up{i}:sharp_bilinear"] = np.clip(cv2.filter2D(lin, -1, kern), 0, 255)
+        d[f"up{i}:bicubic"] = cv2.resize(img, (2 * w, 2 * h), interpolation=cv2.INTER_CUBIC)
+    for i, (h, w) in enumerate([(64, 64), (48, 80)]):
+        vol = rng.gamma(2.0, 150.0, (h, w))                                   # NIfTI-like intensities, float64
+        norm = robust_normalize(vol)
+        np.random.seed(100 + i)
+        sim = simulate_low_field_mri(norm, kspace_crop_factor=0.5, noise_std=5)
+        np.random.seed(100 + i)
+        sd = (5 / 255.0) * np.sqrt(h * w) / 10
+        nr, ni = np.random.normal(0, sd, (h, w)), np.random.normal(0, sd, (h, w))
+        lr = letterbox_resize(np.clip(sim, 0, 1), (w // 2, h // 2), interpolation=InterpolationMethod.AREA)
+        d[f"ks{i}:vol"], d[f"ks{i}:norm"], d[f"ks{i}:sim"] = vol, norm, sim
+        d[f"ks{i}:noise_re"], d[f"ks{i}:noise_im"] = nr, ni
+        d[f"ks{i}:lr_u8"] = np.clip(lr * 255, 0, 255).astype(np.uint8)
+    np.savez_compressed(os.path.join(OUT, "eval.npz"), **d)
+    print("eval: 3 upscaler cases, 2 k-space cases")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(os.cpu_count() or 1)
@@ -302,6 +389,8 @@ def main():
     train_case(UNetSuperRes, ref_losses)
     trained_case(UNetSuperRes, ref_losses)
     perceptual_case_large(ref_losses)
+    preproc_case()
+    eval_case()
 
 
 if __name__ == "__main__":
