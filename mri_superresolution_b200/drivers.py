@@ -51,7 +51,7 @@ class TrainConfig:
                  perceptual_weight: float = 0.0, vgg_layer_idx: int = 35, perceptual_loss_type: str = "l1",
                  base_filters: int = 32, initial_alpha: float = 0.0, patience: int = 20, checkpoint_dir: str = "./checkpoints",
                  model_type: str = "unet", seed: Optional[int] = None, use_graph: bool = True, precision: str = "bf16",
-                 vgg_weights=None, batch_size: Optional[int] = None):
+                 vgg_weights=None, batch_size: Optional[int] = None, augmentation: bool = False, augmentation_params=None):
         if model_type != "unet":
             raise ValueError(f"Unknown model type: {model_type}")             # scripts/train.py:175
         self.__dict__.update(locals())
@@ -77,10 +77,24 @@ def _device_batches(batches: Iterable, device) -> Iterable:
     return DevicePrefetcher(pinned, device)
 
 
+def _to_float_pairs(low_res, high_res, augmenter):
+    """uint8 batches (data.UInt8BatchLoader: low N x H x W, full N x 2H x 2W gray levels) become the float32 N x 1 x . x . pair
+    of ``MRISuperResDataset.__getitem__`` ON THE DEVICE: ``augment_pair`` + ``ToTensor`` (utils/dataset.py:122-136) through
+    utils/preprocess.py; float batches pass through."""
+    if low_res.dtype != torch.uint8:
+        return low_res, high_res
+    from .utils.preprocess import to_tensor
+    if augmenter is not None:
+        return augmenter(high_res, low_res)
+    return to_tensor(low_res), to_tensor(high_res)
+
+
 def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: Callable[[], Iterable], device=None,
           model: Optional[UNetSuperRes] = None, log_stream=None) -> Dict:
     """Epoch loop of scripts/train.py:278-477.  ``train_batches()`` / ``val_batches()`` return a fresh iterable of
-    ``(low_res N x 1 x H x W, high_res N x 1 x 2H x 2W)`` pairs per epoch (a DataLoader, a list, a generator).
+    ``(low_res N x 1 x H x W, high_res N x 1 x 2H x 2W)`` pairs per epoch (a DataLoader, a list, a generator), float32 in [0, 1] -- or uint8 gray levels
+    (low N x H x W, full N x 2H x 2W, e.g. data.UInt8BatchLoader): then ToTensor and, with ``cfg.augmentation``, the reference's
+    augment_pair run on the device (utils/preprocess.py).
     Returns ``{'final_path', 'best_path', 'history'}``; ``history`` holds the printed epoch summaries.
 
     Data parallel (new; the reference is single-device): call under ``torchrun`` after ``dist.init_process_group("nccl")``;
@@ -131,6 +145,11 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
             return comp[1]
         return ssim_metric(output, high_res)
 
+    augmenter = None
+    if getattr(cfg, "augmentation", False):
+        from .utils.preprocess import PairAugmenter
+        augmenter = PairAugmenter(getattr(cfg, "augmentation_params", None))      # draws from `random` like the reference (:142-166)
+
     for epoch in range(cfg.epochs):
         t0 = time.time()
         model.train()                                                          # :285
@@ -142,6 +161,7 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
         total = len(batches)
         every = max(10, total // 10)
         for batch_idx, (low_res, high_res) in enumerate(_device_batches(batches, device)):
+            low_res, high_res = _to_float_pairs(low_res, high_res, augmenter)
             shape = (tuple(low_res.shape), tuple(high_res.shape))
             if cfg.use_graph and graphed is None:
                 from .utils.graph import GraphedTrainStep
@@ -172,6 +192,7 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
         nv = 0
         with torch.no_grad():
             for low_res, high_res in _device_batches(val_batches(), device):
+                low_res, high_res = _to_float_pairs(low_res, high_res, None)       # validation is never augmented
                 output = model(low_res)
                 sums[0] += criterion(output, high_res)
                 sums[1] += metric_of(output, high_res)

@@ -468,3 +468,76 @@ def test_workspace_cache_never_drops_a_pinned_entry():
     assert not any(c.pinned(k) for k in c.keys())
     c.clear()
     assert len(c) == 0
+
+
+def _write_png_pairs(root, n, h=16, w=24, seed=0):
+    from PIL import Image
+    rng = np.random.default_rng(seed)
+    hr_dir, lr_dir = os.path.join(root, "hr"), os.path.join(root, "lr")
+    os.makedirs(hr_dir), os.makedirs(lr_dir)
+    for i in range(n):
+        name = f"sub-HC{i // 3:03d}_ses-01_T1map.nii_s{i:03d}.png"
+        Image.fromarray(rng.integers(0, 256, (2 * h, 2 * w)).astype(np.uint8)).save(os.path.join(hr_dir, name))
+        Image.fromarray(rng.integers(0, 256, (h, w)).astype(np.uint8)).save(os.path.join(lr_dir, name))
+    return hr_dir, lr_dir
+
+
+def test_png_pair_dataset_split_and_sharded_loader(tmp_path):
+    """data.py against the reference's rules: pair discovery / subject ids (utils/dataset.py:37-67), the random_split partition
+    for a seed (scripts/train.py:205-213), ragged last batch single-process, equal shards under data parallelism."""
+    import torch
+    from torch.utils.data import random_split
+    from mri_superresolution_b200.data import PairedPNGDataset, UInt8BatchLoader, split_indices
+    hr_dir, lr_dir = _write_png_pairs(str(tmp_path), 11)
+    open(os.path.join(hr_dir, "notes.txt"), "w").close()
+    ds = PairedPNGDataset(hr_dir, lr_dir)
+    assert len(ds) == 11 and ds.subjects[0] == "HC000" and ds.subjects[10] == "HC003"
+    assert ds.get_subject_indices("HC001") == [3, 4, 5]
+    tr, va = split_indices(len(ds), 0.2, seed=42)
+    ref_tr, ref_va = random_split(range(11), [9, 2], generator=torch.Generator().manual_seed(42))
+    assert tr == list(ref_tr.indices) and va == list(ref_va.indices)
+    low, full = ds.load(3)
+    assert low.dtype == np.uint8 and low.shape == (16, 24) and full.shape == (32, 48)
+    batches = list(UInt8BatchLoader(ds, tr, 4, shuffle=False, num_workers=2))
+    assert [b[0].shape[0] for b in batches] == [4, 4, 1]                       # no drop_last, like the reference's DataLoader
+    assert batches[0][0].dtype == torch.uint8 and batches[0][1].shape == (4, 32, 48)
+    assert np.array_equal(batches[0][0][1].numpy(), ds.load(tr[1])[0])
+    shards = [list(UInt8BatchLoader(ds, tr, 2, shuffle=True, seed=5, num_workers=0, rank=r, world=2)) for r in range(2)]
+    assert len(shards[0]) == len(shards[1]) == 2                               # 9 pairs -> two global batches of 4, one pair dropped
+    seen = torch.cat([b[0].reshape(b[0].shape[0], -1)[:, :8] for s in shards for b in s])
+    assert len({tuple(r.tolist()) for r in seen}) == 8                         # disjoint shards
+    e1 = [b[0] for b in UInt8BatchLoader(ds, tr, 4, shuffle=True, seed=1, num_workers=0)]
+    e2 = [b[0] for b in UInt8BatchLoader(ds, tr, 4, shuffle=True, seed=1, num_workers=0)]
+    assert all(torch.equal(a, b) for a, b in zip(e1, e2))                      # seeded order
+
+
+def test_reference_import_names_resolve_to_the_drop_in_modules():
+    """compat/: `from models.unet_model import UNetSuperRes`, `from utils.losses import CombinedLoss, SSIM` (scripts/train.py:26-33)
+    give the B200 classes when the directory is first on sys.path."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys; sys.path.insert(0, %r); sys.path.insert(1, %r)\n"
+            "from models.unet_model import UNetSuperRes\nfrom utils.losses import CombinedLoss, SSIM, ssim, PerceptualLoss\n"
+            "from utils.dataset import MRISuperResDataset\n"
+            "print(UNetSuperRes.__module__, CombinedLoss.__module__, SSIM.__module__)\n") % (
+                os.path.join(root, "mri_superresolution_b200", "compat"), root)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd="/tmp")
+    assert res.returncode == 0, res.stderr
+    assert res.stdout.split() == ["mri_superresolution_b200.models.unet_model", "mri_superresolution_b200.utils.losses",
+                                  "mri_superresolution_b200.utils.losses"]
+
+
+def test_cli_argument_surface_matches_the_reference():
+    """Same flags and defaults as scripts/train.py:486-548 and scripts/infer.py:452-490."""
+    from mri_superresolution_b200 import infer as I
+    from mri_superresolution_b200 import train as T
+    a = T.parse_args(["--full_res_dir", "hr", "--low_res_dir", "lr"])
+    assert (a.model_type, a.base_filters, a.batch_size, a.epochs, a.learning_rate, a.weight_decay, a.ssim_weight, a.perceptual_weight,
+            a.vgg_layer_idx, a.perceptual_loss_type, a.initial_alpha, a.validation_split, a.patience, a.checkpoint_dir, a.log_dir) == (
+        "unet", 32, 8, 100, 1e-4, 1e-5, 0.3, 0.0, 35, "l1", 0.0, 0.2, 10, "./checkpoints", "./logs")
+    assert not (a.augmentation or a.use_tensorboard or a.use_amp or a.cpu) and 1 <= a.seed <= 10000
+    b = I.parse_args(["--input", "x.png", "--output", "y.png"])
+    assert (b.target, b.checkpoint_dir, b.checkpoint_path, b.model_type, b.base_filters) == (None, "./checkpoints", None, "unet", 64)
+    with pytest.raises(SystemExit):
+        T.parse_args(["--full_res_dir", "hr", "--low_res_dir", "lr", "--model_type", "cnn"])
