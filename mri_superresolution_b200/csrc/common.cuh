@@ -28,6 +28,13 @@ const char* g_err_ptr();
 void count_launch();
 #define MRISR_LAUNCH_CHECK() do { ::mrisr::count_launch(); MRISR_CUDA_CHECK(cudaGetLastError()); } while (0)
 
+// cudaFuncSetAttribute (shared-memory opt-in, cluster size) is per device: a one-time flag must be kept per device, or a process
+// that touches a second GPU launches there without the opt-in.
+struct PerDeviceFlag {
+    bool f[64] = {};
+    bool& cur() { int d = 0; if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) d = 0; return f[d]; }
+};
+
 // Optional per-kernel-family timing (mrisr_prof_* in include/mrisr.h): when enabled, each launcher brackets its
 // launches with CUDA events on the launching stream; mrisr_prof_report() sums them per tag after a sync.
 // Disabled (the default) it costs one predictable branch.

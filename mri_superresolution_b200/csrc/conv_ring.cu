@@ -377,7 +377,7 @@ static RingPlan ring_plan(int W, int Cin, int Cout) {
 
 template <int BN, int KP, int G>
 static int launch_ring_cfg(const ConvRingParams& p, int grid, uint32_t smem, cudaStream_t s) {
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_ring_kernel<BN, KP, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_done = true;

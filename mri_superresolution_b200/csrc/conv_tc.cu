@@ -483,7 +483,7 @@ template <int BN, int BK>
 static int launch_wres(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB, const ConvTcParams& p, int grid,
                        cudaStream_t s) {
     using Cfg = ConvTcCfg<BN, BK, true>;
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
         attr_done = true;
@@ -519,7 +519,7 @@ static int launch_cfg(const CUtensorMap& tA1, const CUtensorMap& tA2, const CUte
             return launch_wres<BN, BK>(tA1, tA2, tB, q, grid, s);
         }
     }
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<BN, BK, MERGE3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_done = true;
@@ -545,10 +545,11 @@ static int launch_bn(int bk, bool merge3, const CUtensorMap& tA1, const CUtensor
 }
 
 int num_sms() {
-    static int n = 0;
+    static int cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    int& n = cache[dev];                       // per device: a process may drive GPUs with different SM counts
     if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
         if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
     }
     return n;

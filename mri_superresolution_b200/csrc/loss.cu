@@ -347,7 +347,7 @@ int run_split(const float* pred, const float* tgt, float* dpred, float* partial,
               const Taps& taps, float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
     constexpr int IN = T + 2 * R;
     const size_t smem_f = (size_t)(2 * IN * IN + 5 * IN * T) * sizeof(float), smem_g = (size_t)(3 * IN * IN + 3 * IN * T) * sizeof(float);
-    static bool configured = false;
+    static PerDeviceFlag configured_pd; bool& configured = configured_pd.cur();
     if (!configured) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(ssim_fwd_maps_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(ssim_grad_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
@@ -436,7 +436,7 @@ template <int R, bool GRAD>
 int run(const float* pred, const float* tgt, float* dpred, float* partial, int N, int H, int W, const Taps& taps,
         float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
     const size_t smem = Geo<R, GRAD>::smem_floats * sizeof(float);
-    static bool configured = false;   // attribute is per-function, idempotent
+    static PerDeviceFlag configured_pd; bool& configured = configured_pd.cur();   // attribute is per-function, idempotent
     if (!configured) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(l1_ssim_kernel<R, GRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;

@@ -551,7 +551,7 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         UpBwdTile tp;
         size_t smem = 0;
         if (up_bwd_plan(ddst, dsrc, tp, smem)) {
-            static bool attr_done = false;
+            static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
             if (!attr_done) {
                 MRISR_CUDA_CHECK(cudaFuncSetAttribute(upsample2x_bwd_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
                 attr_done = true;

@@ -313,7 +313,7 @@ int launch_wgrad_ring(const WgradArgs<bf16>& a, cudaStream_t s) {
     p.R = pl.R; p.halo_lo = pl.halo_lo; p.halo_hi = pl.halo_hi; p.tmem_cols = pl.tmem_cols;
     for (int t = 0; t < 9; ++t) p.sh[t] = pl.halo_lo * 128 + (p.taps == 9 ? (t / 3 - 1) * p.pw + (t % 3 - 1) : 0);
     const int grid = ceil_div(p.num_tiles, p.tiles_per_cta);
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024));
         attr_done = true;

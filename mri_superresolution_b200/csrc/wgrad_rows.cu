@@ -313,17 +313,17 @@ static int wgrad_rows_launch_group(const bf16* x, int64_t csx, int KP, const Wgr
     p.H = H; p.pw = W + 2; p.S = (H + 2) * (W + 2);
     p.SW = pl.SW; p.strips = pl.strips; p.RC = pl.RC; p.chunks = pl.chunks; p.units = pl.units;
     p.R = pl.R; p.tiles = pl.tiles; p.PLB = pl.PLB; p.seg_bytes = pl.seg_bytes; p.tmem_cols = pl.tmem_cols;
-    static bool attr_done[2] = {false, false};
+    static PerDeviceFlag attr_pd[2]; bool attr_done_v[2] = {attr_pd[0].cur(), attr_pd[1].cur()}; bool* attr_done = attr_done_v;
     if (KP == 2) {
         if (!attr_done[0]) {
             MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_rows_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-            attr_done[0] = true;
+            attr_pd[0].cur() = true;
         }
         tc::wgrad_rows_kernel<2><<<pl.grid, 192, pl.smem_bytes, s>>>(p);
     } else {
         if (!attr_done[1]) {
             MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-            attr_done[1] = true;
+            attr_pd[1].cur() = true;
         }
         tc::wgrad_rows_kernel<4><<<pl.grid, 192, pl.smem_bytes, s>>>(p);
     }

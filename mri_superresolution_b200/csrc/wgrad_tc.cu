@@ -299,7 +299,7 @@ int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
     const int cols = pl.MT * Cout;
     p.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
 
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024));
         attr_done = true;

@@ -275,7 +275,7 @@ int launch_wgrad_tc3(const WgradArgs<bf16>& a, cudaStream_t s) {
     p.stage_bytes = pl.stage_bytes; p.b_bytes = (uint32_t)Cout * tc::kBKP3 * 2u;
     p.idesc = tc::make_idesc_bf16(128, Cout, 1, 1);
     p.tmem_cols = pl.tmem_cols;
-    static bool attr_done = false;
+    static PerDeviceFlag attr_done_pd; bool& attr_done = attr_done_pd.cur();
     if (!attr_done) {
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc3_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         MRISR_CUDA_CHECK(cudaFuncSetAttribute(tc::wgrad_tc3_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
