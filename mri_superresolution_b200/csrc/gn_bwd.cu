@@ -325,7 +325,11 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
 // Measured on B200 (batch 64, profiles/r01_gn_bwd_fused.md): clusters of 2 are fastest (gn_bwd 6.8 -> 5.0 ms per step); larger
 // clusters lose more to gang scheduling than their bigger shared-memory share of a unit wins back, and with 2 CTAs the
 // operands kept in shared memory between the phases (K slots) are a few percent of a unit, so the second phase still
-// re-reads most operands (5 passes, now at ~70% of the HBM copy rate instead of 45%).  MRISR_GNBWD_CS
+// re-reads most operands (5 passes, now at ~70% of the HBM copy rate instead of 45%).  A persistent "streamed" form that sizes the
+// units in flight to the L2 (groups of CTAs per unit, arrival counters instead of cluster barriers, the next unit's reduce between
+// arrive and wait) was built and measured in round 2 and LOST (gn_bwd 4.6 -> 7.2 ms per step): the L2 budget forces ~110 KB
+// phases per CTA, whose fixed per-phase instructions made it issue-bound (66 % issue-active, L2 hit rate 30 %, DRAM traffic still
+// 4.2 passes); deleted, numbers in profiles/r02_gn_bwd_stream.md.  MRISR_GNBWD_CS
 // reproduces the cluster-size sweep.
 constexpr int kFtMax = 512;             // threads per CTA of the fused kernel: 512 (2 CTAs / SM) or 256 (4 CTAs / SM)
 constexpr int kMaxUnitCh = 512;         // channels of one unit
@@ -770,275 +774,6 @@ __global__ void __launch_bounds__(FT, (KindTraits<KIND>::pool ? 1 : 2) * (512 / 
     }
 }
 
-// ------------------------------------------------------------------------------------------------------------------
-// Streamed form (bf16, one-pixel kinds): the same reduce -> constants -> apply, organised so that the second read of (r, g)
-// comes from L2 instead of HBM.  The cluster kernel above keeps #SMs x 2 CTAs x (1 MB of a unit) = ~300 MB in flight, so by the
-// time a cluster applies dr its operands have left the 126 MB L2 (measured: 4.45 tensor passes of DRAM traffic instead of 3).
-// Here a persistent grid of (#SMs x 2) CTAs is cut into B = grid / G logical groups of G CTAs; a group owns one unit at a
-// time and G is chosen so that the units in flight (B being reduced + B being applied) fit ~64 MB.  Groups synchronise through
-// a per-unit arrival counter in global memory instead of a cluster barrier, and a CTA never idles at it:
-//     reduce(u0) arrive(u0) | reduce(u1) arrive(u1) | wait(u0) apply(u0) | reduce(u2) arrive(u2) | wait(u1) apply(u1) | ...
-// i.e. between arriving for a unit and needing everybody else's partial sums it reduces the next unit.  Partial sums go through
-// global memory in rank order (deterministic); the parameter-gradient finalize kernel reads the same partials.
-struct StreamParams {
-    int G, B, units, ncv, ups, rows_pc;
-    double inv_count;
-    TrkStep ts;
-    int psr, psg, psd;
-    int* flags;                  // [units] arrival counters (zeroed before the launch) + [1] time-out marker
-};
-
-__device__ __forceinline__ int ld_acquire(const int* p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ float ld_cg(const float* p) {
-    float v;
-    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-    return v;
-}
-
-template <int KIND, int FT, int S, bool SECOND>
-__device__ __forceinline__ void stream_phase(const GnBwdArgs<__nv_bfloat16>& a, const StreamParams& sp, int u, int rank, uint4* cache,
-                                             float* s_w, double (*s_tot)[kMaxUnitCh], float* s_q, float* s_p, float* s_wdl) {
-    using T = __nv_bfloat16;
-    constexpr bool kIncr = Incr<KIND>::on;
-    constexpr int RAWV = 2, NW = FT / 32;
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int ncv = sp.ncv, nchl = ncv * 8;
-    const int n = u / sp.ups, cv0 = (u % sp.ups) * ncv;
-    const int C = a.r.C, gs = C / kGroups;
-    const int UW = a.r.W, UH = a.r.H;
-    const int r0 = min(UH, rank * sp.rows_pc), r1 = min(UH, r0 + sp.rows_pc);
-    const int npx = (r1 - r0) * UW;
-    const int cvl = tid % ncv, cv = cv0 + cvl;
-    const int p0 = tid / ncv, pstep = FT / ncv;
-    const int nu = p0 < npx ? (npx - p0 + pstep - 1) / pstep : 0;
-    const int64_t row = (int64_t)(C + 8);
-
-    ChanCtx c;
-    load_ctx<T, KIND>(a, n, cv, c);
-    float al = 0.f, wv[8];
-    if (KIND == SRC_BLEND_BIL) al = 1.f / (1.f + __expf(-a.alpha[0]));
-    if (KIND == SRC_BLEND_PS) al = 1.f - 1.f / (1.f + __expf(-a.alpha[0]));
-#pragma unroll
-    for (int k = 0; k < 8; ++k) wv[k] = KIND == SRC_OUTER ? a.wvec[cv * 8 + k] : 0.f;
-
-    [[maybe_unused]] const int pitch = a.r.W + 2, gpitch = a.g.W + 2;
-    [[maybe_unused]] const T* rb = nullptr; [[maybe_unused]] const T* gb = nullptr; [[maybe_unused]] T* db = nullptr;
-    if constexpr (kIncr) {
-        rb = a.r.at(n, r0, 0, cv * 8);
-        db = a.dr.at(n, r0, 0, cv * 8);
-        gb = a.g.at(n, r0, 0, a.coff + cv * 8);
-    }
-    auto issue = [&](int i, int sidx, const UnitTrk& t) {
-        uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
-        if constexpr (kIncr) {
-            cp_async16(sl, rb + t.px * sp.psr);
-            cp_async16(sl + FT, gb + t.px * sp.psg);
-            return;
-        }
-        const int pi = p0 + i * pstep;
-        int uy, ux;
-        unit_row_col(pi, UW, uy, ux);
-        uy += r0;
-        cp_async16(sl, a.r.at(n, uy, ux, cv * 8));
-        uint4* sa = sl + FT;
-        if (KIND == SRC_DIRECT) {
-            cp_async16(sa, a.g.at(n, uy, ux, a.coff + cv * 8));
-        } else if (KIND == SRC_BLEND_BIL) {
-            cp_async16(sa, a.g.at(n, uy, ux, cv * 8));
-        } else if (KIND == SRC_BLEND_PS) {
-#pragma unroll
-            for (int ij = 0; ij < 4; ++ij)
-                cp_async4(reinterpret_cast<uint32_t*>(sa) + ij, a.g.at(n, 2 * uy + (ij >> 1), 2 * ux + (ij & 1), 2 * cv));
-        } else if (KIND == SRC_OUTER) {
-            const int64_t pix = ((int64_t)n * a.r.H + uy) * a.r.W + ux;
-            cp_async4(reinterpret_cast<uint32_t*>(sa), a.y + pix);
-            cp_async4(reinterpret_cast<uint32_t*>(sa) + 1, a.dy + pix);
-        }
-    };
-    UnitTrk ti{0, 0, 0, 0}, ta{0, 0, 0, 0};
-    if constexpr (kIncr) { ti = trk_at(p0, UW, pitch, UW + 2, gpitch); ta = ti; }
-#pragma unroll
-    for (int i = 0; i < S; ++i) {
-        if (i < nu) {
-            issue(i, i, ti);
-            if constexpr (kIncr) trk_fwd(ti, sp.ts, UW);
-        }
-        cp_async_commit();
-    }
-    [[maybe_unused]] float cq[8], cp[8];
-    if constexpr (SECOND) {
-        // everybody's partial sums of this unit, in rank order, then the constants of the unit's groups
-        if (tid == 0) {
-            const long long t0 = clock64();
-            while (ld_acquire(sp.flags + u) < sp.G) {
-                if (clock64() - t0 > (1ll << 33)) { sp.flags[sp.units] = 1; break; }      // ~4 s: a lost CTA must not hang the GPU
-                __nanosleep(64);
-            }
-        }
-        __syncthreads();
-        // all G x 2 x nchl partials are fetched in parallel (independent loads, a few per thread; a serial walk over the ranks
-        // costs an L2 latency per rank, longer than the phase itself), staged in s_w, then summed in rank order
-        {
-            const int per = 2 * nchl, total = per * sp.G;
-            const float* base = a.part + ((int64_t)n * sp.G) * 3 * row + cv0 * 8;
-            for (int i = tid; i < total; i += FT) {
-                const int rk = i / per, wc = i % per;
-                s_w[i] = ld_cg(base + (int64_t)rk * 3 * row + (wc / nchl) * row + (wc % nchl));
-            }
-            __syncthreads();
-            if (tid < per) {
-                double t = 0.0;
-                for (int rk = 0; rk < sp.G; ++rk) t += (double)s_w[rk * per + tid];
-                s_tot[tid / nchl][tid % nchl] = t;
-            }
-            __syncthreads();
-        }
-        const int ngl = nchl / gs;
-        if (tid < ngl) {
-            const int g = (cv0 * 8) / gs + tid, ng = n * kGroups + g;
-            const double mean = (double)a.stats[ng * 2], rstd = (double)a.stats[ng * 2 + 1];
-            double m1 = 0.0, m2 = 0.0;
-            for (int j = 0; j < gs; ++j) {
-                const int chl = tid * gs + j, ch = cv0 * 8 + chl;
-                const double gm = (double)a.gamma[KIND == SRC_BLEND_PS ? ch / 4 : ch];
-                m1 += gm * s_tot[0][chl];
-                m2 += gm * (s_tot[1][chl] - mean * s_tot[0][chl]);
-            }
-            m1 *= sp.inv_count;
-            m2 *= rstd * sp.inv_count;
-            s_q[tid] = (float)(-rstd * m1 + mean * rstd * rstd * m2);
-            s_p[tid] = (float)(-rstd * rstd * m2);
-        }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int gl = (cvl * 8 + k) / gs;
-            cq[k] = s_q[gl];
-            cp[k] = s_p[gl];
-        }
-    }
-    float s1[8], s2[8], s3[8], sdl = 0.f;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
-    for (int i = 0; i < nu; ++i) {
-        cp_async_wait<S - 1>();
-        const int sidx = i % S;
-        const uint4* sl = cache + (size_t)sidx * RAWV * FT + tid;
-        Raw<1, false> w;
-        w.r[0] = sl[0];
-        w.a[0] = sl[FT];
-        float rv[1][8], dz[1][8], act[8], dl = 0.f;
-        grads_from_raw<KIND, 1>(c, w, al, wv, rv, dz, dl, act);
-        if constexpr (!SECOND) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { s1[k] += dz[0][k]; s2[k] = fmaf(dz[0][k], rv[0][k], s2[k]); }
-            if (KIND == SRC_OUTER) {
-#pragma unroll
-                for (int k = 0; k < 8; ++k) s3[k] += dl * act[k];
-                if (cvl == 0) sdl += dl;
-            } else if (ThirdRow<KIND>::blend) {
-#pragma unroll
-                for (int k = 0; k < 8; ++k) s3[k] += act[k];
-            }
-        } else {
-            float o[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = fmaf(c.sc[k], dz[0][k], fmaf(cp[k], rv[0][k], cq[k]));
-            if constexpr (kIncr) {
-                store8(db + ta.px * sp.psd, o);
-                trk_fwd(ta, sp.ts, UW);
-            } else {
-                const int pi = p0 + i * pstep;
-                int uy, ux;
-                unit_row_col(pi, UW, uy, ux);
-                store8(a.dr.at(n, uy + r0, ux, cv * 8), o);
-            }
-        }
-        if (i + S < nu) {
-            issue(i + S, sidx, ti);
-            if constexpr (kIncr) trk_fwd(ti, sp.ts, UW);
-        }
-        cp_async_commit();
-    }
-    if constexpr (!SECOND) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            for (int o = 16; o >= ncv; o >>= 1) {
-                s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], o);
-                s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], o);
-                if (ThirdRow<KIND>::on) s3[k] += __shfl_xor_sync(0xffffffffu, s3[k], o);
-            }
-        }
-        if (lane < ncv) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                s_w[(wid * 3 + 0) * nchl + lane * 8 + k] = s1[k];
-                s_w[(wid * 3 + 1) * nchl + lane * 8 + k] = s2[k];
-                s_w[(wid * 3 + 2) * nchl + lane * 8 + k] = s3[k];
-            }
-        }
-        if (KIND == SRC_OUTER) {
-            sdl = warp_sum(sdl);
-            if (lane == 0) s_wdl[wid] = sdl;
-        }
-        __syncthreads();
-        float* out = a.part + ((int64_t)n * sp.G + rank) * 3 * row;
-        for (int i = tid; i < 3 * nchl; i += FT) {
-            const int which = i / nchl, chl = i % nchl;
-            float t = 0.f;
-            if (ncv <= 32) {
-                for (int w2 = 0; w2 < NW; ++w2) t += s_w[(w2 * 3 + which) * nchl + chl];
-            } else {
-                const int v = chl >> 3, par = v >> 5;
-                for (int w2 = par; w2 < NW; w2 += 2) t += s_w[(w2 * 3 + which) * nchl + ((v & 31) * 8 + (chl & 7))];
-            }
-            out[which * row + cv0 * 8 + chl] = t;
-        }
-        if (KIND == SRC_OUTER && tid == 0 && cv0 == 0) {
-            float t = 0.f;
-            for (int w2 = 0; w2 < NW; ++w2) t += s_wdl[w2];
-            out[C] = t;
-        }
-        __threadfence();
-        __syncthreads();
-        if (tid == 0) atomicAdd(sp.flags + u, 1);
-    } else {
-        __syncthreads();                        // s_tot / s_q / s_p are rewritten by the next apply phase
-    }
-}
-
-template <int KIND, int FT, int S>
-__global__ void __launch_bounds__(FT, 2) gn_bwd_stream_kernel(GnBwdArgs<__nv_bfloat16> a, StreamParams sp) {
-    extern __shared__ uint4 dyn_smem[];
-    __shared__ double s_tot[2][kMaxUnitCh];
-    __shared__ float s_q[kGroups], s_p[kGroups], s_wdl[FT / 32];
-    uint4* cache = dyn_smem;                                                         // [S][2][FT]
-    float* s_w = reinterpret_cast<float*>(dyn_smem + (size_t)S * 2 * FT);           // [NW][3][nchl]
-    const int slot = blockIdx.x / sp.G, rank = blockIdx.x % sp.G;
-    int prev = -1;
-    for (int u = slot; u < sp.units; u += sp.B) {
-        stream_phase<KIND, FT, S, false>(a, sp, u, rank, cache, s_w, s_tot, s_q, s_p, s_wdl);
-        if (prev >= 0) stream_phase<KIND, FT, S, true>(a, sp, prev, rank, cache, s_w, s_tot, s_q, s_p, s_wdl);
-        prev = u;
-    }
-    if (prev >= 0) stream_phase<KIND, FT, S, true>(a, sp, prev, rank, cache, s_w, s_tot, s_q, s_p, s_wdl);
-}
-
-// CTAs per unit for a unit of `unit_bytes` of operands: units in flight (B reduced + B applied, B = max_ctas / G) within ~64 MB
-inline int stream_group(double unit_bytes, int UH, int max_ctas) {
-    int G = (int)(2.0 * max_ctas * unit_bytes / (64.0 * 1048576.0)) + 1;
-    if (G < 2) G = 2;
-    if (G > UH) G = UH;
-    if (G > max_ctas) G = max_ctas;
-    const int rows_pc = ceil_div(UH, G);
-    return ceil_div(UH, rows_pc);                      // ranks that actually own rows
-}
-constexpr int kStreamMaxCtas = 2 * 160;               // partial-sum slots are sized for up to 160 SMs x 2 CTAs
-
 struct FusedPlan { bool ok; FusedParams fp; size_t smem; int units; int ft; int depth; };
 
 inline int env_int(const char* name, int dflt) {
@@ -1144,102 +879,11 @@ int run_fused(const GnBwdArgs<__nv_bfloat16>& a, const FusedPlan& pl, cudaStream
     return 0;
 }
 
-struct StreamPlan { bool ok; StreamParams sp; size_t smem; int grid; };
-
-template <int KIND, int FT, int S>
-int stream_max_ctas(size_t smem, int& out) {
-    static PerDeviceFlag attr_pd;
-    int dev = 0;
-    MRISR_CUDA_CHECK(cudaGetDevice(&dev));
-    if (!attr_pd.cur()) {
-        MRISR_CUDA_CHECK(cudaFuncSetAttribute(gn_bwd_stream_kernel<KIND, FT, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        attr_pd.cur() = true;
-    }
-    int per_sm = 0, sms = 0;
-    MRISR_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_bwd_stream_kernel<KIND, FT, S>, FT, smem));
-    MRISR_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    if (per_sm > 2) per_sm = 2;
-    out = per_sm * sms;
-    return 0;
-}
-
-// The streamed kernel covers the one-pixel kinds in bf16; anything it cannot take falls back to the cluster kernel.
-template <int KIND, int FT, int S>
-int stream_plan(const GnBwdArgs<__nv_bfloat16>& a, StreamPlan& pl) {
-    pl.ok = false;
-    static const int enabled = env_int("MRISR_GNBWD_STREAM", 0);      // opt-in until it beats the cluster kernel (profiles/r02_gn_bwd_stream.md)
-    if (!enabled || KindTraits<KIND>::pool || !a.flags) return 0;
-    const int C = a.r.C, nv = C / 8, gs = C / kGroups;
-    const int ncv = a.r.planar() ? 1 : nv;
-    if (C % 8 || ncv * 8 > kMaxUnitCh || FT % ncv || (ncv * 8) % gs || a.r.H < 1 || a.r.W < 1) return 0;
-    if (Incr<KIND>::on) {
-        auto elems = [](const Act<__nv_bfloat16>& t) { return (double)t.sample_pixels() * (t.ps ? t.ps : t.C); };
-        if (elems(a.r) >= 2147483648.0 || elems(a.dr) >= 2147483648.0 || elems(a.g) >= 2147483648.0) return 0;
-        if (a.dr.W != a.r.W || a.dr.H != a.r.H || a.g.W != a.r.W || a.g.H != a.r.H) return 0;
-    }
-    // s_w: per-warp partial sums of the reduce phase, and the staging area of the G x 2 x nchl partials of the apply phase
-    // (G <= kStreamMaxCtas ranks; sized for the bound so that the occupancy query below does not depend on G)
-    const int g_bound = stream_group((double)a.r.H * a.r.W * ncv * 8 * 2 * 2, a.r.H, kStreamMaxCtas);
-    const size_t red_bytes = std::max((size_t)(FT / 32) * 3 * ncv * 8, (size_t)g_bound * 2 * ncv * 8) * sizeof(float);
-    pl.smem = (size_t)S * 2 * FT * 16 + red_bytes;
-    int max_ctas = 0;
-    const int rc = stream_max_ctas<KIND, FT, S>(pl.smem, max_ctas);
-    if (rc) return rc;
-    if (pl.smem > 160 * 1024 || max_ctas < 2) return 0;
-    if (max_ctas > kStreamMaxCtas) max_ctas = kStreamMaxCtas;
-    StreamParams& sp = pl.sp;
-    sp.ncv = ncv;
-    sp.ups = nv / ncv;
-    sp.units = a.r.N * sp.ups;
-    const double unit_bytes = (double)a.r.H * a.r.W * ncv * 8 * 2 * 2;              // r + g of one unit, bf16
-    sp.G = stream_group(unit_bytes, a.r.H, max_ctas);
-    if (sp.G > gn_bwd_slots(a.r.H, a.r.W, C)) return 0;                              // partial-sum scratch is sized by gn_bwd_slots
-    sp.rows_pc = ceil_div(a.r.H, sp.G);
-    sp.B = max_ctas / sp.G;
-    if (sp.B > sp.units) sp.B = sp.units;
-    if (sp.B < 1) return 0;
-    sp.inv_count = 1.0 / ((double)gs * a.r.H * a.r.W);
-    sp.ts = trk_steps(FT / ncv, a.r.W, a.r.W + 2, a.g.W + 2);
-    sp.psr = a.r.ps ? a.r.ps : a.r.C;
-    sp.psg = a.g.ps ? a.g.ps : a.g.C;
-    sp.psd = a.dr.ps ? a.dr.ps : a.dr.C;
-    sp.flags = a.flags;
-    pl.grid = sp.B * sp.G;
-    pl.ok = true;
-    return 0;
-}
-
-template <int KIND, int FT, int S>
-int run_stream(const GnBwdArgs<__nv_bfloat16>& a, const StreamPlan& pl, cudaStream_t s) {
-    MRISR_CUDA_CHECK(cudaMemsetAsync(pl.sp.flags, 0, ((size_t)pl.sp.units + 1) * sizeof(int), s));
-    gn_bwd_stream_kernel<KIND, FT, S><<<pl.grid, FT, pl.smem, s>>>(a, pl.sp);
-    MRISR_LAUNCH_CHECK();
-    const int pcs = KIND == SRC_BLEND_PS ? a.r.C / 4 : a.r.C;
-    gn_bwd_finalize_kernel<__nv_bfloat16, KIND><<<pcs, FTHR, 0, s>>>(a, pl.sp.G, pl.sp.inv_count, 0, a.r.N, 1);
-    MRISR_LAUNCH_CHECK();
-    return 0;
-}
-
 template <typename T, int KIND>
 int run(const GnBwdArgs<T>& a, cudaStream_t s) {
     constexpr int P = KindTraits<KIND>::pool ? 4 : 1;
     const int C = a.r.C, nv = C / 8;
     if (nv > NTHR) { set_error("gn_bwd: C = %d is too wide", C); return -1; }
-    if constexpr (sizeof(T) == 2 && !KindTraits<KIND>::pool) {
-        // pipeline depth 6 while two CTAs still share an SM (planar units: 98 KB), else 4 (NHWC units carry a larger reduction
-        // buffer); whatever fits neither falls through to the cluster kernel
-        StreamPlan spl;
-        const int ncv_ = a.r.planar() ? 1 : nv;
-        if (ncv_ <= 2) {
-            const int rc = stream_plan<KIND, 512, 6>(a, spl);
-            if (rc) return rc;
-            if (spl.ok) return run_stream<KIND, 512, 6>(a, spl, s);
-        } else {
-            const int rc = stream_plan<KIND, 512, 4>(a, spl);
-            if (rc) return rc;
-            if (spl.ok) return run_stream<KIND, 512, 4>(a, spl, s);
-        }
-    }
     if constexpr (sizeof(T) == 2) {
         const FusedPlan fpl = fused_plan<KIND>(a);
         if (fpl.ok) {
@@ -1271,11 +915,8 @@ int gn_bwd_slots(int H, int W, int C) {
     // upper bound over both unit shapes (pool kinds use half the rows and half the columns)
     const int full = ceil_div(H, rows_per_block(W, C / 8, NTHR, UNITS_PER_THREAD));
     const int pool = ceil_div(H / 2, rows_per_block(W / 2, C / 8, NTHR, UNITS_PER_THREAD));
-    int m = full > pool ? full : pool;
-    if (m < 16) m = 16;                      // the cluster kernel uses one slot per cluster rank (<= 16)
-    // the streamed kernel uses one slot per CTA of a unit's group: bound over both layouts (an NHWC unit is the larger one)
-    const int g = stream_group((double)H * W * C * 4.0, H, kStreamMaxCtas);
-    return m > g ? m : g;
+    const int m = full > pool ? full : pool;
+    return m > 16 ? m : 16;                  // the fused kernel uses one slot per cluster rank (<= 16)
 }
 
 template <typename T>

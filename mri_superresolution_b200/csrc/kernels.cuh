@@ -132,7 +132,6 @@ struct GnBwdArgs {
     const float* alpha;           // SRC_BLEND_*
     float* part;                  // scratch [N][slots][C][2]
     float* mstat;                 // scratch [N][8][2]  (m1, m2)
-    int* flags;                   // scratch: N * C/8 + 1 ints (arrival counters of the streamed kernel); null = not available
     float* dgamma; float* dbeta;  // outputs [C] (or [C/4] for SRC_BLEND_PS), overwritten
     float* dwvec;  float* dbias;  // SRC_OUTER only: d(w1x1) [C], d(b1x1) [1]
     Act<T> dr;                    // output: gradient wrt the raw conv output

@@ -126,13 +126,11 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
         DY3 = make_act(ar, 0, f);
         gn_part = (float*)ar.take(gnp_max * sizeof(float));
         mstat = (float*)ar.take((size_t)N * kGroups * 2 * sizeof(float));
-        gn_flags = (int*)ar.take(((size_t)N * 64 + 64) * sizeof(int));
         wg_part = (float*)ar.take(wg_max * sizeof(float));
         const size_t misc_elems = std::max(colsum_scratch_elems(N, H, W, 2 * f), (size_t)4 * f);
         misc = (float*)ar.take(misc_elems * sizeof(float));
     } else {
         gn_part = mstat = wg_part = misc = nullptr;
-        gn_flags = nullptr;
     }
     bytes = ar.used;
 }

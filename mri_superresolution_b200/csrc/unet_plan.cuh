@@ -94,7 +94,6 @@ struct Workspace {
     // backward tensors (train only)
     Act<T> dR[kNumConv], dQ[kNumConv], G[kNumConv], DY3;
     float *gn_part, *mstat, *wg_part, *misc;
-    int* gn_flags;
     int* state;                                    // [0] = 1 after a train-mode forward
     size_t bytes;
 

@@ -198,7 +198,7 @@ struct Runner {
         GnBwdArgs<T> a;
         memset(&a, 0, sizeof(a));
         a.kind = kind; a.r = ws.R[l]; a.stats = ws.stats[l]; a.gamma = P(c.gamma); a.beta = P(c.beta);
-        a.g = g; a.coff = coff; a.part = ws.gn_part; a.mstat = ws.mstat; a.flags = ws.gn_flags;
+        a.g = g; a.coff = coff; a.part = ws.gn_part; a.mstat = ws.mstat;
         a.dgamma = GP(c.gamma); a.dbeta = GP(c.beta); a.dr = ws.dR[l]; a.alpha = P(0);
         return a;
     }
