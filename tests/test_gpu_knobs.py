@@ -42,6 +42,8 @@ KNOBS = [
     ("gn_bwd_cluster8", {"MRISR_GNBWD_CS": "8"}, False),
     ("wgrad_tc_per_tap", {"MRISR_WGRAD_TC3": "0"}, False),
     ("rows_one_cta", {"MRISR_ROWS_CTAS": "1"}, False),
+    ("upbwd_tiled", {"MRISR_UPBWD_RING": "0"}, False),
+    ("ssim_stream", {"MRISR_SSIM_STREAM": "1"}, False),                            # the streamed one-kernel loss                            # the tiled bilinear adjoint instead of the row ring
     # weight gradients on the main stream instead of the side stream: same kernels, same inputs (bit-equal, checked below)
     ("bwd_one_stream", {"MRISR_BWD_SIDE": "0"}, False),
     # the fused halo-2R loss kernel instead of the forward-maps + gradient pair
