@@ -374,163 +374,6 @@ int dispatch_split(int win, const float* pred, const float* tgt, float* dpred, f
     }
 }
 
-// ---------------------------------------------------------------------------------------------------------------------
-// Streamed form: ONE kernel, no tiles.  A CTA owns a strip of columns and walks down a run of rows; every thread owns one
-// column.  Per input row: the horizontal 11-tap pass of (x, y, xx, yy, xy) reads the row from shared memory; the vertical pass
-// is a scatter into 11 register accumulators per map (the row that has just received its last contribution is complete and
-// leaves the window); its SSIM derivative maps go to shared memory, the backward horizontal pass reads them, the backward
-// vertical pass is the same register scatter, and the gradient of row y - 2R leaves 2R rows after row y came in.  Against the
-// tile kernels: no halo recomputation along the walk (a 32 x 32 tile filters 42 x 42 and, fused, 52 x 52), no idle threads in
-// the passes, (x, y) read once, the three derivative maps never touch HBM.
-template <int R, int NT>
-__global__ void __launch_bounds__(NT) l1_ssim_stream_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
-                                                            float* __restrict__ dpred, float* __restrict__ partial, int H, int W,
-                                                            int seg_rows, Taps taps, float C1, float C2, float l1_coef, float ssim_coef) {
-    constexpr int WIN = 2 * R + 1, RING = WIN + 1, WS = NT - 4 * R;
-    __shared__ float2 s_xy[RING][NT];
-    __shared__ float s_dm[3][NT];
-    __shared__ float s_red[2][NT / 32];
-    const int t = threadIdx.x;
-    const int n = blockIdx.z, ry0 = blockIdx.y * seg_rows, ry1 = min(H, ry0 + seg_rows);
-    const int c = blockIdx.x * WS - 2 * R + t;                         // this thread's column
-    const bool col_in = c >= 0 && c < W;
-    const bool col_mid = t >= R && t < NT - R;                         // columns that carry forward maps
-    const bool col_out = t >= 2 * R && t < NT - 2 * R && c < W;        // columns this CTA writes
-    const float* px = pred + (int64_t)n * H * W;
-    const float* py = tgt + (int64_t)n * H * W;
-    float w[WIN];
-#pragma unroll
-    for (int k = 0; k < WIN; ++k) w[k] = taps.w[k];
-    float facc[WIN][5], bacc[WIN][3];
-#pragma unroll
-    for (int j = 0; j < WIN; ++j) {
-#pragma unroll
-        for (int m = 0; m < 5; ++m) facc[j][m] = 0.f;
-#pragma unroll
-        for (int m = 0; m < 3; ++m) bacc[j][m] = 0.f;
-    }
-    float ssum = 0.f, lsum = 0.f;
-    const int yi_end = ry1 + 2 * R;
-    for (int yb = ry0 - 2 * R; yb < yi_end; yb += WIN) {
-#pragma unroll
-        for (int ph = 0; ph < WIN; ++ph) {
-            const int yi = yb + ph;
-            if (yi >= yi_end) break;
-            // 1. the new input row
-            const int slot = (yi - (ry0 - 2 * R)) % RING;
-            float2 v = make_float2(0.f, 0.f);
-            if (col_in && yi >= 0 && yi < H) v = make_float2(px[(int64_t)yi * W + c], py[(int64_t)yi * W + c]);
-            s_xy[slot][t] = v;
-            __syncthreads();
-            // 2. forward horizontal pass at (yi, c), 3. vertical scatter: slot j collects row yi - R + j with weight w[2R - j] = w[j]
-            float h[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-            if (col_mid) {
-#pragma unroll
-                for (int k = 0; k < WIN; ++k) {
-                    const float2 q = s_xy[slot][t + k - R];
-                    h[0] = fmaf(w[k], q.x, h[0]);
-                    h[1] = fmaf(w[k], q.y, h[1]);
-                    h[2] = fmaf(w[k], q.x * q.x, h[2]);
-                    h[3] = fmaf(w[k], q.y * q.y, h[3]);
-                    h[4] = fmaf(w[k], q.x * q.y, h[4]);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < WIN; ++j)
-#pragma unroll
-                for (int m = 0; m < 5; ++m) facc[(j + ph) % WIN][m] = fmaf(w[j], h[m], facc[(j + ph) % WIN][m]);
-            // 4. the completed map row yd = yi - R: SSIM and its derivative maps (zero outside the image)
-            const int yd = yi - R;
-            float d1 = 0.f, d11 = 0.f, d12 = 0.f;
-            {
-                const float m1 = facc[ph % WIN][0], m2 = facc[ph % WIN][1], e11 = facc[ph % WIN][2], e22 = facc[ph % WIN][3], e12 = facc[ph % WIN][4];
-#pragma unroll
-                for (int m = 0; m < 5; ++m) facc[ph % WIN][m] = 0.f;
-                if (col_mid && col_in && yd >= 0 && yd < H && yd >= ry0 - R) {
-                    const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-                    const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
-                    const float inv = 1.f / (B1 * B2);
-                    const float S = A1 * A2 * inv;
-                    if (col_out && yd >= ry0 && yd < ry1) ssum += S;
-                    d11 = -S / B2;
-                    d12 = 2.f * A1 * inv;
-                    d1 = 2.f * m2 * (A2 - A1) * inv - 2.f * m1 * S / B1 + 2.f * m1 * S / B2;
-                }
-            }
-            s_dm[0][t] = d1; s_dm[1][t] = d11; s_dm[2][t] = d12;
-            __syncthreads();
-            // 5. backward horizontal pass at (yd, c), 6. vertical scatter, 7. the completed gradient row yo = yi - 2R
-            float g[3] = {0.f, 0.f, 0.f};
-            if (col_out && dpred) {
-#pragma unroll
-                for (int k = 0; k < WIN; ++k) {
-                    g[0] = fmaf(w[k], s_dm[0][t + k - R], g[0]);
-                    g[1] = fmaf(w[k], s_dm[1][t + k - R], g[1]);
-                    g[2] = fmaf(w[k], s_dm[2][t + k - R], g[2]);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < WIN; ++j)
-#pragma unroll
-                for (int m = 0; m < 3; ++m) bacc[(j + ph) % WIN][m] = fmaf(w[j], g[m], bacc[(j + ph) % WIN][m]);
-            const int yo = yi - 2 * R;
-            const float b0 = bacc[ph % WIN][0], b1 = bacc[ph % WIN][1], b2 = bacc[ph % WIN][2];
-#pragma unroll
-            for (int m = 0; m < 3; ++m) bacc[ph % WIN][m] = 0.f;
-            if (col_out && yo >= ry0 && yo < ry1) {
-                const float2 q = s_xy[(yo - (ry0 - 2 * R)) % RING][t];
-                const float d = q.x - q.y;
-                lsum += fabsf(d);
-                if (dpred) {
-                    const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
-                    dpred[(int64_t)n * H * W + (int64_t)yo * W + c] = l1_coef * sg + ssim_coef * (b0 + 2.f * q.x * b1 + q.y * b2);
-                }
-            }
-        }
-    }
-    ssum = warp_sum(ssum);
-    lsum = warp_sum(lsum);
-    if ((t & 31) == 0) { s_red[0][t >> 5] = lsum; s_red[1][t >> 5] = ssum; }
-    __syncthreads();
-    if (t < 2) {
-        float acc = 0.f;
-        for (int k = 0; k < NT / 32; ++k) acc += s_red[t][k];
-        const int64_t b = ((int64_t)n * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        partial[b * 2 + t] = acc;
-    }
-}
-
-constexpr int kStreamNT = 192;
-inline int stream_seg_rows(int H) { return H >= 256 ? 128 : (H >= 64 ? 64 : H); }
-template <int R> inline int stream_strips(int W) { return ceil_div(W, kStreamNT - 4 * R); }
-inline int stream_blocks(int win, int N, int H, int W) {
-    const int R = win / 2;
-    return N * ceil_div(H, stream_seg_rows(H)) * ceil_div(W, kStreamNT - 4 * R);
-}
-template <int R>
-int run_stream(const float* pred, const float* tgt, float* dpred, float* partial, int N, int H, int W, const Taps& taps, float C1,
-               float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
-    const int seg = stream_seg_rows(H);
-    dim3 grid(stream_strips<R>(W), ceil_div(H, seg), N);
-    l1_ssim_stream_kernel<R, kStreamNT><<<grid, kStreamNT, 0, s>>>(pred, tgt, dpred, partial, H, W, seg, taps, C1, C2, l1_coef, ssim_coef);
-    MRISR_LAUNCH_CHECK();
-    return 0;
-}
-int dispatch_stream(int win, const float* pred, const float* tgt, float* dpred, float* partial, int N, int H, int W, const Taps& taps,
-                    float C1, float C2, float l1_coef, float ssim_coef, cudaStream_t s) {
-    switch (win / 2) {
-        case 1: return run_stream<1>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-        case 2: return run_stream<2>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-        case 3: return run_stream<3>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-        case 4: return run_stream<4>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-        default: return run_stream<5>(pred, tgt, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-    }
-}
-bool ssim_stream_enabled() {
-    static const bool on = [] { const char* e = getenv("MRISR_SSIM_STREAM"); return e && e[0] == '1'; }();
-    return on;
-}
-
 bool ssim_split_enabled() {
     // on by default: measured on B200 in round 2, 0.627 -> 0.558 ms per 64 x 512^2 batch; MRISR_SSIM_SPLIT=0 = the fused kernel
     static const bool on = [] { const char* e = getenv("MRISR_SSIM_SPLIT"); return !(e && e[0] == '0'); }();
@@ -618,7 +461,6 @@ int dispatch(int win, const float* pred, const float* tgt, float* dpred, float* 
 }  // namespace
 
 static size_t partial_bytes(int N, int H, int W) {
-    // block partials of the tile kernels; the streamed kernel has fewer blocks than tiles for every window size
     return (((size_t)N * ceil_div(H, T) * ceil_div(W, T) * 2 * sizeof(float)) + 255) & ~(size_t)255;
 }
 size_t l1_ssim_scratch_bytes(int N, int H, int W) {
@@ -637,11 +479,8 @@ int launch_l1_ssim(const float* pred, const float* target, float* dpred, float* 
     const float ssim_coef = ssim_w > 0.f ? (float)(-ssim_w / numel) : 0.f;
     float* partial = (float*)scratch;
     int rc;
-    int nblocks = N * ceil_div(H, T) * ceil_div(W, T);
-    if (ssim_stream_enabled() && stream_blocks(win, N, H, W) <= nblocks) {
-        nblocks = stream_blocks(win, N, H, W);
-        rc = dispatch_stream(win, pred, target, dpred, partial, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
-    } else if (ssim_split_enabled()) {
+    const int nblocks = N * ceil_div(H, T) * ceil_div(W, T);
+    if (ssim_split_enabled()) {
         float* dmaps = (float*)((char*)scratch + partial_bytes(N, H, W));
         rc = dispatch_split(win, pred, target, dpred, partial, dmaps, N, H, W, taps, C1, C2, l1_coef, ssim_coef, s);
     } else {

@@ -284,6 +284,9 @@ __global__ void __launch_bounds__(NTHR) upsample2x_bwd_kernel(Act<T> ddst, Act<T
 // gradient rows / columns that tile gathers from are contiguous 16-byte vectors in both layouts (one plane of a planar-8
 // tensor, or all channels of an NHWC tensor), so they are staged global -> shared memory once with cp.async (coalesced,
 // everything in flight at once) and the ~16-20 taps of every output then read shared memory instead of L1/L2.
+// (A row-ring form -- a CTA walking down source rows with the destination rows streaming through a 12-slot cp.async ring, every
+// row fetched once -- was measured in round 2 and lost, 0.634 -> 0.825 ms at 32@256^2: two barriers per source row with eight
+// warps per CTA cost more than the tile's load-wait-compute bubble; profiles/r02_lost_variants.md.)
 __device__ __forceinline__ void cp_async16_na(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
@@ -413,113 +416,6 @@ static void adj_ranges_host(int in_size, std::vector<int>& lo, std::vector<int>&
         if (i1 != i0 && w1 != 0.f) { lo[i1] = std::min(lo[i1], d); hi[i1] = std::max(hi[i1], d); }
     }
 }
-// Ring form (bf16): a CTA owns a strip of source columns of one (sample, channel-vector range) and WALKS DOWN a run of source
-// rows; the destination-gradient rows it gathers from stream through a ring of RD row slots in shared memory, one cp.async
-// commit group per row, issued RD rows ahead of the row being reduced.  Every destination row is fetched once per strip (the
-// tiled form re-fetches ~2 halo rows per 4-5 source rows and, more importantly, loads a whole tile, waits, then computes: with
-// two CTAs per SM the memory system idles about half the time, 2.3 TB/s in profiles/r02_launches_step.md).
-struct UpRing { int TW, ncv, cols_cap, RD, rows_per_cta, tiles_x, chunks_y; };
-
-__device__ __forceinline__ void cp_async_wait_dyn(int pending) {
-    switch (pending) {
-        case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
-        case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
-        case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
-        case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
-        case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
-        case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
-        case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
-        case 7: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
-        case 8: asm volatile("cp.async.wait_group 8;" ::: "memory"); break;
-        case 9: asm volatile("cp.async.wait_group 9;" ::: "memory"); break;
-        case 10: asm volatile("cp.async.wait_group 10;" ::: "memory"); break;
-        default: asm volatile("cp.async.wait_group 11;" ::: "memory"); break;
-    }
-}
-
-__global__ void __launch_bounds__(NTHR, 2) upsample2x_bwd_ring_kernel(Act<__nv_bfloat16> ddst, Act<__nv_bfloat16> addend,
-                                                                      Act<__nv_bfloat16> dsrc, const AdjTap5* __restrict__ tab_y,
-                                                                      const AdjTap5* __restrict__ tab_x, UpRing tp) {
-    extern __shared__ uint4 up_smem[];                                            // [RD][cols_cap] 16-byte vectors
-    const int tid = threadIdx.x, ncv = tp.ncv, RD = tp.RD;
-    const int tile_x = blockIdx.x % tp.tiles_x, chunk = blockIdx.x / tp.tiles_x;
-    const int units_per_sample = (dsrc.C / 8) / ncv;
-    const int n = blockIdx.y / units_per_sample, cv0 = (blockIdx.y % units_per_sample) * ncv;
-    const int y0 = chunk * tp.rows_per_cta, y1 = min(dsrc.H, y0 + tp.rows_per_cta);
-    const int x0 = tile_x * tp.TW, tw = min(tp.TW, dsrc.W - x0);
-    const AdjTap5 xa = tab_x[x0], xb = tab_x[x0 + tw - 1], ya = tab_y[y0], yb = tab_y[y1 - 1];
-    const int X_lo = xa.lo, ncols = (xb.lo + xb.cnt - X_lo) * ncv;
-    const int d_lo = ya.lo, total = yb.lo + yb.cnt - d_lo;                         // destination rows d_lo .. d_lo + total - 1
-    if (ncols > tp.cols_cap) __trap();
-    const int per_row = tw * ncv;
-    AdjTap5 tx[2];
-    int xl[2], cvl[2], off[2];
-#pragma unroll
-    for (int u = 0; u < 2; ++u) {
-        const int j = min(tid + u * NTHR, per_row - 1);
-        xl[u] = j / ncv;
-        cvl[u] = j - xl[u] * ncv;
-        tx[u] = tab_x[x0 + xl[u]];
-        off[u] = (tx[u].lo - X_lo) * ncv + cvl[u];
-    }
-    int issued = 0;
-    auto issue_row = [&]() {
-        const __nv_bfloat16* src = ddst.at(n, d_lo + issued, X_lo, cv0 * 8);
-        uint4* dst = up_smem + (size_t)(issued % RD) * tp.cols_cap;
-        for (int c = tid; c < ncols; c += NTHR) cp_async16_na(dst + c, src + (int64_t)c * 8);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        ++issued;
-    };
-    while (issued < total && issued < RD) issue_row();
-    AdjTap5 ty = ya;
-    for (int y = y0; y < y1; ++y) {
-        const int next_lo = y + 1 < y1 ? tab_y[y + 1].lo : d_lo + total;
-        cp_async_wait_dyn(issued - (ty.lo + ty.cnt - d_lo));                      // rows up to this row's last tap have landed
-        __syncthreads();
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            if (tid + u * NTHR >= per_row) continue;
-            float add[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) add[k] = 0.f;
-            if (addend.p) load8(addend.at(n, y, x0 + xl[u], (cv0 + cvl[u]) * 8), add);
-            float acc[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-            for (int jy = 0; jy < ty.cnt; ++jy) {
-                const uint4* base = up_smem + (size_t)((ty.lo + jy - d_lo) % RD) * tp.cols_cap + off[u];
-                float h[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) h[k] = 0.f;
-#pragma unroll
-                for (int jx = 0; jx < 5; ++jx) {
-                    if (jx < tx[u].cnt) {
-                        const uint4 raw = base[jx * ncv];
-                        const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            h[2 * i] = fmaf(tx[u].w[jx], __uint_as_float(w4[i] << 16), h[2 * i]);
-                            h[2 * i + 1] = fmaf(tx[u].w[jx], __uint_as_float(w4[i] & 0xffff0000u), h[2 * i + 1]);
-                        }
-                    }
-                }
-                const float wy = ty.w[jy];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) acc[k] = fmaf(wy, h[k], acc[k]);
-            }
-            float o[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = add[k] + acc[k];
-            store8(dsrc.at(n, y, x0 + xl[u], (cv0 + cvl[u]) * 8), o);
-        }
-        __syncthreads();                                                           // rows below next_lo are free for reuse
-        while (issued < total && issued - (next_lo - d_lo) < RD) issue_row();
-        if (y + 1 < y1) ty = tab_y[y + 1];
-    }
-}
-
-static bool up_ring_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>& dsrc, UpRing& tp, size_t& smem);
-
 static int max_span(const std::vector<int>& lo, const std::vector<int>& hi, int tile) {
     int m = 0;
     const int n = (int)lo.size();
@@ -559,33 +455,6 @@ static bool up_bwd_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>
     tp.tiles_x = ceil_div(dsrc.W, tp.TW);
     tp.tiles_y = ceil_div(dsrc.H, tp.TR);
     return true;
-}
-
-static bool up_ring_plan(const Act<__nv_bfloat16>& ddst, const Act<__nv_bfloat16>& dsrc, UpRing& tp, size_t& smem) {
-    static const bool on = [] { const char* e = getenv("MRISR_UPBWD_RING"); return !(e && e[0] == '0'); }();
-    if (!on || dsrc.C % 8 || ddst.planar() != dsrc.planar()) return false;
-    const int nv = dsrc.C / 8;
-    tp.ncv = ddst.planar() ? 1 : nv;
-    std::vector<int> ylo, yhi, xlo, xhi;
-    adj_ranges_host(dsrc.H, ylo, yhi);
-    adj_ranges_host(dsrc.W, xlo, xhi);
-    for (int i = 0; i < dsrc.H; ++i) if (yhi[i] < 0 || yhi[i] - ylo[i] + 1 > 5) return false;
-    for (int i = 0; i < dsrc.W; ++i) if (xhi[i] < 0 || xhi[i] - xlo[i] + 1 > 5) return false;
-    for (int i = 1; i < dsrc.H; ++i) if (ylo[i] < ylo[i - 1] || yhi[i] < yhi[i - 1]) return false;     // the ring relies on monotone taps
-    // fewest column strips whose destination rows fit 8 KB (512 vectors) and whose source row fits 2 pairs per thread
-    int tiles = 1;
-    for (;; ++tiles) {
-        const int tw = ceil_div(dsrc.W, tiles);
-        if (max_span(xlo, xhi, tw) * tp.ncv <= 512 && tw * tp.ncv <= 2 * NTHR) { tp.TW = tw; break; }
-        if (tw <= 2) return false;
-    }
-    tp.tiles_x = ceil_div(dsrc.W, tp.TW);
-    tp.cols_cap = max_span(xlo, xhi, tp.TW) * tp.ncv;
-    tp.RD = 12;
-    tp.rows_per_cta = dsrc.H >= 64 ? dsrc.H / 8 : (dsrc.H >= 8 ? 8 : dsrc.H);
-    tp.chunks_y = ceil_div(dsrc.H, tp.rows_per_cta);
-    smem = (size_t)tp.RD * tp.cols_cap * 16;
-    return smem <= 100u * 1024u;
 }
 
 inline int grid_for(int64_t total) {
@@ -681,24 +550,6 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-    if constexpr (sizeof(T) == 2) {
-        UpRing rp;
-        size_t rsmem = 0;
-        if (up_ring_plan(ddst, dsrc, rp, rsmem)) {
-            static PerDeviceFlag ring_attr_pd; bool& ring_attr = ring_attr_pd.cur();
-            if (!ring_attr) {
-                MRISR_CUDA_CHECK(cudaFuncSetAttribute(upsample2x_bwd_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-                ring_attr = true;
-            }
-            const AdjTap5* ty = adj_table(dsrc.H, s);
-            const AdjTap5* tx = dsrc.W == dsrc.H ? ty : adj_table(dsrc.W, s);
-            if (!ty || !tx) { set_error("upsample2x_bwd: tap table allocation failed"); return -1; }
-            dim3 grid(rp.tiles_x * rp.chunks_y, dsrc.N * ((dsrc.C / 8) / rp.ncv));
-            upsample2x_bwd_ring_kernel<<<grid, NTHR, rsmem, s>>>(ddst, addend, dsrc, ty, tx, rp);
-            MRISR_LAUNCH_CHECK();
-            return 0;
-        }
-    }
     if constexpr (sizeof(T) == 2) {
         UpBwdTile tp;
         size_t smem = 0;
