@@ -76,13 +76,6 @@ int mrisr_unet_backward(const float* params, const float* dy, const float* y, fl
                         void* workspace, size_t workspace_bytes, int N, int H, int W, int base_filters,
                         int precision, void* stream);
 
-/* Diagnostic (host-only arithmetic, no device needed): which kernel family runs convolution `conv_index` (0..19, the order of
- * models/unet_model.py:137-173 with the three up-path 1x1 convs at 8, 11, 14) in bf16 mode at input size H x W:
- * 0 = CUDA cores, 1 = NHWC TMA / tcgen05 (conv_tc, wgrad_tc), 2 = planar-8 sliding-window tcgen05 (conv_ring, wgrad_rows).
- * Levels <= 0 use 2 while three padded pixel rows of every 3x3 layer of the level fit in shared memory, else the whole
- * level falls back to 1 (512 x 512 input, BASELINE.json config 4).  -1 = bad argument. */
-int mrisr_unet_layer_engine(int base_filters, int conv_index, int H, int W);
-
 /* ---- data-parallel support: gradient-readiness marks ------------------------------------------------------------
  * The reference is single-device (scripts/train.py:296-318 has no exchange step); BASELINE.json config 3 adds a bucketed
  * gradient all-reduce that overlaps the backward pass.  The backward schedule finishes the conv blocks in the order
@@ -225,6 +218,20 @@ size_t mrisr_robust_normalize_scratch_bytes(int N, int H, int W);
 int mrisr_robust_normalize_f64(const double* src, float* dst, double* window, void* scratch, size_t scratch_bytes, int N, int H, int W,
                                double lower_percentile, double upper_percentile, double target_lo, double target_hi, void* stream);
 
+/* ==================================================================================================================
+ * MRISR_INTERNAL -- test, diagnosis and measurement aids.  Exported so that tests/ and bench.py can reach single kernels and
+ * internal tensors through the same C ABI; NOT part of the product surface INTEGRATION.md describes, and free to change.
+ * Define MRISR_NO_INTERNAL before including this header to hide the declarations.
+ * ================================================================================================================== */
+#ifndef MRISR_NO_INTERNAL
+
+/* Diagnostic (host-only arithmetic, no device needed): which kernel family runs convolution `conv_index` (0..19, the order of
+ * models/unet_model.py:137-173 with the three up-path 1x1 convs at 8, 11, 14) in bf16 mode at input size H x W:
+ * 0 = CUDA cores, 1 = NHWC TMA / tcgen05 (conv_tc, wgrad_tc), 2 = planar-8 sliding-window tcgen05 (conv_ring, wgrad_rows).
+ * Levels <= 0 use 2 while three padded pixel rows of every 3x3 layer of the level fit in shared memory, else the whole
+ * level falls back to 1 (512 x 512 input, BASELINE.json config 4).  -1 = bad argument. */
+int mrisr_unet_layer_engine(int base_filters, int conv_index, int H, int W);
+
 /* ---- convolution building block over padded NHWC bf16 tensors ---------------------------------
  * The implicit-GEMM kernels behind every nn.Conv2d of models/unet_model.py:29,34,72,101,152,168 (and of the VGG19
  * feature stack, utils/losses.py:90-95), exposed one layer at a time: the parity tests call them with both engines.
@@ -262,6 +269,8 @@ long long mrisr_launch_count(void);
  * into the HOST buffer buf (NUL-terminated, at most cap bytes); returns the number of tags. */
 int mrisr_prof_enable(int on);
 int mrisr_prof_report(char* host_buf, size_t cap);
+
+#endif /* MRISR_NO_INTERNAL */
 
 #ifdef __cplusplus
 }

@@ -11,10 +11,7 @@ import subprocess
 from ctypes import c_char_p, c_double, c_float, c_int, c_int64, c_size_t, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# MRISR_B200_VARIANT=<name> loads lib/libmrisr_b200_<name>.so, a staged build made with `make VARIANT=<name> EXTRA=-D...`
-# (csrc/Makefile) for A/B runs; unset = the measured default build.  A missing variant fails like a missing default.
-_VARIANT = os.environ.get("MRISR_B200_VARIANT", "")
-LIB_PATH = os.path.join(_HERE, "lib", f"libmrisr_b200{'_' + _VARIANT if _VARIANT else ''}.so")
+LIB_PATH = os.path.join(_HERE, "lib", "libmrisr_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 FP32 = 0

@@ -329,8 +329,7 @@ __global__ void __launch_bounds__(NTHR) gn_bwd_apply_kernel(GnBwdArgs<T> a, int 
 // units in flight to the L2 (groups of CTAs per unit, arrival counters instead of cluster barriers, the next unit's reduce between
 // arrive and wait) was built and measured in round 2 and LOST (gn_bwd 4.6 -> 7.2 ms per step): the L2 budget forces ~110 KB
 // phases per CTA, whose fixed per-phase instructions made it issue-bound (66 % issue-active, L2 hit rate 30 %, DRAM traffic still
-// 4.2 passes); deleted, numbers in profiles/r02_gn_bwd_stream.md.  MRISR_GNBWD_CS
-// reproduces the cluster-size sweep.
+// 4.2 passes); deleted, numbers in profiles/r02_gn_bwd_stream.md.
 constexpr int kFtMax = 512;             // threads per CTA of the fused kernel: 512 (2 CTAs / SM) or 256 (4 CTAs / SM)
 constexpr int kMaxUnitCh = 512;         // channels of one unit
 
@@ -796,7 +795,6 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     // two CTAs per SM (64 registers) for the one-pixel kinds; the 2x2-window kinds need 128 registers -> one CTA with all the SM's
     // shared memory
     const int smem_kb = FT == 512 ? (POOL ? 190 : 96) : (POOL ? 95 : 40);
-    static const int cs_env = env_int("MRISR_GNBWD_CS", 0);
     if (!enabled) return pl;
     const int C = a.r.C, nv = C / 8, gs = C / kGroups;
     const int ncv = a.r.planar() ? 1 : nv;
@@ -806,7 +804,7 @@ FusedPlan fused_plan(const GnBwdArgs<__nv_bfloat16>& a) {
     const size_t red_bytes = (size_t)(FT / 32) * 3 * ncv * 8 * sizeof(float);
     const size_t budget = (size_t)smem_kb * 1024 > red_bytes + 4096 ? (size_t)smem_kb * 1024 - red_bytes : 4096;
     const int kmax = (int)(budget / ((size_t)FT * RAWV * 16));
-    int cs = cs_env ? cs_env : 2;
+    int cs = 2;                          // clusters of 2 won the sweep in both rounds (4: +0.11 ms, 8: +0.42 ms per step under graph replay)
     while (cs > UH && cs > 1) cs >>= 1;
     if (cs != 1 && cs != 2 && cs != 4 && cs != 8 && cs != 16) return pl;
     pl.ft = FT;

@@ -52,8 +52,6 @@ inline bool level_is_planar(int f, int lvl, int H, int W) {
 // ENG_RING: planar-8 sliding-window tcgen05 (conv_ring.cu / wgrad_ring.cu), the narrow layers at levels <= 0.
 enum Engine : int { ENG_GENERIC = 0, ENG_TC = 1, ENG_RING = 2 };
 inline int layer_engine(const ConvDesc& c, int l, int H, int W, int f) {
-    static const bool disabled = getenv("MRISR_DEBUG_NO_TC") != nullptr;   // debugging aid: all layers on CUDA cores
-    if (disabled) return ENG_GENERIC;
     const int h = lvl_dim(H, c.lvl), w = lvl_dim(W, c.lvl);
     const int c1 = is_concat_conv(l) ? c.cin / 2 : c.cin, c2 = c.cin - c1;
     if (level_is_planar(f, c.lvl, H, W)) {

@@ -39,7 +39,6 @@ def baseline(tmp_path_factory):
 # (max-pool ties, LeakyReLU signs flip for a few elements), which the cancellation-heavy GroupNorm parameter gradients amplify.
 KNOBS = [
     ("gn_bwd_unfused", {"MRISR_GNBWD_FUSED": "0"}, False),
-    ("gn_bwd_cluster8", {"MRISR_GNBWD_CS": "8"}, False),
     ("wgrad_tc_per_tap", {"MRISR_WGRAD_TC3": "0"}, False),
     ("rows_one_cta", {"MRISR_ROWS_CTAS": "1"}, False),
     ("upbwd_tiled", {"MRISR_UPBWD_RING": "0"}, False),
