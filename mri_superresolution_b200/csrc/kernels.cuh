@@ -91,6 +91,9 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
 
 // dst[2h x 2w] = bilinear x2 (align_corners=True) of src[h x w]
 template <typename T> int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s);
+constexpr int MRISR_NOT_APPLICABLE = -12345;      // internal: "this fused form does not cover the shape, use the plain path"
+// same, also leaving dst's GroupNorm partials (gn_stats layout, *slots per sample) in `part`; MRISR_NOT_APPLICABLE if the shape needs the plain path
+template <typename T> int launch_upsample2x_stats(Act<T> src, Act<T> dst, float* part, size_t part_cap_floats, int* slots, cudaStream_t s);
 // dsrc = adjoint(upsample)(ddst) (+ addend if addend.p != nullptr)
 template <typename T> int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t s);
 

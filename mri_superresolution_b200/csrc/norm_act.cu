@@ -520,6 +520,23 @@ int launch_gn_apply(Act<T> r, const float* stats, const float* gamma, const floa
     return 0;
 }
 
+// forward bilinear x2 that also leaves the GroupNorm partials of dst in `part` (slots = the returned *slots per sample);
+// returns MRISR_NOT_APPLICABLE when the shape needs the plain path (the caller then runs gn_stats itself)
+template <typename T>
+int launch_upsample2x_stats(Act<T> src, Act<T> dst, float* part, size_t part_cap_floats, int* slots, cudaStream_t s) {
+    if (!((int64_t)(src.W + 2) * (src.ps ? src.ps : src.C) < (1ll << 31) / (src.H + 2) &&
+          (int64_t)(dst.W + 2) * (dst.ps ? dst.ps : dst.C) < (1ll << 31) / (dst.H + 2)) || dst.C > 2048 || dst.C % 8)
+        return MRISR_NOT_APPLICABLE;
+    const int rows = dst.H >= 64 ? 16 : 8;
+    dim3 grid_s(ceil_div(dst.H, rows), dst.N);
+    if ((size_t)dst.N * grid_s.x * kGroups * 2 > part_cap_floats) return MRISR_NOT_APPLICABLE;
+    ProfScope prof_("upsample2x", s);
+    upsample2x_slide_stats_kernel<T, NTHR><<<grid_s, NTHR, 0, s>>>(src, dst, up_scale(src.H), up_scale(src.W), rows, part);
+    MRISR_LAUNCH_CHECK();
+    *slots = (int)grid_s.x;
+    return 0;
+}
+
 template <typename T>
 int launch_upsample2x(Act<T> src, Act<T> dst, cudaStream_t s) {
     ProfScope prof_("upsample2x", s);
@@ -582,6 +599,7 @@ int launch_upsample2x_bwd(Act<T> ddst, Act<T> addend, Act<T> dsrc, cudaStream_t 
     template int launch_gn_stats<T>(Act<T>, float*, cudaStream_t);                                                \
     template int launch_gn_apply<T>(Act<T>, const float*, const float*, const float*, Act<T>, Act<T>, cudaStream_t); \
     template int launch_upsample2x<T>(Act<T>, Act<T>, cudaStream_t);                                              \
+    template int launch_upsample2x_stats<T>(Act<T>, Act<T>, float*, size_t, int*, cudaStream_t);                  \
     template int launch_upsample2x_bwd<T>(Act<T>, Act<T>, Act<T>, cudaStream_t);
 INST(float)
 INST(__nv_bfloat16)

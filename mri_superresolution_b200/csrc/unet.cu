@@ -115,6 +115,7 @@ Workspace<T>::Workspace(void* base, int N_, int H_, int W_, int f_, bool train) 
     UB = make_act(ar, -1, f);
     XM = make_act(ar, -1, f / 2);
     stat_part = (float*)ar.take(part_max * sizeof(float));
+    stat_part_floats = part_max;
     if (train) {
         for (int l = 0; l < kNumConv; ++l) {
             const ConvDesc& c = conv[l];

@@ -92,6 +92,7 @@ struct Workspace {
     // backward tensors (train only)
     Act<T> dR[kNumConv], dQ[kNumConv], G[kNumConv], DY3;
     float *gn_part, *mstat, *wg_part, *misc;
+    size_t stat_part_floats = 0;          // capacity of stat_part
     int* state;                                    // [0] = 1 after a train-mode forward
     size_t bytes;
 

@@ -22,6 +22,35 @@ static int64_t grads_final_from(const ParamLayout& pl, const ConvDesc (&conv)[kN
 // end of backward.  They only read activations and dR (never rewritten during backward: every tensor of the workspace has its
 // own buffer) and write the gradient arena and their own partial-sum scratch, so they are independent of the data-gradient
 // chain; the chain is the critical path and its small deep-level kernels leave SMs idle that the weight gradients can use.
+// All 20 convolutions' operand copies in ONE launch (bf16 mode): fp32 [Cout][Cin][ks][ks] -> the forward and data-gradient
+// layouts of the layer's engine (conv_tc.cu / conv_ring.cu / conv_generic.cu state them).  20 separate launches of 5 - 6 us
+// each were 0.16 ms of the step for 7 MB of traffic.
+struct PackEntry { const float* w; __nv_bfloat16* wf; __nv_bfloat16* wd; int Cout, Cin, taps, kind; long long first; };
+struct PackTable { PackEntry e[kNumConv]; int n; long long total; };
+__global__ void __launch_bounds__(256) pack_weights_all_kernel(const __grid_constant__ PackTable tb) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < tb.total; i += (long long)gridDim.x * blockDim.x) {
+        int l = 0;
+        while (l + 1 < tb.n && i >= tb.e[l + 1].first) ++l;
+        const PackEntry& p = tb.e[l];
+        const long long j = i - p.first;
+        const int taps = p.taps, Cin = p.Cin, Cout = p.Cout;
+        const int tap = (int)(j % taps);
+        const int ci = (int)((j / taps) % Cin);
+        const int co = (int)(j / ((long long)taps * Cin));
+        const __nv_bfloat16 v = __float2bfloat16_rn(p.w[j]);
+        if (p.kind == ENG_TC) {
+            p.wf[((long long)tap * Cout + co) * Cin + ci] = v;
+            if (p.wd) p.wd[((long long)(taps - 1 - tap) * Cin + ci) * Cout + co] = v;
+        } else if (p.kind == ENG_RING) {
+            p.wf[(((long long)tap * (Cin / 8) + ci / 8) * Cout + co) * 8 + (ci & 7)] = v;
+            if (p.wd) p.wd[(((long long)(taps - 1 - tap) * (Cout / 8) + co / 8) * Cin + ci) * 8 + (co & 7)] = v;
+        } else {
+            p.wf[((long long)tap * Cin + ci) * Cout + co] = v;
+            if (p.wd) p.wd[((long long)(taps - 1 - tap) * Cout + co) * Cin + ci] = v;
+        }
+    }
+}
+
 // Created on first use outside stream capture (the graph helpers warm up eagerly first); fork / join by events, which a
 // capturing stream records as graph dependencies.
 struct SideStream {
@@ -108,10 +137,16 @@ struct Runner {
     int up_branch(int l, Act<T> src) {
         const Act<T> none{nullptr, 0, 0, 0, 0};
         TRY(conv(l, src, none, ws.Q[l], false));
-        TRY(launch_upsample2x<T>(ws.Q[l], ws.R[l], s));
-        TRY(launch_gn_stats<T>(ws.R[l], ws.stat_part, s));
-        TRY(launch_gn_finalize(ws.stat_part, ws.stats[l], ws.N, stat_slots_generic(ws.R[l].H, ws.R[l].W, ws.R[l].C),
-                               (double)(ws.R[l].C / kGroups) * ws.R[l].H * ws.R[l].W, s));
+        // the interpolation kernel sums what it stores: no separate statistics pass over the up-sampled tensor
+        int slots = 0;
+        const int rc = launch_upsample2x_stats<T>(ws.Q[l], ws.R[l], ws.stat_part, ws.stat_part_floats, &slots, s);
+        if (rc != 0 && rc != MRISR_NOT_APPLICABLE) return rc;
+        if (rc == MRISR_NOT_APPLICABLE) {
+            TRY(launch_upsample2x<T>(ws.Q[l], ws.R[l], s));
+            TRY(launch_gn_stats<T>(ws.R[l], ws.stat_part, s));
+            slots = stat_slots_generic(ws.R[l].H, ws.R[l].W, ws.R[l].C);
+        }
+        TRY(launch_gn_finalize(ws.stat_part, ws.stats[l], ws.N, slots, (double)(ws.R[l].C / kGroups) * ws.R[l].H * ws.R[l].W, s));
         return gn_act(l, none);
     }
     BlendArgs<T> blend_args() {
@@ -124,7 +159,21 @@ struct Runner {
 
     int forward(const float* x, float* y, bool train) {
         const Act<T> none{nullptr, 0, 0, 0, 0};
-        for (int l = 0; l < kNumConv; ++l) {
+        if constexpr (sizeof(T) == 2) {
+            PackTable tb;
+            tb.n = kNumConv;
+            long long first = 0;
+            for (int l = 0; l < kNumConv; ++l) {
+                const ConvDesc& c = ws.conv[l];
+                tb.e[l] = PackEntry{P(c.w), ws.wf[l], train && l > 0 ? ws.wd[l] : nullptr, c.cout, c.cin, c.ks * c.ks, eng(l), first};
+                first += (long long)c.cout * c.cin * c.ks * c.ks;
+            }
+            tb.total = first;
+            ProfScope prof_("pack_weights", s);
+            pack_weights_all_kernel<<<(int)((first + 255) / 256 > 1184 ? 1184 : (first + 255) / 256), 256, 0, s>>>(tb);
+            MRISR_LAUNCH_CHECK();
+        }
+        for (int l = 0; l < kNumConv && sizeof(T) != 2; ++l) {
             const ConvDesc& c = ws.conv[l];
             if constexpr (sizeof(T) == 2) {
                 if (eng(l) != ENG_GENERIC) {

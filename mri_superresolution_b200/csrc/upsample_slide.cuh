@@ -1,5 +1,7 @@
-// Bilinear x2 (align_corners=True) with the two source rows of a destination column kept in registers
-// (staged build, -DMRISR_UPSAMPLE_SLIDE; the default is upsample2x_kernel in norm_act.cu).
+// Bilinear x2 (align_corners=True) with the two source rows of a destination column kept in registers (the default forward
+// kernel since round 2; upsample2x_kernel in norm_act.cu is the fallback for tensors beyond 32-bit offsets).
+// STATS: the thread also sums the values it stores (as rounded to T) and their squares per channel; the kernel reduces them to
+// per-(sample, block, group) GroupNorm partials, so the up-branch tensors need no separate gn_stats pass (round 2).
 //
 // upsample2x_kernel gathers 4 source vectors and evaluates 5 Act::at address chains per destination vector: 325 SASS
 // instructions per two destination vectors, issue-bound at ~42 % of the HBM copy rate (profiles/r01_elementwise_issue.md).
@@ -34,9 +36,10 @@ __host__ __device__ __forceinline__ void unpack_raw(const RawVec<__nv_bfloat16>&
 
 // PF: the source row the NEXT destination row will need is loaded (raw) before the current row is blended and stored, so its
 // latency overlaps that work instead of stalling the next iteration (16 more registers per column).
-template <typename T, int UB, bool PF = false>
+template <typename T, int UB, bool PF = false, bool STATS = false>
 __host__ __device__ __forceinline__ void upsample2x_slide_body(const Act<T>& src, const Act<T>& dst, float sy, float sx, int rows_pb,
-                                                               int n, int block, int tid, int nthr) {
+                                                               int n, int block, int tid, int nthr, float* s1 = nullptr,
+                                                               float* s2 = nullptr) {
     const RowMap m = row_map(dst, nthr, tid);
     if (!m.active) return;
     const int Y0 = block * rows_pb, Y1 = Y0 + rows_pb < dst.H ? Y0 + rows_pb : dst.H;
@@ -118,6 +121,14 @@ MRISR_UNROLL
 MRISR_UNROLL
                 for (int k = 0; k < 8; ++k) o[k] = h0 * top[u][k] + h1 * bot[u][k];
                 store8(dp[u] + (int64_t)Y * drs, o);
+                if (STATS) {
+MRISR_UNROLL
+                    for (int k = 0; k < 8; ++k) {
+                        const float q = to_f(from_f<T>(o[k]));             // statistics of the tensor as stored
+                        s1[k] += q;
+                        s2[k] += q * q;
+                    }
+                }
             }
         }
     }
@@ -127,6 +138,38 @@ MRISR_UNROLL
 template <typename T, int UB, int NT, bool PF = false>
 __global__ void __launch_bounds__(NT) upsample2x_slide_kernel(Act<T> src, Act<T> dst, float sy, float sx, int rows_pb) {
     upsample2x_slide_body<T, UB, PF>(src, dst, sy, sx, rows_pb, blockIdx.y, blockIdx.x, threadIdx.x, NT);
+}
+
+// + GroupNorm partial statistics of dst: part[((n * gridDim.x + block) * 8 + g) * 2 + {sum, sum of squares}] (gn_stats_kernel's
+// layout with slots = gridDim.x, finalised by gn_finalize_kernel)
+template <typename T, int NT>
+__global__ void __launch_bounds__(NT) upsample2x_slide_stats_kernel(Act<T> src, Act<T> dst, float sy, float sx, int rows_pb,
+                                                                    float* __restrict__ part) {
+    __shared__ float s_red[2][NT * 8];
+    __shared__ float s_ch[2][2048];
+    float s1[8], s2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+    upsample2x_slide_body<T, 1, false, true>(src, dst, sy, sx, rows_pb, blockIdx.y, blockIdx.x, threadIdx.x, NT, s1, s2);
+    const int tid = threadIdx.x, C = dst.C, nv = C / 8;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s_red[0][tid * 8 + k] = s1[k]; s_red[1][tid * 8 + k] = s2[k]; }
+    __syncthreads();
+    const bool planar = dst.planar();
+    const int cnt = NT / nv;                      // inactive threads (NT % nv != 0) hold zeros
+    for (int i = tid; i < 2 * C; i += NT) {
+        const int which = i / C, c = i % C, cv = c >> 3, k = c & 7;
+        float t = 0.f;
+        for (int j = 0; j < cnt; ++j) t += s_red[which][(planar ? cv * cnt + j : cv + j * nv) * 8 + k];
+        s_ch[which][c] = t;
+    }
+    __syncthreads();
+    if (tid < 2 * kGroups) {
+        const int which = tid / kGroups, g = tid % kGroups, gs = C / kGroups;
+        float t = 0.f;
+        for (int c = g * gs; c < (g + 1) * gs; ++c) t += s_ch[which][c];
+        part[(((int64_t)blockIdx.y * gridDim.x + blockIdx.x) * kGroups + g) * 2 + which] = t;
+    }
 }
 #endif
 
