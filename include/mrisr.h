@@ -140,6 +140,17 @@ int     mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, c
                                      float* dpred_accum, float* out1, void* workspace, size_t workspace_bytes, int N, int H,
                                      int W, const int* host_cfg, int ncfg, int loss_type, float grad_scale, void* stream);
 
+/* fp32 parity mode of the same term: fp32 activations and weights on CUDA cores (no `packed` copies; the weights are re-laid
+ * out inside the workspace on every call), for checking L6 / L7 against a float32 framework at 1e-4 the way mode MRISR_FP32
+ * does for the U-Net.  Same arguments and results as the calls above; sized for test images (a 512^2 slice costs 0.2 TFLOP
+ * per forward without tensor cores).  Workspace: zero-filled once per shape, from mrisr_vgg_workspace_bytes_fp32. */
+size_t  mrisr_vgg_workspace_bytes_fp32(int N, int H, int W, const int* host_cfg, int ncfg, int grad);
+int     mrisr_vgg_features_fp32(const float* weights, const float* img, float* feat, void* workspace, size_t workspace_bytes,
+                                int N, int H, int W, const int* host_cfg, int ncfg, void* stream);
+int     mrisr_vgg_perceptual_fwd_bwd_fp32(const float* weights, const float* pred, const float* target, float* dpred_accum,
+                                          float* out1, void* workspace, size_t workspace_bytes, int N, int H, int W,
+                                          const int* host_cfg, int ncfg, int loss_type, float grad_scale, void* stream);
+
 /* ---- fused Adam (replaces torch.optim.Adam(lr, weight_decay) of scripts/train.py:186,318) -- */
 /* L2 weight decay folded into the gradient (torch.optim.Adam semantics, not AdamW);
  * grad_scale multiplies g first (1/world_size for data parallel, 1/loss_scale for AMP). */

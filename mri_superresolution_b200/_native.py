@@ -76,6 +76,11 @@ SIGNATURES = {
                                    c_void_p, c_int, c_void_p]),
     "mrisr_vgg_perceptual_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                              c_int, c_int, c_int, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "mrisr_vgg_workspace_bytes_fp32": (c_size_t, [c_int, c_int, c_int, c_void_p, c_int, c_int]),
+    "mrisr_vgg_features_fp32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                        c_void_p, c_int, c_void_p]),
+    "mrisr_vgg_perceptual_fwd_bwd_fp32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                                  c_int, c_int, c_int, c_void_p, c_int, c_int, c_float, c_void_p]),
     "mrisr_unet_layer_engine": (c_int, [c_int, c_int, c_int, c_int]),
     "mrisr_launch_count": (ctypes.c_longlong, []),
     "mrisr_prof_enable": (c_int, [c_int]),

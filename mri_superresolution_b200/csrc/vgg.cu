@@ -62,7 +62,8 @@ __global__ void __launch_bounds__(NTHR) vgg_pack_input_kernel(const float* __res
 }
 
 // dimg[n,y,x] += scale * sum_c g[n,y,x,c] / std_c      (adjoint of repeat + normalise)
-__global__ void __launch_bounds__(NTHR) vgg_dimg_kernel(Act<bf16> g, float* __restrict__ dimg, float scale) {
+template <typename T>
+__global__ void __launch_bounds__(NTHR) vgg_dimg_kernel(Act<T> g, float* __restrict__ dimg, float scale) {
     const int64_t total = (int64_t)g.N * g.H * g.W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int xx = (int)(i % g.W), yy = (int)((i / g.W) % g.H), n = (int)(i / ((int64_t)g.W * g.H));
@@ -72,7 +73,8 @@ __global__ void __launch_bounds__(NTHR) vgg_dimg_kernel(Act<bf16> g, float* __re
     }
 }
 
-__global__ void __launch_bounds__(NTHR) vgg_maxpool_kernel(Act<bf16> a, Act<bf16> p) {
+template <typename T>
+__global__ void __launch_bounds__(NTHR) vgg_maxpool_kernel(Act<T> a, Act<T> p) {
     const int nv = a.C / 8;
     const int64_t total = (int64_t)p.N * p.H * p.W * nv;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -93,7 +95,8 @@ __global__ void __launch_bounds__(NTHR) vgg_maxpool_kernel(Act<bf16> a, Act<bf16
 
 // da[pos] = (pos is the first maximum of its 2x2 window in scan order, and a[pos] > 0) ? dp : 0
 // (max_pool2d backward followed by the ReLU backward of the conv that produced a)
-__global__ void __launch_bounds__(NTHR) vgg_pool_bwd_kernel(Act<bf16> a, Act<bf16> dp, Act<bf16> da) {
+template <typename T>
+__global__ void __launch_bounds__(NTHR) vgg_pool_bwd_kernel(Act<T> a, Act<T> dp, Act<T> da) {
     const int nv = a.C / 8;
     const int64_t total = (int64_t)dp.N * dp.H * dp.W * nv;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -125,7 +128,8 @@ __global__ void __launch_bounds__(NTHR) vgg_pool_bwd_kernel(Act<bf16> a, Act<bf1
 
 // Feature loss: partial[b] = sum |fg - ft| (L1) or sum (fg - ft)^2 (MSE); dfg = d(mean loss)/d(fg) masked by fg > 0
 // (ReLU backward of the last conv).  loss_type: 1 = L1, 2 = MSE   (utils/losses.py:128-131)
-__global__ void __launch_bounds__(NTHR) vgg_feat_loss_kernel(Act<bf16> fg, Act<bf16> ft, Act<bf16> dfg, float* __restrict__ partial,
+template <typename T>
+__global__ void __launch_bounds__(NTHR) vgg_feat_loss_kernel(Act<T> fg, Act<T> ft, Act<T> dfg, float* __restrict__ partial,
                                                              int loss_type, float inv_numel) {
     __shared__ float s_w[NTHR / 32];
     const int nv = fg.C / 8;
@@ -166,7 +170,8 @@ __global__ void vgg_loss_finalize_kernel(const float* __restrict__ partial, int 
 }
 
 // copy a padded NHWC bf16 tensor out as dense NCHW fp32 (test aid: VGGFeatureExtractor.forward parity)
-__global__ void vgg_unpack_kernel(Act<bf16> a, float* __restrict__ out) {
+template <typename T>
+__global__ void vgg_unpack_kernel(Act<T> a, float* __restrict__ out) {
     const int64_t total = (int64_t)a.N * a.C * a.H * a.W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int x = (int)(i % a.W), y = (int)((i / a.W) % a.H);
@@ -298,7 +303,120 @@ static int vgg_features(const VggNet& net, const void* packed, const float* weig
         cur = A[i];
         if (net.pool_after[i]) {
             ProfScope prof_("vgg_maxpool", s);
-            vgg_maxpool_kernel<<<grid_for((int64_t)P[i].N * P[i].H * P[i].W * (P[i].C / 8)), NTHR, 0, s>>>(A[i], P[i]);
+            vgg_maxpool_kernel<bf16><<<grid_for((int64_t)P[i].N * P[i].H * P[i].W * (P[i].C / 8)), NTHR, 0, s>>>(A[i], P[i]);
+            MRISR_LAUNCH_CHECK();
+            cur = P[i];
+        }
+    }
+    return 0;
+}
+
+
+// ---- fp32 parity mode (CUDA cores): the same term with fp32 activations and weights on conv_generic<float>, so that the
+// north_star's 1e-4 fp32-mode bound can be tested for L6 / L7 as it is for the U-Net.  Test-sized images only: a 512^2 image
+// is 204 GFLOP per forward on CUDA cores.  Layout: padded NHWC fp32; the first conv's 3 input channels are padded to 8.
+__global__ void __launch_bounds__(NTHR) vgg_pack_input_f32_kernel(const float* __restrict__ x, Act<float> dst) {
+    const int64_t total = (int64_t)dst.N * dst.H * dst.W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int xx = (int)(i % dst.W), yy = (int)((i / dst.W) % dst.H), n = (int)(i / ((int64_t)dst.W * dst.H));
+        const float v = x[i];
+        float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) o[c] = (v - c_vgg_mean[c]) / c_vgg_std[c];
+        store8(dst.at(n, yy, xx, 0), o);
+    }
+}
+// [Cout][3][3][3] -> [Cout][8][3][3] with zero input channels 3..7
+__global__ void vgg_expand_first_kernel(const float* __restrict__ w, float* __restrict__ w8, int Cout) {
+    const int total = Cout * 8 * 9;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int tap = i % 9, ci = (i / 9) % 8, co = i / 72;
+        w8[i] = ci < 3 ? w[((int64_t)co * 3 + ci) * 9 + tap] : 0.f;
+    }
+}
+// in place over the interior of a padded tensor: relu (mask == nullptr) or zero where mask <= 0
+__global__ void __launch_bounds__(NTHR) vgg_relu_mask_f32_kernel(Act<float> a, Act<float> mask) {
+    const int nv = a.C / 8;
+    const int64_t total = (int64_t)a.N * a.H * a.W * nv;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % nv);
+        const int x = (int)((i / nv) % a.W), y = (int)((i / ((int64_t)nv * a.W)) % a.H);
+        const int n = (int)(i / ((int64_t)nv * a.W * a.H));
+        float v[8], m[8];
+        load8(a.at(n, y, x, cv * 8), v);
+        if (mask.p) load8(mask.at(n, y, x, cv * 8), m);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = mask.p ? (m[k] > 0.f ? v[k] : 0.f) : fmaxf(v[k], 0.f);
+        store8(a.at(n, y, x, cv * 8), v);
+    }
+}
+
+static Act<float> make_nhwc_f32(Carve& ar, int N, int H, int W, int C) {
+    Act<float> a;
+    a.N = N; a.H = H; a.W = W; a.C = C; a.ps = C; a.cs = 8;
+    a.p = (float*)ar.take((size_t)a.rows() * C * sizeof(float));
+    return a;
+}
+struct VggWsF {
+    Act<float> X0g, X0t, Ag[kMaxCfg], At[kMaxCfg], Pg[kMaxCfg], Pt[kMaxCfg], dA[kMaxCfg], dP[kMaxCfg], dX0;
+    float* wf[kMaxCfg]; float* wd[kMaxCfg]; float* w8;
+    float* partial;
+    size_t bytes, zero_bytes;
+    VggWsF(void* base, const VggNet& net, int N, int H, int W, bool grad) {
+        Carve ar(base);
+        X0g = make_nhwc_f32(ar, N, H, W, 8);
+        X0t = make_nhwc_f32(ar, N, H, W, 8);
+        for (int i = 0; i < net.n_conv; ++i) {
+            const int h = H >> net.lvl[i], w = W >> net.lvl[i];
+            Ag[i] = make_nhwc_f32(ar, N, h, w, net.cout[i]);
+            At[i] = make_nhwc_f32(ar, N, h, w, net.cout[i]);
+            if (net.pool_after[i]) { Pg[i] = make_nhwc_f32(ar, N, h / 2, w / 2, net.cout[i]); Pt[i] = make_nhwc_f32(ar, N, h / 2, w / 2, net.cout[i]); }
+            if (grad) {
+                dA[i] = make_nhwc_f32(ar, N, h, w, net.cout[i]);
+                if (net.pool_after[i]) dP[i] = make_nhwc_f32(ar, N, h / 2, w / 2, net.cout[i]);
+            }
+        }
+        if (grad) dX0 = make_nhwc_f32(ar, N, H, W, 8);
+        zero_bytes = ar.used;                                   // everything above relies on the zero border
+        for (int i = 0; i < net.n_conv; ++i) {
+            const size_t n = (size_t)9 * net.cout[i] * (i == 0 ? 8 : net.cin[i]) * sizeof(float);
+            wf[i] = (float*)ar.take(n);
+            wd[i] = (float*)ar.take(n);
+        }
+        w8 = (float*)ar.take((size_t)net.cout[0] * 72 * sizeof(float));
+        partial = (float*)ar.take((size_t)148 * 16 * sizeof(float));
+        bytes = ar.used;
+    }
+};
+static int check_args_f32(const VggNet& net, int N, int H, int W) {
+    if (!net.ok) { set_error("vgg: bad config"); return MRISR_E_BADARG; }
+    if (N <= 0 || H <= 0 || W <= 0) { set_error("vgg: N, H, W must be positive"); return MRISR_E_BADARG; }
+    const int div = 1 << net.n_pool;
+    if (H % div || W % div) { set_error("vgg: H and W must be multiples of %d (%d poolings), got %dx%d", div, net.n_pool, H, W); return MRISR_E_SHAPE; }
+    return 0;
+}
+static int vgg_pack_f32(const VggNet& net, const float* weights, VggWsF& ws, cudaStream_t s) {
+    vgg_expand_first_kernel<<<ceil_div(net.cout[0] * 72, 256), 256, 0, s>>>(weights + net.w_off[0], ws.w8, net.cout[0]);
+    MRISR_LAUNCH_CHECK();
+    for (int i = 0; i < net.n_conv; ++i)
+        TRY(launch_pack_weights<float>(i == 0 ? ws.w8 : weights + net.w_off[i], ws.wf[i], ws.wd[i], net.cout[i], i == 0 ? 8 : net.cin[i], 3, s));
+    return 0;
+}
+static int vgg_features_f32(const VggNet& net, const float* weights, const float* img, VggWsF& ws, Act<float> X0, Act<float>* A,
+                            Act<float>* P, cudaStream_t s) {
+    vgg_pack_input_f32_kernel<<<grid_for((int64_t)X0.N * X0.H * X0.W), NTHR, 0, s>>>(img, X0);
+    MRISR_LAUNCH_CHECK();
+    const Act<float> none{nullptr, 0, 0, 0, 0};
+    Act<float> cur = X0;
+    for (int i = 0; i < net.n_conv; ++i) {
+        ConvArgs<float> a;
+        a.src1 = cur; a.src2 = none; a.w = ws.wf[i]; a.bias = weights + net.b_off[i]; a.dst = A[i]; a.stat_part = nullptr; a.ks = 3;
+        TRY(launch_conv_generic<float>(a, s));
+        vgg_relu_mask_f32_kernel<<<grid_for((int64_t)A[i].N * A[i].H * A[i].W * (A[i].C / 8)), NTHR, 0, s>>>(A[i], none);
+        MRISR_LAUNCH_CHECK();
+        cur = A[i];
+        if (net.pool_after[i]) {
+            vgg_maxpool_kernel<float><<<grid_for((int64_t)P[i].N * P[i].H * P[i].W * (P[i].C / 8)), NTHR, 0, s>>>(A[i], P[i]);
             MRISR_LAUNCH_CHECK();
             cur = P[i];
         }
@@ -359,7 +477,7 @@ int mrisr_vgg_features(const void* packed, const float* weights, const float* im
     if (ws.bytes > workspace_bytes) { set_error("vgg: workspace too small (%zu > %zu)", ws.bytes, workspace_bytes); return MRISR_E_WORKSPACE; }
     cudaStream_t s = (cudaStream_t)stream;
     TRY(vgg_features(net, packed, weights, img, ws.X0g, ws.Ag, ws.Pg, s));
-    vgg_unpack_kernel<<<148 * 4, 256, 0, s>>>(ws.Ag[net.n_conv - 1], feat);
+    vgg_unpack_kernel<bf16><<<148 * 4, 256, 0, s>>>(ws.Ag[net.n_conv - 1], feat);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -385,7 +503,7 @@ int mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, const
         const Act<bf16>& fg = ws.Ag[L];
         const int64_t numel = (int64_t)fg.N * fg.C * fg.H * fg.W;
         const int nb = grid_for(numel / 8);
-        vgg_feat_loss_kernel<<<nb, NTHR, 0, s>>>(fg, ws.At[L], grad ? ws.dA[L] : none, ws.partial, loss_type, (float)(1.0 / (double)numel));
+        vgg_feat_loss_kernel<bf16><<<nb, NTHR, 0, s>>>(fg, ws.At[L], grad ? ws.dA[L] : none, ws.partial, loss_type, (float)(1.0 / (double)numel));
         MRISR_LAUNCH_CHECK();
         vgg_loss_finalize_kernel<<<1, 32, 0, s>>>(ws.partial, nb, 1.0 / (double)numel, out1);
         MRISR_LAUNCH_CHECK();
@@ -404,15 +522,87 @@ int mrisr_vgg_perceptual_fwd_bwd(const void* packed, const float* weights, const
         if (pooled_input) {
             ProfScope prof_("vgg_pool_bwd", s);
             const Act<bf16>& dp = ws.dP[i - 1];
-            vgg_pool_bwd_kernel<<<grid_for((int64_t)dp.N * dp.H * dp.W * (dp.C / 8)), NTHR, 0, s>>>(ws.Ag[i - 1], dp, ws.dA[i - 1]);
+            vgg_pool_bwd_kernel<bf16><<<grid_for((int64_t)dp.N * dp.H * dp.W * (dp.C / 8)), NTHR, 0, s>>>(ws.Ag[i - 1], dp, ws.dA[i - 1]);
             MRISR_LAUNCH_CHECK();
         }
     }
     {
         ProfScope prof_("vgg_dimg", s);
-        vgg_dimg_kernel<<<grid_for((int64_t)N * H * W), NTHR, 0, s>>>(ws.dX0, dpred_accum, grad_scale);
+        vgg_dimg_kernel<bf16><<<grid_for((int64_t)N * H * W), NTHR, 0, s>>>(ws.dX0, dpred_accum, grad_scale);
         MRISR_LAUNCH_CHECK();
     }
+    return 0;
+}
+
+
+/* ---- fp32 parity mode of the same term (CUDA cores; include/mrisr.h) ---- */
+size_t mrisr_vgg_workspace_bytes_fp32(int N, int H, int W, const int* host_cfg, int ncfg, int grad) {
+    VggNet net(host_cfg, ncfg);
+    if (check_args_f32(net, N, H, W)) return 0;
+    return VggWsF(nullptr, net, N, H, W, grad != 0).bytes;
+}
+
+int mrisr_vgg_features_fp32(const float* weights, const float* img, float* feat, void* workspace, size_t workspace_bytes, int N,
+                            int H, int W, const int* host_cfg, int ncfg, void* stream) {
+    VggNet net(host_cfg, ncfg);
+    int rc = check_args_f32(net, N, H, W);
+    if (rc) return rc;
+    if (!weights || !img || !feat || !workspace) { set_error("vgg_features_fp32: null pointer"); return MRISR_E_BADARG; }
+    VggWsF ws(workspace, net, N, H, W, false);
+    if (ws.bytes > workspace_bytes) { set_error("vgg: workspace too small (%zu > %zu)", ws.bytes, workspace_bytes); return MRISR_E_WORKSPACE; }
+    cudaStream_t s = (cudaStream_t)stream;
+    TRY(vgg_pack_f32(net, weights, ws, s));
+    TRY(vgg_features_f32(net, weights, img, ws, ws.X0g, ws.Ag, ws.Pg, s));
+    vgg_unpack_kernel<float><<<148 * 4, 256, 0, s>>>(ws.Ag[net.n_conv - 1], feat);
+    MRISR_LAUNCH_CHECK();
+    return 0;
+}
+
+int mrisr_vgg_perceptual_fwd_bwd_fp32(const float* weights, const float* pred, const float* target, float* dpred_accum, float* out1,
+                                      void* workspace, size_t workspace_bytes, int N, int H, int W, const int* host_cfg, int ncfg,
+                                      int loss_type, float grad_scale, void* stream) {
+    VggNet net(host_cfg, ncfg);
+    int rc = check_args_f32(net, N, H, W);
+    if (rc) return rc;
+    if (!weights || !pred || !target || !out1 || !workspace) { set_error("vgg_perceptual_fp32: null pointer"); return MRISR_E_BADARG; }
+    if (loss_type != 1 && loss_type != 2) { set_error("vgg_perceptual: loss_type must be 1 (L1) or 2 (MSE)"); return MRISR_E_BADARG; }
+    const bool grad = dpred_accum != nullptr;
+    VggWsF ws(workspace, net, N, H, W, grad);
+    if (ws.bytes > workspace_bytes) { set_error("vgg: workspace too small (%zu > %zu)", ws.bytes, workspace_bytes); return MRISR_E_WORKSPACE; }
+    cudaStream_t s = (cudaStream_t)stream;
+    const Act<float> none{nullptr, 0, 0, 0, 0};
+    const int L = net.n_conv - 1;
+    TRY(vgg_pack_f32(net, weights, ws, s));
+    TRY(vgg_features_f32(net, weights, target, ws, ws.X0t, ws.At, ws.Pt, s));
+    TRY(vgg_features_f32(net, weights, pred, ws, ws.X0g, ws.Ag, ws.Pg, s));
+    {
+        const Act<float>& fg = ws.Ag[L];
+        const int64_t numel = (int64_t)fg.N * fg.C * fg.H * fg.W;
+        const int nb = grid_for(numel / 8);
+        vgg_feat_loss_kernel<float><<<nb, NTHR, 0, s>>>(fg, ws.At[L], grad ? ws.dA[L] : none, ws.partial, loss_type, (float)(1.0 / (double)numel));
+        MRISR_LAUNCH_CHECK();
+        vgg_loss_finalize_kernel<<<1, 32, 0, s>>>(ws.partial, nb, 1.0 / (double)numel, out1);
+        MRISR_LAUNCH_CHECK();
+    }
+    if (!grad) return 0;
+    for (int i = L; i >= 0; --i) {
+        const bool pooled_input = i > 0 && net.pool_after[i - 1];
+        ConvArgs<float> a;
+        a.src1 = ws.dA[i]; a.src2 = none; a.w = ws.wd[i]; a.bias = nullptr; a.stat_part = nullptr; a.ks = 3;
+        a.dst = i == 0 ? ws.dX0 : (pooled_input ? ws.dP[i - 1] : ws.dA[i - 1]);
+        TRY(launch_conv_generic<float>(a, s));
+        if (i > 0 && !pooled_input) {
+            const Act<float>& d = ws.dA[i - 1];
+            vgg_relu_mask_f32_kernel<<<grid_for((int64_t)d.N * d.H * d.W * (d.C / 8)), NTHR, 0, s>>>(d, ws.Ag[i - 1]);
+            MRISR_LAUNCH_CHECK();
+        } else if (pooled_input) {
+            const Act<float>& dp = ws.dP[i - 1];
+            vgg_pool_bwd_kernel<float><<<grid_for((int64_t)dp.N * dp.H * dp.W * (dp.C / 8)), NTHR, 0, s>>>(ws.Ag[i - 1], dp, ws.dA[i - 1]);
+            MRISR_LAUNCH_CHECK();
+        }
+    }
+    vgg_dimg_kernel<float><<<grid_for((int64_t)N * H * W), NTHR, 0, s>>>(ws.dX0, dpred_accum, grad_scale);
+    MRISR_LAUNCH_CHECK();
     return 0;
 }
 

@@ -122,7 +122,8 @@ def train(cfg: TrainConfig, train_batches: Callable[[], Iterable], val_batches: 
                                                            patience=max(cfg.patience // 2, 0))               # :189
     criterion = CombinedLoss(ssim_weight=cfg.ssim_weight, perceptual_weight=cfg.perceptual_weight,
                              vgg_layer_idx=cfg.vgg_layer_idx, perceptual_loss_type=cfg.perceptual_loss_type,
-                             window_size=11, sigma=1.5, val_range=1.0, device=device, vgg_weights=cfg.vgg_weights)  # :236-245
+                             window_size=11, sigma=1.5, val_range=1.0, device=device, vgg_weights=cfg.vgg_weights,
+                             precision=cfg.precision)                                                      # :236-245
     ssim_metric = SSIM(window_size=11, sigma=1.5, val_range=1.0, device=device)                                      # :248
     os.makedirs(cfg.checkpoint_dir, exist_ok=True)
     log_message({"model_type": cfg.model_type, "batch_size": cfg.batch_size, "epochs": cfg.epochs,

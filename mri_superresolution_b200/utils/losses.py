@@ -116,9 +116,10 @@ class CombinedLoss(nn.Module):
     with l1_w = 1 - ssim_w - perceptual_w (utils/losses.py:153-240)."""
 
     def __init__(self, ssim_weight=0.5, perceptual_weight=0.0, vgg_layer_idx=35, perceptual_loss_type="l1",
-                 window_size=11, sigma=1.5, val_range=1.0, device=torch.device("cpu"), vgg_weights=None):
+                 window_size=11, sigma=1.5, val_range=1.0, device=torch.device("cpu"), vgg_weights=None, precision=None):
         """``vgg_weights`` (extra, optional): (weight, bias) pairs for the VGG19 convolutions instead of torchvision's
-        ImageNet download (utils/losses.py:90) -- for offline machines and tests."""
+        ImageNet download (utils/losses.py:90) -- for offline machines and tests.  ``precision`` (extra): 'fp32' runs the
+        perceptual term in its CUDA-core parity mode (the L1 + SSIM kernel is fp32 in either mode)."""
         super().__init__()
         if not (0 <= ssim_weight <= 1):
             raise ValueError("ssim_weight must be between 0 and 1")
@@ -139,7 +140,7 @@ class CombinedLoss(nn.Module):
         if self.use_perceptual:
             from .perceptual import PerceptualLoss
             self.perceptual_loss = PerceptualLoss(feature_layer_idx=vgg_layer_idx, loss_type=perceptual_loss_type,
-                                                  vgg_weights=vgg_weights)
+                                                  vgg_weights=vgg_weights, precision=precision)
         else:
             self.perceptual_loss = None
         self._holder = {}

@@ -5,11 +5,14 @@ constructor keywords, ``feature_extractor.features`` (an ``nn.Sequential`` of th
 ``feature_layer_idx``, frozen), ``mean`` / ``std`` buffers, ``criterion`` and the ``ValueError`` for an unknown loss
 type (:133).  The computation itself -- both feature passes, the feature L1 / MSE and the data gradient of the
 generated branch -- is one C-ABI call (``mrisr_vgg_perceptual_fwd_bwd``): bf16 operands, fp32 accumulation, the ReLU
-and its backward fused into the convolution epilogues.  No CPU fallback.
+and its backward fused into the convolution epilogues.  ``precision='fp32'`` (or MRISR_PRECISION=fp32) runs the same
+term with fp32 activations and weights on CUDA cores (``mrisr_vgg_perceptual_fwd_bwd_fp32``): the parity mode the 1e-4
+bound of the north star is tested in, sized for test images.  No CPU fallback.
 """
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -42,8 +45,11 @@ class VGGFeatureExtractor(nn.Module):
     (utils/losses.py:90), which needs the weight file in the torch hub cache."""
 
     def __init__(self, feature_layer_idx: int = 35, use_maxpool: bool = False,
-                 weights: Optional[Sequence[Tuple[torch.Tensor, torch.Tensor]]] = None):
+                 weights: Optional[Sequence[Tuple[torch.Tensor, torch.Tensor]]] = None, precision: Optional[str] = None):
         super().__init__()
+        self.precision = precision or os.environ.get("MRISR_PRECISION", "bf16")
+        if self.precision not in ("bf16", "fp32"):
+            raise ValueError(f"precision must be 'bf16' or 'fp32', got {self.precision!r}")
         kinds = _vgg19_layers(feature_layer_idx)
         if not kinds or kinds[-1][0] != "relu":
             raise ValueError("feature_layer_idx must select a ReLU layer of vgg19.features (e.g. 35 = relu5_4); the fused "
@@ -97,11 +103,12 @@ class VGGFeatureExtractor(nn.Module):
         return flat, packed
 
     def _workspace(self, n, h, w, grad, device):
-        key = (n, h, w, bool(grad), device)
+        key = (n, h, w, bool(grad), device, self.precision)
 
         def alloc():
             arr, nc = self._cfg_array()
-            nbytes = _native.lib().mrisr_vgg_workspace_bytes(n, h, w, arr, nc, 1 if grad else 0)
+            size_fn = _native.lib().mrisr_vgg_workspace_bytes_fp32 if self.precision == "fp32" else _native.lib().mrisr_vgg_workspace_bytes
+            nbytes = size_fn(n, h, w, arr, nc, 1 if grad else 0)
             if nbytes == 0:
                 raise ValueError(_native.lib().mrisr_last_error().decode())
             return torch.zeros(nbytes, dtype=torch.uint8, device=device)     # zero borders are an invariant of the kernels
@@ -134,8 +141,12 @@ class VGGFeatureExtractor(nn.Module):
         pools = sum(1 for c in self.cfg if c < 0)
         cout = [c for c in self.cfg if c > 0][-1]
         feat = torch.empty(n, cout, h >> pools, w >> pools, dtype=torch.float32, device=img.device)
-        rc = _native.lib().mrisr_vgg_features(_native.ptr(packed), _native.ptr(flat), _native.ptr(img), _native.ptr(feat),
-                                              _native.ptr(ws), ws.numel(), n, h, w, arr, nc, _native.stream_ptr())
+        if self.precision == "fp32":
+            rc = _native.lib().mrisr_vgg_features_fp32(_native.ptr(flat), _native.ptr(img), _native.ptr(feat), _native.ptr(ws),
+                                                       ws.numel(), n, h, w, arr, nc, _native.stream_ptr())
+        else:
+            rc = _native.lib().mrisr_vgg_features(_native.ptr(packed), _native.ptr(flat), _native.ptr(img), _native.ptr(feat),
+                                                  _native.ptr(ws), ws.numel(), n, h, w, arr, nc, _native.stream_ptr())
         _native.check(rc, "mrisr_vgg_features")
         return feat
 
@@ -154,9 +165,14 @@ class _PerceptualFunction(torch.autograd.Function):
         arr, nc = extractor._cfg_array()
         out1 = torch.empty(1, dtype=torch.float32, device=pred.device)
         dpred = torch.zeros_like(pred) if need_grad else None
-        rc = _native.lib().mrisr_vgg_perceptual_fwd_bwd(
-            _native.ptr(packed), _native.ptr(flat), _native.ptr(pred), _native.ptr(tgt), _native.ptr(dpred), _native.ptr(out1),
-            _native.ptr(ws), ws.numel(), n, h, w, arr, nc, int(loss_type), 1.0, _native.stream_ptr())
+        if extractor.precision == "fp32":
+            rc = _native.lib().mrisr_vgg_perceptual_fwd_bwd_fp32(
+                _native.ptr(flat), _native.ptr(pred), _native.ptr(tgt), _native.ptr(dpred), _native.ptr(out1),
+                _native.ptr(ws), ws.numel(), n, h, w, arr, nc, int(loss_type), 1.0, _native.stream_ptr())
+        else:
+            rc = _native.lib().mrisr_vgg_perceptual_fwd_bwd(
+                _native.ptr(packed), _native.ptr(flat), _native.ptr(pred), _native.ptr(tgt), _native.ptr(dpred), _native.ptr(out1),
+                _native.ptr(ws), ws.numel(), n, h, w, arr, nc, int(loss_type), 1.0, _native.stream_ptr())
         _native.check(rc, "mrisr_vgg_perceptual_fwd_bwd")
         ctx.shape, ctx.dtype = tuple(generated.shape), generated.dtype
         if need_grad:
@@ -172,9 +188,9 @@ class _PerceptualFunction(torch.autograd.Function):
 class PerceptualLoss(nn.Module):
     """criterion(VGG(generated), no_grad VGG(target)) (utils/losses.py:120-151)."""
 
-    def __init__(self, feature_layer_idx=35, loss_type="l1", vgg_weights=None):
+    def __init__(self, feature_layer_idx=35, loss_type="l1", vgg_weights=None, precision=None):
         super().__init__()
-        self.feature_extractor = VGGFeatureExtractor(feature_layer_idx=feature_layer_idx, weights=vgg_weights)
+        self.feature_extractor = VGGFeatureExtractor(feature_layer_idx=feature_layer_idx, weights=vgg_weights, precision=precision)
         if loss_type == "l1":
             self.criterion = nn.L1Loss()
             self._loss_code = 1

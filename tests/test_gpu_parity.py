@@ -493,6 +493,50 @@ def test_perceptual_target_branch_has_no_gradient_and_l2_alias(golden_dir):
 
 
 @pytest.mark.gpu
+def test_vgg_fp32_parity_mode_features_and_loss(golden_dir):
+    """precision='fp32' of the perceptual term (mrisr_vgg_*_fp32, CUDA cores): the north star's fp32-mode bound, 1e-4, for L6 /
+    L7 -- features against the float32 restatement, then CombinedLoss values against the reference run recorded in
+    tests/golden/perceptual.npz and the gradient against the reference autograd gradient."""
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    from mri_superresolution_b200.utils.perceptual import VGGFeatureExtractor
+    d = _golden(golden_dir, "perceptual")
+    vggp = LO.make_vgg_params(seed=1235)
+    ext = VGGFeatureExtractor(35, weights=vggp, precision="fp32")
+    feat = ext(torch.from_numpy(d["pred"]).to(_dev()))
+    ref = LO.vgg_features(vggp, torch.from_numpy(d["pred"]))
+    e = float((feat.cpu().double() - ref.double()).norm() / ref.double().norm())
+    assert e < 1e-4, e
+    for tag in ("a", "b", "c"):
+        sw, pw, typ = [float(v) for v in d[f"{tag}:cfg"]]
+        crit = CombinedLoss(ssim_weight=sw, perceptual_weight=pw, perceptual_loss_type="l1" if typ == 1 else "mse",
+                            vgg_weights=vggp, precision="fp32")
+        p = torch.from_numpy(d["pred"]).to(_dev()).requires_grad_(True)
+        loss = crit(p, torch.from_numpy(d["target"]).to(_dev()))
+        loss.backward()
+        assert abs(loss.item() - float(d[f"{tag}:loss"])) < 1e-4 * abs(float(d[f"{tag}:loss"])), tag
+        g, r = p.grad.double().cpu().reshape(-1), torch.from_numpy(d[f"{tag}:grad"]).double().reshape(-1)
+        # fp32 accumulation order differs from cuDNN/MKL's; a ReLU or pooling tie may route differently at a handful of pixels
+        assert float((g - r).norm() / r.norm()) < 2e-3, (tag, float((g - r).norm() / r.norm()))
+        assert float((g * r).sum() / (g.norm() * r.norm())) > 0.99999
+
+
+@pytest.mark.gpu
+def test_vgg_fp32_mode_agrees_with_bf16_mode_and_rejects_bad_precision(golden_dir):
+    from mri_superresolution_b200.utils.perceptual import PerceptualLoss
+    d = _golden(golden_dir, "perceptual")
+    vggp = LO.make_vgg_params(seed=1235)
+    p, t = torch.from_numpy(d["pred"]).to(_dev()), torch.from_numpy(d["target"]).to(_dev())
+    a = PerceptualLoss(35, "l1", vgg_weights=vggp, precision="fp32")(p, t).item()
+    b = PerceptualLoss(35, "l1", vgg_weights=vggp, precision="bf16")(p, t).item()
+    assert abs(a - b) < 2e-2 * abs(a)
+    # twice through the same workspace (zero-border invariant survives a call), and a shallower prefix with a pooling at the end of a block
+    crit = PerceptualLoss(8, "mse", vgg_weights=vggp[:4], precision="fp32")
+    assert crit(p, t).item() == crit(p, t).item()
+    with pytest.raises(ValueError):
+        PerceptualLoss(35, "l1", vgg_weights=vggp, precision="fp16")
+
+
+@pytest.mark.gpu
 def test_device_prefetcher_order_and_reuse():
     """DevicePrefetcher hands out every host batch once, in order, while the next one is being staged."""
     from mri_superresolution_b200.utils.prefetch import DevicePrefetcher
