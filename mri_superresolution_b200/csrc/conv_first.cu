@@ -17,31 +17,55 @@ constexpr int kUnitsBwd = 64;
 // output vectors per thread and block of conv_first_kernel.  Swept on B200 in round 2 (64, 256 vectors): 0.199 -> 0.206, 0.217 ms,
 // the fixed per-block price (72 scalar weight loads, the statistics reduction) is not what bounds it.
 inline int units_fwd() { return 16; }
+// rows per block: `units` output vectors per thread, capped so that the staged input rows stay within `tile_bytes`
+inline int rows_first(int W, int nv, int units, size_t tile_bytes) {
+    int r = rows_per_block(W, nv, NTHR, units);
+    const int cap = (int)(tile_bytes / ((size_t)(W + 2) * sizeof(bf16))) - 2;
+    if (r > cap) r = cap;
+    return r < 1 ? 1 : r;
+}
+inline int rows_fwd(int W, int nv) { return rows_first(W, nv, units_fwd(), 24 * 1024); }
+inline int rows_bwd(int W, int nv) { return rows_first(W, nv, kUnitsBwd, 8 * 1024); }      // + 16 KB ring + 21 KB static < 48 KB
 
+// The input rows a block touches (its rows +- 1, whole padded width: ONE contiguous run of the padded-linear tensor) are staged
+// in shared memory first, all loads in flight at once: read per pixel from global memory every column step of every warp waited
+// on its own compulsory miss (~1.6 k cycles per step against 135 instructions of work; ncu: 48 % of cycles without an eligible warp).
 // x: [N][H+2][W+2][1] (zero border), w: packed [tap][1][Cout] bf16, dst planar-8 [Cout]
 __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf16* __restrict__ w, Act<bf16> dst,
                                                           float* __restrict__ stat_part, int rows_pb) {
+    extern __shared__ __align__(16) unsigned char cf_smem[];
+    bf16* s_x = reinterpret_cast<bf16*>(cf_smem);               // [(rows + 2)][W + 2]
     __shared__ float s_red[2][NTHR * 8];
     __shared__ float s_ch[2][512];
     const int C = dst.C, nv = C / 8, tid = threadIdx.x, n = blockIdx.y;
     const RowMap m = row_map(dst, NTHR, tid);
+    const int pw = x.W + 2;
+    const int y_begin = blockIdx.x * rows_pb, y_end = min(dst.H, y_begin + rows_pb);
+    {
+        const bf16* src = x.p + x.pix(n, y_begin - 1, -1);
+        const int count = (y_end - y_begin + 2) * pw;
+        for (int i = tid; i < count; i += NTHR) s_x[i] = src[i];
+    }
     float s1[8], s2[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+    float wr[9][8];
     if (m.active) {
-        float wr[9][8];
 #pragma unroll
         for (int t = 0; t < 9; ++t)
 #pragma unroll
             for (int k = 0; k < 8; ++k) wr[t][k] = to_f(w[t * C + m.cv * 8 + k]);
-        const int pw = x.W + 2;
-        const int y_end = min(dst.H, (int)(blockIdx.x + 1) * rows_pb);
-        for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
-            const bf16* xr = x.p + x.pix(n, y, 0);                  // padded-linear index of (y, 0); taps read +-1 row / col
-            for (int xx = m.x0; xx < dst.W; xx += m.xstep) {
+    }
+    __syncthreads();
+    if (m.active) {
+        const int dstep = m.xstep * (dst.ps ? dst.ps : dst.C);
+        for (int y = y_begin; y < y_end; ++y) {
+            const bf16* xu = s_x + (y - y_begin) * pw + m.x0 + 1;  // tap (-1, 0) of column x0; the tile starts at (y_begin - 1, -1)
+            bf16* dp = dst.at(n, y, m.x0, m.cv * 8);
+            for (int xx = m.x0; xx < dst.W; xx += m.xstep, xu += m.xstep, dp += dstep) {
                 float v[9];
 #pragma unroll
-                for (int t = 0; t < 9; ++t) v[t] = to_f(xr[xx + (t / 3 - 1) * pw + (t % 3 - 1)]);
+                for (int t = 0; t < 3; ++t) { v[t] = to_f(xu[t - 1]); v[3 + t] = to_f(xu[pw + t - 1]); v[6 + t] = to_f(xu[2 * pw + t - 1]); }
                 float o[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -52,7 +76,7 @@ __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf1
                     s1[k] += acc;
                     s2[k] = fmaf(acc, acc, s2[k]);
                 }
-                store8(dst.at(n, y, xx, m.cv * 8), o);
+                store8(dp, o);
             }
         }
     }
@@ -78,26 +102,64 @@ __global__ void __launch_bounds__(NTHR) conv_first_kernel(Act<bf16> x, const bf1
 }
 
 // partial[(n * slots + slot)][tap][C] = block sums of X[p + shift(tap)] * dY[p][c]
+// Same staging of the input rows; the gradient vectors (16 B per thread and step, streamed once from HBM) run through a
+// per-thread cp.async ring kWfDepth steps deep, so a step waits on shared memory instead of a DRAM round trip.
+constexpr int kWfDepth = 4;
+__device__ __forceinline__ void wf_cp16(void* sdst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory");
+}
 __global__ void __launch_bounds__(NTHR) wgrad_first_kernel(Act<bf16> x, Act<bf16> dy, float* __restrict__ partial, int rows_pb) {
+    extern __shared__ __align__(16) unsigned char cf_smem[];
+    uint4* s_g = reinterpret_cast<uint4*>(cf_smem);                         // [kWfDepth][NTHR]
+    bf16* s_x = reinterpret_cast<bf16*>(cf_smem + (size_t)kWfDepth * NTHR * 16);   // [(rows + 2)][W + 2]
     __shared__ float s_w[NTHR / 32][72];
     __shared__ float s_wn[NTHR / 32][8][72];
     const int C = dy.C, nv = C / 8, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n = blockIdx.y;
     const RowMap m = row_map(dy, NTHR, tid);
+    const int pw = x.W + 2;
+    const int y_begin = blockIdx.x * rows_pb, y_end = min(dy.H, y_begin + rows_pb);
+    // this thread's steps: rows y_begin .. y_end - 1, columns x0, x0 + xstep, ... (same count on every row)
+    const int per_row = m.active && m.x0 < dy.W ? (dy.W - m.x0 + m.xstep - 1) / m.xstep : 0;
+    const int steps = per_row * (y_end - y_begin);
+    const int gstep = m.xstep * (dy.ps ? dy.ps : dy.C);
+    const int64_t grow = (int64_t)pw * (dy.ps ? dy.ps : dy.C);              // elements between the same column of two rows
+    const bf16* gp = m.active ? dy.at(n, y_begin, m.x0, m.cv * 8) : dy.p;   // next vector to fetch
+    int fcol = 0;                                                            // its column step inside the row
+    auto fetch = [&](int slot) {
+        wf_cp16(&s_g[slot * NTHR + tid], gp);
+        if (++fcol == per_row) { fcol = 0; gp += grow - (int64_t)(per_row - 1) * gstep; } else gp += gstep;
+    };
+#pragma unroll
+    for (int d = 0; d < kWfDepth - 1; ++d) {
+        if (d < steps) fetch(d);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    {
+        const bf16* src = x.p + x.pix(n, y_begin - 1, -1);
+        const int count = (y_end - y_begin + 2) * pw;
+        for (int i = tid; i < count; i += NTHR) s_x[i] = src[i];
+    }
     float acc[9][8];
 #pragma unroll
     for (int t = 0; t < 9; ++t)
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[t][k] = 0.f;
-    if (m.active) {
-        const int pw = x.W + 2;
-        const int y_end = min(dy.H, (int)(blockIdx.x + 1) * rows_pb);
-        for (int y = blockIdx.x * rows_pb; y < y_end; ++y) {
-            const bf16* xr = x.p + x.pix(n, y, 0);
-            for (int xx = m.x0; xx < dy.W; xx += m.xstep) {
+    __syncthreads();
+    {
+        int it = 0;
+        for (int y = y_begin; y < y_end && per_row; ++y) {
+            const bf16* xu = s_x + (y - y_begin) * pw + m.x0 + 1;
+            for (int c = 0; c < per_row; ++c, ++it, xu += m.xstep) {
+                if (it + kWfDepth - 1 < steps) fetch((it + kWfDepth - 1) % kWfDepth);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                asm volatile("cp.async.wait_group %0;" ::"n"(kWfDepth - 1) : "memory");
+                const uint4 raw = s_g[(it % kWfDepth) * NTHR + tid];         // written by this thread's own copies only
+                const uint32_t r4[4] = {raw.x, raw.y, raw.z, raw.w};
                 float g[8], v[9];
-                load8(dy.at(n, y, xx, m.cv * 8), g);
 #pragma unroll
-                for (int t = 0; t < 9; ++t) v[t] = to_f(xr[xx + (t / 3 - 1) * pw + (t % 3 - 1)]);
+                for (int i = 0; i < 4; ++i) { g[2 * i] = __uint_as_float(r4[i] << 16); g[2 * i + 1] = __uint_as_float(r4[i] & 0xffff0000u); }
+#pragma unroll
+                for (int t = 0; t < 3; ++t) { v[t] = to_f(xu[t - 1]); v[3 + t] = to_f(xu[pw + t - 1]); v[6 + t] = to_f(xu[2 * pw + t - 1]); }
 #pragma unroll
                 for (int t = 0; t < 9; ++t)
 #pragma unroll
@@ -169,9 +231,9 @@ bool conv_first_supported(const Act<__nv_bfloat16>& src, const Act<__nv_bfloat16
     const int nv = dst.C / 8;
     return ks == 3 && src.C == 1 && dst.C % 8 == 0 && dst.C <= 64 && (NTHR / nv) % 32 == 0 && NTHR % nv == 0 && 32 % nv == 0;
 }
-int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_per_block(W, Cout / 8, NTHR, units_fwd())); }
+int conv_first_stat_slots(int H, int W, int Cout) { return ceil_div(H, rows_fwd(W, Cout / 8)); }
 size_t wgrad_first_scratch_elems(int N, int H, int W, int Cout) {
-    return (size_t)N * ceil_div(H, rows_per_block(W, Cout / 8, NTHR, kUnitsBwd)) * 9 * Cout;
+    return (size_t)N * ceil_div(H, rows_bwd(W, Cout / 8)) * 9 * Cout;
 }
 
 int launch_conv_first(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s) {
@@ -183,8 +245,14 @@ int launch_conv_first(const ConvArgs<__nv_bfloat16>& a, cudaStream_t s) {
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-    const int rpb = rows_per_block(a.dst.W, a.dst.C / 8, NTHR, units_fwd());
-    conv_first_kernel<<<dim3(ceil_div(a.dst.H, rpb), a.dst.N), NTHR, 0, s>>>(a.src1, a.w, a.dst, a.stat_part, rpb);
+    const int rpb = rows_fwd(a.dst.W, a.dst.C / 8);
+    const size_t smem = (size_t)(rpb + 2) * (a.dst.W + 2) * sizeof(__nv_bfloat16);
+    static PerDeviceFlag attr_pd; bool& attr_done = attr_pd.cur();
+    if (!attr_done) {                                             // very wide images: one staged row triple may pass the 48 KB default
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(conv_first_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_done = true;
+    }
+    conv_first_kernel<<<dim3(ceil_div(a.dst.H, rpb), a.dst.N), NTHR, smem, s>>>(a.src1, a.w, a.dst, a.stat_part, rpb);
     MRISR_LAUNCH_CHECK();
     return 0;
 }
@@ -198,9 +266,15 @@ int launch_wgrad_first(const WgradArgs<__nv_bfloat16>& a, cudaStream_t s) {
         tag = prof_intern(tbuf);
     }
     ProfScope prof_(tag, s);
-    const int rpb = rows_per_block(a.dy.W, a.dy.C / 8, NTHR, kUnitsBwd);
+    const int rpb = rows_bwd(a.dy.W, a.dy.C / 8);
     const int slots = ceil_div(a.dy.H, rpb);
-    wgrad_first_kernel<<<dim3(slots, a.dy.N), NTHR, 0, s>>>(a.src1, a.dy, a.partial, rpb);
+    const size_t smem = (size_t)kWfDepth * NTHR * 16 + (size_t)(rpb + 2) * (a.dy.W + 2) * sizeof(__nv_bfloat16);
+    static PerDeviceFlag attr_pd; bool& attr_done = attr_pd.cur();
+    if (!attr_done) {
+        MRISR_CUDA_CHECK(cudaFuncSetAttribute(wgrad_first_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_done = true;
+    }
+    wgrad_first_kernel<<<dim3(slots, a.dy.N), NTHR, smem, s>>>(a.src1, a.dy, a.partial, rpb);
     MRISR_LAUNCH_CHECK();
     wgrad_first_reduce_kernel<<<9 * a.dy.C, 256, 0, s>>>(a.partial, a.dw, slots * a.dy.N, a.dy.C);
     MRISR_LAUNCH_CHECK();
