@@ -1,4 +1,4 @@
-// Incremental unit addressing of the fused GroupNorm-backward kernel (gn_bwd.cu, builds with -DMRISR_GNBWD_INCR).
+// Incremental unit addressing of the fused GroupNorm-backward kernel (gn_bwd.cu: the kinds with Incr<KIND>::on).
 // Plain C++ so that tests/test_host_logic.py can compile it with g++ and replay the kernel's issue / apply order on the host.
 //
 // A thread owns the units pi = p0 + i * pstep (i = 0, 1, ...) of its CTA's rows, unit pi at (row, column) = (pi / UW, pi % UW).

@@ -173,9 +173,8 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ scratch, float*
 template <typename T>
 int launch_head_blend(const BlendArgs<T>& a, cudaStream_t s) {
     ProfScope prof_("head_blend", s);
-    // 2x2 quads per thread and block (MRISR_HEADBLEND_UPT; 2 in the measured build).  A block first folds both branches'
-    // GroupNorm into 80 per-thread constants (160 scalar loads, 40 integer divisions: load_blend_ctx), which at 2 quads per
-    // thread is about as long as the blend itself (527 instructions per quad); not swept yet.
+    // A block first folds both branches' GroupNorm into 80 per-thread constants (160 scalar loads, 40 integer divisions:
+    // load_blend_ctx), about as long as two quads of the blend itself (527 instructions per quad): long blocks amortise it.
     constexpr int upt = 8;       // 2x2 quads per thread: swept on B200 in round 2, 2 -> 8: 0.471 -> 0.392 ms per step
     const int rpb = rows_per_block(a.r_ps.W, a.xm.C / 8, NTHR, upt);
     head_blend_kernel<T><<<dim3(ceil_div(a.r_ps.H, rpb), a.xm.N), NTHR, 0, s>>>(a, rpb);

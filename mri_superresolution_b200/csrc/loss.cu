@@ -190,14 +190,15 @@ __global__ void __launch_bounds__(NTHR, 2) l1_ssim_kernel(const float* __restric
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// STAGED (MRISR_SSIM_SPLIT=1, default off, not yet measured on a B200): the same loss and gradient as l1_ssim_kernel<R, true>
-// in two kernels with halo R each instead of one kernel with halo 2R.  The fused tile recomputes the five forward maps on a
+// Training path (default since round 2; MRISR_SSIM_SPLIT=0 keeps the fused kernel: 0.63 -> 0.57 ms per 64 x 512^2 batch on B200,
+// profiles/r02_staged_variants.md): the same loss and gradient as l1_ssim_kernel<R, true> in two kernels with halo R each
+// instead of one kernel with halo 2R.  The fused tile recomputes the five forward maps on a
 // (T + 2R)^2 region to have the three derivative maps where the backward filters need them: ~430 FMA per output pixel
 // against 176 for the separable filters themselves.  Here the forward kernel writes the derivative maps of its OWN pixels
 // (d1, d11, d12: 12 B per pixel to scratch) and the gradient kernel filters them with halo R: ~203 FMA per pixel and
 // +24 B per pixel of HBM traffic (0.07 ms at batch 64), ~40 KB of shared memory per block instead of 149 KB.
-// Every map value is produced by the same run_filter calls in the same tap order as in the fused kernel, so the gradient is
-// expected to be bit-identical to the fused kernel's.
+// Every map value is produced by the same run_filter calls in the same tap order as in the fused kernel: the two paths
+// agree to fp32 rounding (tests/test_gpu_knobs.py compares a whole train step under MRISR_SSIM_SPLIT=0 with the default).
 constexpr int NTHR2 = 256;
 
 template <int R>
@@ -464,7 +465,7 @@ static size_t partial_bytes(int N, int H, int W) {
     return (((size_t)N * ceil_div(H, T) * ceil_div(W, T) * 2 * sizeof(float)) + 255) & ~(size_t)255;
 }
 size_t l1_ssim_scratch_bytes(int N, int H, int W) {
-    // block partials, and (staged two-kernel variant only) the three derivative maps
+    // block partials, and (two-kernel training path) the three derivative maps
     return partial_bytes(N, H, W) + (ssim_split_enabled() ? (size_t)3 * N * H * W * sizeof(float) : 0);
 }
 

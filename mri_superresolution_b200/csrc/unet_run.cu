@@ -17,7 +17,7 @@ static int64_t grads_final_from(const ParamLayout& pl, const ConvDesc (&conv)[kN
     return l <= 0 ? 0 : pl.off[conv[l].w];
 }
 
-// MRISR_BWD_SIDE=1 (staged, default off, not measured yet): weight-gradient kernels run on a second, lower-priority stream,
+// Side stream (default on, MRISR_BWD_SIDE=0 disables; 0.2 ms of the step on B200): weight-gradient kernels run on a second stream,
 // forked from the main stream once their layer's dR is ready and joined before a gradient-readiness mark is recorded / at the
 // end of backward.  They only read activations and dR (never rewritten during backward: every tensor of the workspace has its
 // own buffer) and write the gradient arena and their own partial-sum scratch, so they are independent of the data-gradient
