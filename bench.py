@@ -686,9 +686,12 @@ def main():
                     help="square network input size; 256 = the headline workload, 512 / 320 = the slice sizes of BASELINE.json "
                          "configs 4 / 5 (use with --mode infer and a --batch that is one rank's chunk)")
     ap.add_argument("--layer-report", default=None, help="write the per-kernel-tag (per layer shape) timing table here")
+    ap.add_argument("--base-filters", type=int, default=32,
+                    help="32 = the headline workload (scripts/train.py:501); 64 = the default of the reference's scripts/infer.py:473")
     args = ap.parse_args()
-    global H, W
+    global H, W, BASE_FILTERS
     H = W = args.input
+    BASE_FILTERS = args.base_filters
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)

@@ -40,18 +40,20 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
-int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols) {
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols,
+                      uint64_t row_stride_elems) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return -6; }
     const uint32_t bytes = box_cols * 2;
     CUtensorMapSwizzle sw = bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                           : bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
-    if (sw == CU_TENSOR_MAP_SWIZZLE_NONE || box_rows > 256 || (cols * 2) % 16 != 0 || ((uintptr_t)base & 15) != 0) {
+    if (sw == CU_TENSOR_MAP_SWIZZLE_NONE || box_rows > 256 || (cols * 2) % 16 != 0 || (row_stride_elems * 2) % 16 != 0 ||
+        ((uintptr_t)base & 15) != 0) {
         set_error("make_tmap_2d_bf16: unsupported box %ux%u / cols %llu / base %p", box_rows, box_cols, (unsigned long long)cols, base);
         return -6;
     }
     const cuuint64_t gdim[2] = {cols, rows};
-    const cuuint64_t gstride[1] = {cols * 2};
+    const cuuint64_t gstride[1] = {(row_stride_elems ? row_stride_elems : cols) * 2};     // a channel slice of a wider tensor
     const cuuint32_t box[2] = {box_cols, box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,

@@ -191,7 +191,9 @@ __device__ __forceinline__ float sliced_partial_sum(const float* __restrict__ fi
     return r;
 }
 
-int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols);
+// row_stride_elems: elements between rows (0 = cols: a dense tensor); > cols addresses a channel slice of a wider tensor
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols,
+                      uint64_t row_stride_elems = 0);
 
 }  // namespace tc
 }  // namespace mrisr

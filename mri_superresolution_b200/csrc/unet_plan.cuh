@@ -59,9 +59,11 @@ inline int layer_engine(const ConvDesc& c, int l, int H, int W, int f) {
         return planar_ok && conv_ring_supported(h, w, c1, c2, c.cout, c.ks) && conv_ring_supported(h, w, c.cout, 0, c.cin, c.ks) &&
                        wgrad_ring_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_RING : ENG_GENERIC;
     }
-    if ((int64_t)(h + 2) * (w + 2) < 128 || c.cout > 256 || c.cin > 256) return ENG_GENERIC;   // GroupNorm-statistics epilogue: <= 2 samples per tile
-    return conv_tc_supported(h, w, c1, c2, c.cout, c.ks) && conv_tc_supported(h, w, c.cout, 0, c.cin, c.ks) &&
-                   wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_TC : ENG_GENERIC;
+    if ((int64_t)(h + 2) * (w + 2) < 128) return ENG_GENERIC;   // GroupNorm-statistics epilogue: <= 2 samples per tile
+    if (!conv_tc_supported(h, w, c1, c2, c.cout, c.ks) || !conv_tc_supported(h, w, c.cout, 0, c.cin, c.ks)) return ENG_GENERIC;
+    // 512-channel layers (base_filters = 64, the default of the reference's scripts/infer.py:473): conv_tc in two 256-column
+    // blocks with the GroupNorm statistics from a separate pass (unet_run.cu), weight gradient over the two halves of dY
+    return wgrad_tc_supported(h, w, c1, c2, c.cout, c.ks) ? ENG_TC : ENG_GENERIC;
 }
 
 // Bump allocator over the caller's workspace (base == nullptr -> size query only).

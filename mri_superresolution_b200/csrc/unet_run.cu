@@ -108,6 +108,15 @@ struct Runner {
                 if (eng(l) == ENG_RING) {
                     TRY(launch_conv_ring(a, s));
                     if (want_stats) TRY(launch_gn_finalize_ring(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W, c.cin, c.cout, count, s));
+                } else if (dst.C > 256) {
+                    // two column blocks per tile: the statistics epilogue covers one block's groups only -> separate pass
+                    // (512 channels only occur at the 32 x 32 bottleneck of base_filters = 64: 1 MB per sample)
+                    a.stat_part = nullptr;
+                    TRY(launch_conv_tc(a, s));
+                    if (want_stats) {
+                        TRY(launch_gn_stats<T>(dst, ws.stat_part, s));
+                        TRY(launch_gn_finalize(ws.stat_part, ws.stats[l], ws.N, stat_slots_generic(dst.H, dst.W, dst.C), count, s));
+                    }
                 } else {
                     TRY(launch_conv_tc(a, s));
                     if (want_stats) TRY(launch_gn_finalize_tc(ws.stat_part, ws.stats[l], ws.N, dst.H, dst.W, count, s));
@@ -271,7 +280,9 @@ struct Runner {
             if (use_tc) {
                 const int c2 = src2.p ? src2.C : 0;
                 if (e == ENG_RING && wgrad_rows_supported(dy.N, dy.H, dy.W, src1.C, c2, dy.C, c.ks)) TRY(launch_wgrad_rows(w, sw));
-                else TRY(e == ENG_RING ? launch_wgrad_ring(w, sw) : launch_wgrad_tc(w, sw));
+                else if (e == ENG_RING) TRY(launch_wgrad_ring(w, sw));
+                else if (wgrad_tc_supported(dy.H, dy.W, src1.C, c2, dy.C, c.ks)) TRY(launch_wgrad_tc(w, sw));
+                else TRY(launch_wgrad_generic<T>(w, sw));
                 done = true;
             }
             else if (l == 0 && conv_first_supported(src1, dy, c.ks)) { TRY(launch_wgrad_first(w, sw)); done = true; }

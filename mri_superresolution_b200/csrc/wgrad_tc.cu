@@ -240,11 +240,13 @@ static WgradPlan make_plan(int N, int H, int W, int C1, int C2, int Cout, int ks
 using bf16 = __nv_bfloat16;
 
 bool wgrad_tc_supported(int H, int W, int C1, int C2, int Cout, int ks) {
-    const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256;
+    // Cout = 512 (the bottleneck of base_filters = 64) runs as two 256-column halves of dY (launch_wgrad_tc)
+    const bool cout_ok = Cout == 16 || Cout == 32 || Cout == 64 || Cout == 128 || Cout == 256 || Cout == 512;
     return cout_ok && C1 >= 16 && C1 % 16 == 0 && C2 % 16 == 0 && (ks == 1 || ks == 3);
 }
 
 size_t wgrad_tc_scratch_elems(int N, int H, int W, int C1, int C2, int Cout, int ks) {
+    if (Cout > 256) Cout = 256;                                  // the halves run one after the other through the same scratch
     const tc::WgradPlan pl = tc::make_plan(N, H, W, C1, C2, Cout, ks);
     const size_t own = (size_t)pl.splits * (size_t)ks * ks * (C1 + C2) * Cout;
     const size_t merged = wgrad_tc3_supported(N, H, W, C1, C2, Cout, ks) ? wgrad_tc3_scratch_elems(N, H, W, C1, C2, Cout) : 0;
@@ -264,6 +266,19 @@ int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
         set_error("wgrad_tc: unsupported shape C1=%d C2=%d Cout=%d ks=%d", C1, C2, Cout, a.ks);
         return -2;
     }
+    if (Cout == 512) {
+        // one MMA holds N <= 256: two launches over the channel halves of dY (same pixel stride, dw rows [256 h, 256 h + 256))
+        for (int h = 0; h < 2; ++h) {
+            WgradArgs<bf16> b = a;
+            b.dy.p = a.dy.p + 256 * h;
+            b.dy.C = 256;
+            b.dy.ps = a.dy.ps ? a.dy.ps : a.dy.C;
+            b.dw = a.dw + (size_t)256 * h * Cin * a.ks * a.ks;
+            const int rc2 = launch_wgrad_tc(b, s);
+            if (rc2) return rc2;
+        }
+        return 0;
+    }
     if (use_tc3() && wgrad_tc3_supported(N, H, W, C1, C2, Cout, a.ks)) return launch_wgrad_tc3(a, s);
     const char* tag = "wgrad_tc";
     char tbuf[96];
@@ -279,7 +294,8 @@ int launch_wgrad_tc(const WgradArgs<bf16>& a, cudaStream_t s) {
     if (rc) return rc;
     if (C2) { rc = tc::make_tmap_2d_bf16(&tX2, a.src2.p, (uint64_t)rows, (uint64_t)C2, tc::kBKP, (uint32_t)pl.CS); if (rc) return rc; }
     else tX2 = tX1;
-    rc = tc::make_tmap_2d_bf16(&tDY, a.dy.p, (uint64_t)rows, (uint64_t)Cout, tc::kBKP, (uint32_t)pl.CSB);
+    rc = tc::make_tmap_2d_bf16(&tDY, a.dy.p, (uint64_t)rows, (uint64_t)Cout, tc::kBKP, (uint32_t)pl.CSB,
+                               (uint64_t)(a.dy.ps > Cout ? a.dy.ps : 0));
     if (rc) return rc;
 
     tc::WgradTcParams p;

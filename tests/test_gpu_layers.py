@@ -264,5 +264,12 @@ def test_every_layer_forward_and_backward_bf16_ragged_shape():
     _run_layers("bf16", 16, 3, 24, 40)
 
 
+def test_every_layer_forward_and_backward_bf16_base_filters_64():
+    """f = 64 is the default of the reference's inference command (scripts/infer.py:473) and of its load_model (:50): 512
+    channels at the bottleneck (conv_tc in two column blocks with a separate statistics pass, CUDA-core weight gradient:
+    unet_plan.cuh layer_engine), NHWC at every level.  128 x 128 so that the 16 x 16 bottleneck is on the tensor-core kernels."""
+    _run_layers("bf16", 64, 2, 128, 128)
+
+
 def test_every_layer_forward_and_backward_fp32_mode():
     _run_layers("fp32", 16, 2, 32, 48)

@@ -14,3 +14,6 @@ cp gpurun_out/${tag}_traffic.json profiles/r02_traffic.json
 timeout 900 python bench.py --layer-report gpurun_out/${tag}_layers.txt > gpurun_out/${tag}_bench.log 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
 grep '^{' gpurun_out/${tag}_bench.log | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.readline()); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline'])"
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${tag}_bench_ref.log 2>&1; grep '^{' gpurun_out/${tag}_bench_ref.log | tail -1 | cut -c1-160
+# base_filters = 64 (the default of the reference's inference command): side records
+timeout 600 python bench.py --base-filters 64 --mode infer --no-cpu-baseline --no-eager-baseline > gpurun_out/${tag}_bench_f64_infer.log 2>&1; grep '^{' gpurun_out/${tag}_bench_f64_infer.log | tail -1 | cut -c1-170
+timeout 600 python bench.py --base-filters 64 --no-cpu-baseline --no-eager-baseline --no-infer --steps 5 --layer-report gpurun_out/${tag}_layers_f64.txt > gpurun_out/${tag}_bench_f64_train.log 2>&1; grep '^{' gpurun_out/${tag}_bench_f64_train.log | tail -1 | cut -c1-170
