@@ -463,12 +463,14 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, k):
+    def timed(fn, k, tail=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(k):
             fn()
+        if tail is not None:
+            tail()                               # work still in flight on another stream joins before the closing event
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -604,6 +606,41 @@ def run_ours(args):
                                      "pinned host memory every step"},
                  "workload": f"inference forward (scripts/infer.py:268-276) of the same model, batch {nb}/GPU, {H}x{W} -> {2 * H}x{2 * W}",
                  "unet_conv_tflops": round(unet_flops_per_slice(BASE_FILTERS, H, W, False) * nb / (ms_i / args.steps * 1e-3) / 1e12, 2)}
+        # the same forward in the formats scripts/infer.py moves: 8-bit gray levels in (PNG, :97), percentile window + min-max
+        # on the device (:97-130), 8-bit images out ((x * 255).astype(uint8), :331); the copy of step i's images overlaps step i + 1
+        from mri_superresolution_b200.utils.preprocess import preprocess_images
+        u8_pin = (torch.rand(nb, H, W, generator=torch.Generator().manual_seed(SEED)) * 255).to(torch.uint8).pin_memory()
+        y8_pin = [torch.empty((nb, 2 * H, 2 * W), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        y8_dev = [None, None]
+        ev_ready = [torch.cuda.Event() for _ in range(2)]
+        ev_done = [torch.cuda.Event() for _ in range(2)]
+        copy_stream = torch.cuda.Stream()
+        slot = [0]
+
+        def infer_png():
+            k = slot[0]
+            y = gf(preprocess_images(u8_pin.to(dev, non_blocking=True)))
+            y8_dev[k] = (y[:, 0] * 255).to(torch.uint8)
+            ev_ready[k].record()
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ev_ready[k])
+                y8_pin[k].copy_(y8_dev[k], non_blocking=True)
+                ev_done[k].record()
+            slot[0] = k ^ 1
+            ev_done[k ^ 1].synchronize()                  # the previous step's images are on the host
+
+        with torch.cuda.stream(copy_stream):
+            for e in ev_done:
+                e.record()
+        for _ in range(3):
+            infer_png()
+        ms_ip = timed(infer_png, e2e_steps, tail=lambda: torch.cuda.current_stream().wait_stream(copy_stream))
+        copy_stream.synchronize()
+        infer["e2e_png_formats"] = {
+            "value": nb * world * e2e_steps / (ms_ip * 1e-3), "unit": "slices/s", "ms_per_step": ms_ip / e2e_steps,
+            "h2d_bytes_per_step": nb * H * W, "d2h_bytes_per_step": nb * 4 * H * W,
+            "pipeline": "pinned uint8 slices -> device -> percentile window + min-max (mrisr_percentile_normalize_u8) -> "
+                        "GraphedForward -> x 255 truncated to uint8 -> pinned host, the copy overlapping the next step"}
         gf.close()
         del gf, feeder_i
         model.train()
