@@ -193,6 +193,7 @@ __host__ __device__ __forceinline__ RowMap row_map(const Act<T>& t, int nthr, in
 }
 // rows of `units_w` columns per block so that a block of nthr threads handles about `per_thread` units per thread
 inline int rows_per_block(int units_w, int nv, int nthr, int per_thread) {
+    if (units_w <= 0 || nv <= 0) return 1;        // e.g. the pooled width of a one-pixel-wide level: no such launch, size queries only
     const int r = (nthr * per_thread) / (units_w * nv);
     return r < 1 ? 1 : r;
 }

@@ -537,6 +537,34 @@ def test_vgg_fp32_mode_agrees_with_bf16_mode_and_rejects_bad_precision(golden_di
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(32, 1, 8, 8), (32, 3, 16, 8), (16, 2, 8, 24), (64, 1, 8, 8)])
+def test_smallest_slices_forward_and_train_step(shape):
+    """8-pixel edges: one pixel at the deepest level (every layer falls back to the kernels without tile-size floors).  fp32
+    mode against the oracle at 1e-4; bf16 mode runs a whole train step and stays finite."""
+    from mri_superresolution_b200.models.unet_model import UNetSuperRes
+    from mri_superresolution_b200.utils.losses import CombinedLoss
+    f, n, h, w = shape
+    params = UO.init_params(f, seed=77)
+    x, t = make_pairs(n, h, w, seed=78)
+    x, t = x.to(_dev()), t.to(_dev())
+    m = UNetSuperRes(base_filters=f, precision="fp32").to(_dev())
+    m.load_state_dict(params)
+    m.train()
+    y = m(x)
+    ref = UO.unet_forward(params, x.cpu())
+    assert float((y.detach().cpu() - ref).abs().max()) < 1e-4 * max(1.0, float(ref.abs().max()))
+    CombinedLoss(ssim_weight=0.4)(y, t).backward()
+    assert all(torch.isfinite(p.grad).all() for p in m.parameters())
+    mb = UNetSuperRes(base_filters=f).to(_dev())
+    mb.load_state_dict(params)
+    mb.train()
+    yb = mb(x)
+    CombinedLoss(ssim_weight=0.4)(yb, t).backward()
+    assert torch.isfinite(yb).all() and all(torch.isfinite(p.grad).all() for p in mb.parameters())
+    assert float((yb.detach().cpu() - ref).norm() / ref.norm()) < 0.1
+
+
+@pytest.mark.gpu
 def test_device_prefetcher_order_and_reuse():
     """DevicePrefetcher hands out every host batch once, in order, while the next one is being staged."""
     from mri_superresolution_b200.utils.prefetch import DevicePrefetcher

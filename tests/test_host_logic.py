@@ -57,6 +57,11 @@ def test_shape_validation_and_workspace_query():
     assert b"multiples of 8" in L.mrisr_last_error()
     assert L.mrisr_unet_workspace_bytes(2, 32, 32, 24, _native.FP32, 1) == 0        # f % 16 != 0
     assert L.mrisr_unet_workspace_bytes(2, 32, 32, 16, 7, 1) == 0                   # unknown precision
+    # the smallest legal slices (one pixel at the deepest level): the size arithmetic used to divide by the zero pooled width
+    for h, w in ((8, 8), (16, 8), (8, 24)):
+        for f in (16, 32, 64):
+            for prec in (_native.BF16, _native.FP32):
+                assert L.mrisr_unet_workspace_bytes(1, h, w, f, prec, 1) > L.mrisr_unet_workspace_bytes(1, h, w, f, prec, 0) > 0
     rc = L.mrisr_unet_forward(None, None, None, None, 0, 1, 8, 8, 16, 0, 0, None)
     assert rc == -1
 
