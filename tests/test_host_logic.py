@@ -462,3 +462,40 @@ def test_cli_argument_surface_matches_the_reference():
     assert (b.target, b.checkpoint_dir, b.checkpoint_path, b.model_type, b.base_filters) == (None, "./checkpoints", None, "unet", 64)
     with pytest.raises(SystemExit):
         T.parse_args(["--full_res_dir", "hr", "--low_res_dir", "lr", "--model_type", "cnn"])
+
+
+def test_size_queries_survive_degenerate_arguments():
+    """Every host-only size / layout query of include/mrisr.h with zero, negative, misaligned and oversized arguments: a number or
+    0 comes back, the process does not die (an 8-pixel-wide slice used to divide by zero in the workspace arithmetic).  Run in a
+    child process so that a crash fails this test instead of the session."""
+    import subprocess
+    import sys
+    body = """
+import ctypes as C, itertools
+from mri_superresolution_b200 import _native
+L = _native.lib()
+for n, h, w, f, p, t in itertools.product((0, 1, -1, 3), (0, 8, 16, -8, 24, 2048), (0, 8, 16, 1024), (0, 16, 32, 48, 64, -16, 8), (0, 1, 2, 7), (0, 1)):
+    L.mrisr_unet_workspace_bytes(n, h, w, f, p, t)
+for f in (0, 8, 16, 32, 64, 128, -16, 24):
+    L.mrisr_unet_param_elems(f)
+    for i in (-1, 0, 5, 63, 64, 100):
+        L.mrisr_unet_param_offset(f, i); L.mrisr_unet_param_size(f, i)
+    for c in (-1, 0, 19, 20):
+        L.mrisr_unet_grads_final_from(f, c)
+for f, l, h, w in itertools.product((0, 16, 32, 64, -1), (-1, 0, 8, 19, 20), (0, 8, 256, 1024), (0, 8, 256, 1024)):
+    L.mrisr_unet_layer_engine(f, l, h, w)
+for n, h, w in itertools.product((0, 1, -1, 64), (0, 1, 31, 512, -3), (0, 1, 33, 512)):
+    L.mrisr_l1_ssim_scratch_bytes(n, h, w); L.mrisr_image_metrics_scratch_bytes(n, h, w)
+    L.mrisr_kspace_scratch_bytes(n, h, w); L.mrisr_robust_normalize_scratch_bytes(n, h, w)
+    L.mrisr_match_histograms_scratch_bytes(n, h, w, h, w)
+for n, h, w, c1, c2, co, ks in itertools.product((0, 1), (0, 1, 16), (0, 24), (0, 8, 16, 512, 24), (0, 16, 512), (0, 8, 256, 512, 24), (0, 1, 3, 5)):
+    L.mrisr_conv2d_scratch_bytes(n, h, w, c1, c2, co, ks)
+for cfg in ([], [64], [64, -1], [-1, 64], [64, 64, -1, 128], [7], [64] * 40, [64, -1, -1, 128], [0], [512, 512]):
+    a = (C.c_int * max(1, len(cfg)))(*cfg)
+    L.mrisr_vgg_weight_elems(a, len(cfg)); L.mrisr_vgg_packed_bytes(a, len(cfg))
+    for n, h, w, g in itertools.product((0, 1, -1), (0, 16, 24, 256), (0, 16, 48), (0, 1)):
+        L.mrisr_vgg_workspace_bytes(n, h, w, a, len(cfg), g); L.mrisr_vgg_workspace_bytes_fp32(n, h, w, a, len(cfg), g)
+print("survived")
+"""
+    r = subprocess.run([sys.executable, "-c", body], capture_output=True, text=True, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0 and "survived" in r.stdout, (r.returncode, r.stderr[-500:])
