@@ -1,7 +1,8 @@
 """Data-parallel CUDA-graph check, run under torchrun on >= 2 GPUs:
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/check_graph_dp.py
 Three training steps with the eager data-parallel step and with GraphedTrainStep(buckets=...) from the same initial state must
-give the same parameters on every rank (same kernels, same NCCL reductions, only launched differently)."""
+give the same parameters on every rank (same kernels, same NCCL reductions, only launched differently).
+CHECK_BASE_FILTERS=16 / 64 runs the same check at another width (another bucket plan)."""
 import os
 import sys
 
@@ -29,7 +30,7 @@ def main():
     results = []
     for use_graph in (False, True):
         torch.manual_seed(7)
-        model = UNetSuperRes(base_filters=32).to(dev)
+        model = UNetSuperRes(base_filters=int(os.environ.get("CHECK_BASE_FILTERS", "32"))).to(dev)
         crit = CombinedLoss(ssim_weight=0.4)
         opt = FusedAdam(model, lr=1e-3, weight_decay=1e-5, capturable=use_graph)
         buckets = GradientBuckets(model)
